@@ -1,0 +1,78 @@
+/* thcm_oracle.h -- C ABI of the CPU oracle (TEST INFRASTRUCTURE, never shipped).
+ *
+ * The oracle is a structure-faithful C++ restatement of the reference's Fortran THCM
+ * kernels (src/ocean/{usrc,spf,boundary,assemble,matetc,forcing,grid,mix_imp}.F90) plus
+ * the C++ glue of src/ocean/THCM.C (static graph, sign flip, integral condition) and of
+ * src/gmressolver/GMRESSolver.H.  It materialises the dense stencil tensor An(27,6,6,n,m,l)
+ * exactly like the reference does.
+ *
+ * PARITY STATUS: the reference itself cannot be built in this image (no Fortran compiler,
+ * no MPI, no Trilinos), and its tests hold no stored RHS/Jacobian vectors, so the oracle is
+ * pinned by the reference's own invariants I1-I6, not by golden vectors:
+ * "parity unpinned" beyond those invariants.
+ *
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs
+ * may call anything declared here.
+ */
+#ifndef THCM_ORACLE_H
+#define THCM_ORACLE_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct thcm_oracle thcm_oracle;
+
+/* Mirrors the argument list of Fortran init (usrc.F90:6-139) + m_global::initialize flags. */
+typedef struct {
+  int n, m, l;
+  double xmin, xmax, ymin, ymax; /* radians (THCM.C:201-204 converts degrees) */
+  int periodic;
+  double hdim, qz;
+  double alphaT, alphaS;
+  int ih, vmix, tap, rho_mixing, coriolis_on, forcing_type;
+  int tres, sres, iza, ite, its;
+  int coupled_T, coupled_S;
+  int int_sign;          /* "Salinity Integral Sign", THCM.C:254 */
+  int intcond_i, intcond_j; /* "Integral row coordinate i/j" (0-based, -1 = N-1 / M-1) */
+  int fix_pressure_points;
+} thcm_oracle_config;
+
+thcm_oracle* thcm_oracle_create(const thcm_oracle_config* cfg, const int* landm /* (n+2)(m+2)(l+2), i fastest */);
+void thcm_oracle_destroy(thcm_oracle*);
+
+void thcm_oracle_set_par(thcm_oracle*, int idx1, double value); /* setparcs, usrc.F90:163 */
+double thcm_oracle_get_par(thcm_oracle*, int idx1);
+int thcm_oracle_ndim(thcm_oracle*);
+
+/* Fortran-level entry points (usrc.F90:432, :506): value-dependent CSR, 1-based. */
+void thcm_oracle_fortran_rhs(thcm_oracle*, const double* un, double* B);
+void thcm_oracle_fortran_matrix(thcm_oracle*, const double* un);
+int64_t thcm_oracle_fortran_nnz(thcm_oracle*);
+void thcm_oracle_fortran_csr(thcm_oracle*, int* begA, int* jcoA, double* coA, double* coB);
+void thcm_oracle_frc(thcm_oracle*, double* frc); /* current Frc (after boundaries masking) */
+
+/* THCM.C level (THCM::evaluate :949-1192): static CreateMaximalGraph pattern, 0-based. */
+int64_t thcm_oracle_graph_nnz(thcm_oracle*);
+void thcm_oracle_graph(thcm_oracle*, int* rowptr /* ndim+1 */, int* col /* nnz */);
+void thcm_oracle_eval_rhs(thcm_oracle*, const double* x, double* F);
+void thcm_oracle_eval_jac(thcm_oracle*, const double* x, double* val /* nnz */, double* diagB /* ndim */);
+int thcm_oracle_rowintcon(thcm_oracle*);
+void thcm_oracle_intcond_coeff(thcm_oracle*, double* c /* ndim */);
+void thcm_oracle_set_intcond_correction(thcm_oracle*, double corr);
+int64_t thcm_oracle_dropped_entries(thcm_oracle*); /* Fortran entries outside the static graph in the last eval_jac */
+
+/* matAvec-order CSR SpMV (matetc.F90:147-166), 0-based CSR. */
+void thcm_oracle_spmv(int nrows, const int* rowptr, const int* col, const double* val, const double* x, double* y);
+
+/* GMRESSolver.H:81-255 restated for plain vectors; prec: 0 none, 1 = 6x6 point-block Jacobi
+ * (blocks given inverted, row-major, nrows/6 of them) applied as right (flexible) preconditioner.
+ * hist[it] = resid_ after inner iteration it (length >= maxit+2).  Returns GMRESSolver::solve() code. */
+int thcm_oracle_gmres(int nrows, const int* rowptr, const int* col, const double* val,
+                      const double* b, double* x, int m, int maxit, double tol,
+                      int prec, const double* blockinv, double* hist, int* iters);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
