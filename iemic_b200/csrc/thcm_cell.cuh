@@ -1,0 +1,52 @@
+// thcm_cell.cuh -- one (cell, unknown) row from start to finish: build, boundaries, filter, store / contract.
+// Shared by the CUDA kernels (thcm_kernels.cu) and by the host harness in tests/ (host_rowcheck.cpp).
+#pragma once
+#include "thcm_rows.cuh"
+
+namespace thcm {
+
+// Rows the C++ glue of the reference overwrites after the Fortran call (THCM.C:1006-1033, :1160-1165).
+struct SpecialRows { int rowintcon, rowPfix1, rowPfix2; };
+
+// Jacobian row A of cell c -> `out` (first stored value of the row in the static CSR), returns diag(B) entry.
+// The integral-condition row is left untouched (its dense values are static, written by jac_intcond_row).
+template <int A, class F, class Out>
+THCM_HD double jac_row(const Scalars& S, const Tables& T, const Cell& c, const F& f, const SpecialRows& sp, int row, Out out) {
+  Row<A> r;
+  JacRow<A, F>::build(r, S, T, c, f);
+  apply_boundaries<A>(r, c.sig);
+  filter_row<A>(r);
+  // fillcolB (assemble.F90:18-54) times "Mass" = 1 (THCM.C:1150-1153)
+  double b = 0.0;
+  if (!sbit(c.sig, SIG_NOTOCEAN)) {
+    if (A == UU) b = sbit(c.sig, SIG_BU) ? -S.epsr : 0.0;
+    if (A == VV) b = sbit(c.sig, SIG_BV) ? -S.epsr : 0.0;
+    if (A == TT || A == SS) b = -1.0;
+  }
+  if (row == sp.rowintcon) return 0.0;                    // intcond_S, THCM.C:2137-2139
+  if constexpr (A == PP) {
+    if (row == sp.rowPfix1 || row == sp.rowPfix2) { // fixPressurePoints, THCM.C:2201-2238
+      r.clear();
+      r.template at<5, PP>() = 1.0;
+      b = 0.0;
+    }
+  }
+  emit_row<A>(r, S, c, out);
+  return b;
+}
+
+// Residual row A of cell c: F = -( (-Au - mix + Frc) * (1-landm) )   (usrc.F90:559-574, THCM.C:1003)
+// X::raw(di,dj,dk,var) gives raw neighbour state; mixv is the mixing term of this row (0 unless T/S).
+template <int A, class F, class X>
+THCM_HD double rhs_row(const Scalars& S, const Tables& T, const Cell& c, const F& f, const X& x, double frc, double mixv) {
+  Row<A> r;
+  RhsRow<A, F>::build(r, S, T, c, f);
+  apply_boundaries<A>(r, c.sig);
+  filter_row<A>(r);
+  double Au = row_dot<A>(r, x);
+  double B = -Au - mixv + frc - 0.0;
+  B = B * (sbit(c.sig, SIG_LANDVAL) ? 0.0 : 1.0);
+  return B * -1.0;
+}
+
+} // namespace thcm

@@ -1,0 +1,409 @@
+// thcm_host.cpp -- see thcm_host.h.  Compiled by the host compiler with -ffp-contract=off so that the
+// coefficient tables carry exactly the roundings of the reference's (FMA-free) Fortran expressions.
+#include "thcm_host.h"
+#include <cmath>
+#include <cstring>
+#include <stdexcept>
+#include <algorithm>
+
+namespace thcm {
+namespace {
+const double pi = 3.14159265358979323846; // par.F90:14
+// usr.F90:129-160
+const double omegadim = 7.292e-05, r0dim = 6.37e+06, udim = 0.1e+00, gdim = 9.8e+00, rhodim = 1.024e+03;
+const double s0 = 35.0, cp0 = 4.2e+03, deltas = 1.0;
+const double alpt1 = 2.93, alpt2 = 8.3e-02, alpt3 = 6.6e-04;
+const double ah = 2.5e+05, av = 1.0e-03, kappah = 1.0e+03, kappav = 1.0e-04;
+const double zmin = -1.0, zmax = 0.0;
+enum { OCEAN = 0, LAND = 1, PERIO = 3 };
+
+// grid.F90:62-95
+double fz(double z, double qz) {
+  if (qz > 1.0) return -1 + std::tanh(qz * (z + 1)) / std::tanh(qz);
+  return z + (1. - qz) * z * (1 - z);
+}
+double dfdz(double z, double qz) {
+  if (qz > 1.0) { double c = std::cosh(qz * (z + 1)); return qz / (std::tanh(qz) * c * c); }
+  return 1.0 + (1. - qz) * (1. - 2. * z);
+}
+// spf.F90:795-853
+double amh(double y, int ih) { return ih == 0 ? 1.0 : 1. + 10.0 * std::exp(-5 * y * y); }
+double bmh(double y, int ih) { return ih == 0 ? 1.0 : 1.0 + 10.0 * std::exp(-5 * y * y); }
+double bmhy(double y, int ih) { return ih == 0 ? 0.0 : -10. * 10.0 * y * std::exp(-5 * y * y); }
+} // namespace
+
+Host::Host(const Config& c, const int* landm_in) : cfg(c), n(c.n), m(c.m), l(c.l) {
+  if (n < 3 || m < 2 || l < 2) throw std::runtime_error("thcm_b200: grid too small (need n>=3, m>=2, l>=2)");
+  ncell = (size_t)n * m * l;
+  ndim = 6 * ncell;
+  if (105ull * ncell > 0x7fffffffull) throw std::runtime_error("thcm_b200: grid too large for 32-bit CSR offsets");
+  version = 1; mask_version = 0; intCorrection = 0.0;
+  make_grid();
+  stpnt();
+  check_supported();
+  set_landmask(landm_in); // signatures, graph, tables, forcing
+}
+
+// grid.F90:2-60
+void Host::make_grid() {
+  x.assign(n + 1, 0); y.assign(m + 2, 0); z.assign(l + 1, 0); xu.assign(n + 1, 0); yv.assign(m + 1, 0);
+  zw.assign(l + 1, 0); dfzT.assign(l + 1, 0); dfzW.assign(l + 1, 0);
+  dx = (cfg.xmax - cfg.xmin) / n;
+  dy = (cfg.ymax - cfg.ymin) / m;
+  dz = (zmax - zmin) / l;
+  for (int i = 1; i <= n; i++) { x[i] = ((double)i - 0.5) * dx + cfg.xmin; xu[i] = ((double)i) * dx + cfg.xmin; }
+  xu[0] = cfg.xmin;
+  for (int j = 1; j <= m; j++) { y[j] = ((double)j - 0.5) * dy + cfg.ymin; yv[j] = ((double)j) * dy + cfg.ymin; }
+  y[0] = y[1] - dy; y[m + 1] = y[m] + dy; yv[0] = cfg.ymin;
+  for (int k = 1; k <= l; k++) {
+    double ze = ((double)k - 0.5) * dz + zmin, zwe = ((double)k) * dz + zmin;
+    z[k] = fz(ze, cfg.qz); zw[k] = fz(zwe, cfg.qz);
+    dfzT[k] = dfdz(ze, cfg.qz); dfzW[k] = dfdz(zwe, cfg.qz);
+  }
+  zw[0] = zmin; dfzW[0] = dfdz(zmin, cfg.qz);
+}
+
+// usrc.F90:1136-1172 and mix_imp.f:92-107
+void Host::stpnt() {
+  for (int i = 0; i <= NPAR; i++) par[i] = 0.0;
+  const double hdim = cfg.hdim;
+  par[P_AL_T] = 0.1 / (2 * omegadim * rhodim * hdim * udim * dz * dfzT[l]);
+  par[P_RAYL] = cfg.alphaT * gdim * hdim / (2 * omegadim * udim * r0dim);
+  par[P_EK_V] = av / (2 * omegadim * hdim * hdim);
+  par[P_EK_H] = ah / (2 * omegadim * r0dim * r0dim);
+  par[P_ROSB] = udim / (2 * omegadim * r0dim);
+  par[P_PE_H] = kappah / (udim * r0dim);
+  par[P_PE_V] = kappav * r0dim / (udim * hdim * hdim);
+  par[P_P_VC] = 2.5e+04 * par[P_PE_V];
+  par[P_LAMB] = cfg.alphaS / cfg.alphaT;
+  par[P_BIOT] = r0dim / (75. * 3600. * 24. * udim);
+  par[P_ALPC] = 1.0; par[P_ENER] = 1.0e+02;
+  par[P_SPL1] = 2.0e+03; par[P_SPL2] = 0.01;
+  if (cfg.vmix == 0) { par[P_MIXP] = 0.0; par[P_P_VC] = 0.0; par[P_ALPC] = 1.0; par[P_ENER] = 1.0e+2; par[P_MKAP] = 0.0; }
+}
+
+// What the B200 path implements; everything else fails loudly instead of silently diverging.
+void Host::check_supported() const {
+  if (cfg.vmix != 0 && cfg.vmix != 1) throw std::runtime_error("thcm_b200: Mixing must be 0 or 1 (adaptive partitioning, vmix=2, is not on the B200 path)");
+  if (cfg.iza != 2 || cfg.ite != 1 || cfg.its != 1) throw std::runtime_error("thcm_b200: only idealized forcing (Wind Forcing Type=2, Levitus T=1, Levitus S=1) is supported");
+  if (cfg.coupled_S != 0) throw std::runtime_error("thcm_b200: Coupled Salinity=1 is not on the B200 path yet");
+  if (std::abs(cfg.int_sign) != 1) throw std::runtime_error("thcm_b200: invalid integral sign"); // THCM.C:277-280
+}
+
+void Host::set_par(int idx1, double value) {
+  if (idx1 >= 1 && idx1 <= NPAR) par[idx1] = value;
+  // neutral physics / GM / consistent mixing would add 27-point T,S couplings outside the static graph
+  if (cfg.vmix != 0 && (par[P_MIXP] * par[P_PE_H] != 0.0 || par[P_MKAP] * par[P_PE_H] != 0.0 || (1.0 - par[P_ALPC]) * par[P_ENER] * par[P_PE_V] != 0.0))
+    throw std::runtime_error("thcm_b200: MIXP/MKAP/ALPC settings enable neutral-physics or consistent mixing, which the B200 path does not implement");
+  build_tables();
+  build_forcing();
+  version++;
+}
+
+// init (usrc.F90:79-107) and set_landmask (usrc.F90:336-395) border rules
+void Host::set_landmask(const int* landm_in) {
+  landm.assign((size_t)(n + 2) * (m + 2) * (l + 2), OCEAN);
+  const bool per = cfg.periodic != 0;
+  auto L = [&](int i, int j, int k) -> int& { return landm[(size_t)i + (size_t)(n + 2) * (j + (size_t)(m + 2) * k)]; };
+  size_t pos = 0;
+  for (int k = 0; k <= l + 1; k++) for (int j = 0; j <= m + 1; j++) for (int i = 0; i <= n + 1; i++) {
+    int v = landm_in[pos++];
+    if (!per && v == PERIO) v = OCEAN;
+    L(i, j, k) = v;
+  }
+  for (int i = 1; i <= n; i++) for (int j = 1; j <= m; j++) for (int k = l; k >= 2; k--) // land inversion fix
+    if (L(i, j, k) == LAND && L(i, j, k - 1) == OCEAN) L(i, j, k - 1) = LAND;
+  for (int k = 0; k <= l + 1; k++) for (int j = 0; j <= m + 1; j++) if (!per) { L(0, j, k) = LAND; L(n + 1, j, k) = LAND; }
+  for (int k = 0; k <= l + 1; k++) for (int i = 0; i <= n + 1; i++) { L(i, 0, k) = LAND; L(i, m + 1, k) = LAND; }
+  for (int j = 0; j <= m + 1; j++) for (int i = 0; i <= n + 1; i++) { L(i, j, 0) = LAND; L(i, j, l + 1) = LAND; }
+  for (int k = 1; k <= l; k++) for (int j = 1; j <= m; j++) for (int i = 1; i <= n; i++)
+    if (L(i, j, k) != OCEAN && L(i, j, k) != LAND) throw std::runtime_error("thcm_b200: interior land mask values must be 0 (ocean) or 1 (land)");
+  // THCM.C:647-704 integral condition row
+  rowintcon = -1;
+  if (cfg.sres == 0) {
+    int Nic = cfg.intcond_i == -1 ? n - 1 : cfg.intcond_i, Mic = cfg.intcond_j == -1 ? m - 1 : cfg.intcond_j;
+    if (Nic < 0 || Nic >= n || Mic < 0 || Mic >= m || L(Nic + 1, Mic + 1, l) != OCEAN)
+      throw std::runtime_error("thcm_b200: integral row coordinates give a land point"); // THCM.C:678-682
+    rowintcon = 6 * (((l - 1) * m + Mic) * n + Nic) + SS - 1;
+  }
+  if (cfg.fix_pressure_points) { // THCM.C:763-772
+    rowPfix1 = 6 * (((l - 1) * m + (m - 1)) * n + (n - 1)) + PP - 1;
+    rowPfix2 = 6 * (((l - 1) * m + (m - 1)) * n + (n - 2)) + PP - 1;
+  } else { rowPfix1 = -1; rowPfix2 = -1; }
+  // thcm_utils.F90:285-323
+  intcond.assign(ndim, 0.0);
+  for (int k = 1; k <= l; k++) for (int j = 1; j <= m; j++) for (int i = 1; i <= n; i++)
+    if (L(i, j, k) == OCEAN) intcond[6 * ((((size_t)k - 1) * m + (j - 1)) * n + (i - 1)) + SS - 1] = std::cos(y[j]) * dfzT[k];
+  build_signatures();
+  build_graph();
+  build_tables();
+  build_forcing();
+  version++; mask_version++;
+}
+
+void Host::build_signatures() {
+  sig.assign(ncell, 0);
+  const bool per = cfg.periodic != 0;
+  auto isLand = [&](int i, int j, int k) { return lm(i, j, k) == LAND; };
+  auto isoc = [&](int i, int j, int k) { int v = lm(i, j, k); return v == OCEAN || v == PERIO; };
+  for (int k = 1; k <= l; k++) for (int j = 1; j <= m; j++) for (int i = 1; i <= n; i++) {
+    uint64_t g = 0;
+    for (int s = 1; s <= 27; s++)
+      if (isLand(i + slot_di(s), j + slot_dj(s), k + slot_dk(s))) g |= 1ull << (s - 1);
+    if (i < n) {
+      if (isLand(i + 2, j - 1, k)) g |= 1ull << SIG_SOUTHEE;
+      if (isLand(i + 2, j, k)) g |= 1ull << SIG_EASTEAST;
+      if (isLand(i + 2, j + 1, k)) g |= 1ull << SIG_NORTHEE;
+      if (j < m && isLand(i + 2, j + 2, k)) g |= 1ull << SIG_NNORTHEE;
+    }
+    if (j < m && isLand(i, j + 2, k)) g |= 1ull << SIG_NN;
+    if (lm(i, j, k) != OCEAN) g |= 1ull << SIG_NOTOCEAN;
+    if (lm(i, j, k) == 1) g |= 1ull << SIG_LANDVAL;
+    // usol: u,v at corner (i,j) are zeroed by any land cell (i',j') in {i,i+1}x{j,j+1} with i'<=n, j'<=m (:1087-1102),
+    // by the north wall j=M (:1055-1058) and, without periodicity, by the east wall i=N (:1044-1047).
+    bool live = !(j == m) && !(!per && i == n);
+    for (int di = 0; di <= 1 && live; di++) for (int dj = 0; dj <= 1; dj++) {
+      int ii = i + di, jj = j + dj;
+      if (ii <= n && jj <= m && lm(ii, jj, k) == 1) live = false;
+    }
+    if (live) g |= 1ull << SIG_LIVE;
+    if (per && i == n) { // u(0,j,k): zeroed only by land cells (1,j,k) and (1,j+1,k)
+      bool lw = !(lm(1, j, k) == 1) && !(j + 1 <= m && lm(1, j + 1, k) == 1);
+      if (lw) g |= 1ull << SIG_LIVEWRAP;
+    }
+    if (isoc(i, j, k) && isoc(i, j, k + 1)) g |= 1ull << SIG_FACE_UP;
+    if (isoc(i, j, k) && isoc(i, j, k - 1)) g |= 1ull << SIG_FACE_DN;
+    if (!isLand(i + 1, j, k)) g |= 1ull << SIG_BU;
+    if (!isLand(i, j + 1, k)) g |= 1ull << SIG_BV;
+    sig[(((size_t)k - 1) * m + (j - 1)) * n + (i - 1)] = g;
+  }
+}
+
+
+Tables Host::tables(const double* base) const {
+  Tables T;
+  const size_t nj = (size_t)m + 2, nk = (size_t)l + 1;
+  const double* p = base;
+  const double** jt[NJTAB] = {&T.cdxu, &T.cdyu, &T.cyv, &T.tanv, &T.cdxt, &T.cdyt,
+                              &T.uu_we, &T.uu_s, &T.uu_n, &T.uu_ch, &T.uv_c, &T.uv_w, &T.uv_e,
+                              &T.vv_we, &T.vv_s, &T.vv_n, &T.vv_ch, &T.vu_c, &T.vu_w, &T.vu_e,
+                              &T.pu, &T.pv_s, &T.pv_n, &T.tt_we, &T.tt_s, &T.tt_n, &T.tt_ch, nullptr, nullptr};
+  for (int q = 0; q < NJTAB; q++) { if (jt[q]) *jt[q] = p; p += nj; }
+  const double** kt[NKTAB] = {&T.uu_b, &T.uu_t, &T.uu_cv, &T.tt_b, &T.tt_t, &T.tt_cv, &T.wp, &T.pw, &T.tdzi8, &T.dfzT, &T.dzdfzT, &T.dzdfzW};
+  for (int q = 0; q < NKTAB; q++) { *kt[q] = p; p += nk; }
+  return T;
+}
+
+// Coefficients of the linear operator Al (lin, usrc.F90:588-772) and of the atoms in spf.F90, tabulated
+// per latitude / per level with the reference's own expression order.
+void Host::build_tables() {
+  const size_t nj = (size_t)m + 2, nk = (size_t)l + 1;
+  tab.assign(NJTAB * nj + NKTAB * nk, 0.0);
+  Tables T = tables(tab.data());
+  auto W = [](const double* p) { return const_cast<double*>(p); };
+  const int ih = cfg.ih;
+  const double EV = par[P_EK_V], EH = par[P_EK_H], ph = (1 - par[P_MIXP]) * par[P_PE_H], pv = par[P_PE_V];
+  const double lambda = par[P_LAMB], xes = par[P_NLES], bi = par[P_BIOT], Ra = par[P_RAYL];
+  for (int j = 0; j <= m; j++) {
+    W(T.cdxu)[j] = 1.0 / (2 * std::cos(yv[j]) * dx);  // unlin/vnlin costdxi (spf.F90:563,...), gradp cosdxi (:331)
+    W(T.cdyu)[j] = 1.0 / (2 * std::cos(yv[j]) * dy);
+    W(T.cyv)[j] = std::cos(yv[j]);
+    W(T.tanv)[j] = std::tan(yv[j]);
+  }
+  for (int j = 0; j <= m + 1; j++) {
+    W(T.cdxt)[j] = 1.0 / (4 * std::cos(y[j]) * dx);   // tnlin costdxi (spf.F90:403,415)
+    W(T.cdyt)[j] = 1.0 / (4 * std::cos(y[j]) * dy);
+  }
+  for (int j = 1; j <= m; j++) {
+    const bool in = j <= m - 1; // uderiv/vderiv/coriolis/gradp loop j=1..m-1
+    double c = 1.0 / (std::cos(yv[j]) * dx), cosdx2i = c * c;
+    double r = 1.0 / dy, rdy2i = r * r;
+    // uderiv (spf.F90:13-76)
+    double uxx2 = in ? amh(yv[j], ih) * cosdx2i : 0.0, uxx5 = in ? -(uxx2 + uxx2) : 0.0;
+    double uyy4 = in ? rdy2i * bmh(y[j], ih) * std::cos(y[j]) / std::cos(yv[j]) : 0.0;
+    double uyy6 = in ? rdy2i * bmh(y[j + 1], ih) * std::cos(y[j + 1]) / std::cos(yv[j]) : 0.0;
+    double uyy5 = in ? -(uyy4 + uyy6) : 0.0;
+    double tand2 = 1 - std::tan(yv[j]) * std::tan(yv[j]);
+    double ucsi5 = in ? bmh(yv[j], ih) * tand2 + std::tan(yv[j]) * bmhy(yv[j], ih) : 0.0;
+    double tanv = std::tan(yv[j]), cosv = std::cos(yv[j]);
+    double vxs2 = in ? (bmhy(yv[j], ih) - (amh(yv[j], ih) + bmh(yv[j], ih)) * tanv) / (dx * cosv) : 0.0;
+    double vxs8 = in ? -(bmhy(yv[j], ih) - (amh(yv[j], ih) + bmh(yv[j], ih)) * tanv) / (dx * cosv) : 0.0;
+    double corv = in ? std::sin(yv[j]) * cfg.coriolis_on : 0.0;
+    W(T.uu_we)[j] = -EH * (uxx2 + 0.0 + 0.0) - EV * 0.0;
+    W(T.uu_s)[j] = -EH * (0.0 + uyy4 + 0.0) - EV * 0.0;
+    W(T.uu_n)[j] = -EH * (0.0 + uyy6 + 0.0) - EV * 0.0;
+    W(T.uu_ch)[j] = -EH * (uxx5 + uyy5 + ucsi5);
+    W(T.uv_c)[j] = -corv - EH * 0.0;
+    W(T.uv_w)[j] = -0.0 - EH * vxs2;
+    W(T.uv_e)[j] = -0.0 - EH * vxs8;
+    // vderiv (spf.F90:78-141)
+    double vxx2 = in ? bmh(yv[j], ih) * cosdx2i : 0.0, vxx5 = in ? -2 * bmh(yv[j], ih) * cosdx2i : 0.0;
+    double vyy4 = in ? rdy2i * amh(y[j], ih) * std::cos(y[j]) / std::cos(yv[j]) : 0.0;
+    double vyy6 = in ? rdy2i * amh(y[j + 1], ih) * std::cos(y[j + 1]) / std::cos(yv[j]) : 0.0;
+    double vyy5 = in ? -(vyy4 + vyy6) : 0.0;
+    double vcsi5 = in ? bmh(yv[j], ih) - amh(yv[j], ih) * std::tan(yv[j]) * std::tan(yv[j]) + bmhy(yv[j], ih) * std::tan(yv[j]) : 0.0;
+    double uxs2 = in ? -((amh(yv[j], ih) + bmh(yv[j], ih)) * tanv - bmhy(yv[j], ih)) / (dx * cosv) : 0.0;
+    double uxs8 = in ? ((amh(yv[j], ih) + bmh(yv[j], ih)) * tanv - bmhy(yv[j], ih)) / (dx * cosv) : 0.0;
+    W(T.vv_we)[j] = -EH * (vxx2 + 0.0 + 0.0) - EV * 0.0;
+    W(T.vv_s)[j] = -EH * (0.0 + vyy4 + 0.0) - EV * 0.0;
+    W(T.vv_n)[j] = -EH * (0.0 + vyy6 + 0.0) - EV * 0.0;
+    W(T.vv_ch)[j] = -EH * (vxx5 + vyy5 + vcsi5);
+    W(T.vu_c)[j] = corv - EH * 0.0;
+    W(T.vu_w)[j] = 0.0 - EH * uxs2;
+    W(T.vu_e)[j] = 0.0 - EH * uxs8;
+    // pderiv (spf.F90:143-196)
+    W(T.pu)[j] = 1.0 / (2 * std::cos(y[j]) * dx);
+    double cos2i = 1. / (2 * std::cos(y[j]) * dy);
+    W(T.pv_s)[j] = -std::cos(yv[j - 1]) * cos2i;
+    W(T.pv_n)[j] = std::cos(yv[j]) * cos2i;
+    // tderiv 3,4 (spf.F90:216-236), surface-land factor (1-landm(i,j,l)) == 1 on every ocean row
+    double ct = 1.0 / (std::cos(y[j]) * dx), ctdx2i = ct * ct;
+    double txx2 = ctdx2i, txx5 = -2 * ctdx2i;
+    double tyy4 = (rdy2i * std::cos(yv[j - 1]) / std::cos(y[j])), tyy6 = (rdy2i * std::cos(yv[j]) / std::cos(y[j]));
+    double tyy5 = -(tyy4 + tyy6);
+    W(T.tt_we)[j] = -ph * (txx2 + 0.0) - pv * 0.0;
+    W(T.tt_s)[j] = -ph * (0.0 + tyy4) - pv * 0.0;
+    W(T.tt_n)[j] = -ph * (0.0 + tyy6) - pv * 0.0;
+    W(T.tt_ch)[j] = -ph * (txx5 + tyy5);
+  }
+  const double rz = 1.0 / dz, rdz2i = rz * rz, dzi = 1.0 / dz;
+  for (int k = 1; k <= l; k++) {
+    double h1 = 1. / (dfzT[k] * dfzW[k]), h2 = 1. / (dfzT[k] * dfzW[k - 1]);
+    double uzz14 = h2 * rdz2i, uzz23 = h1 * rdz2i, uzz5 = -(uzz14 + uzz23); // uderiv(4)
+    W(T.uu_b)[k] = -0.0 - EV * uzz14;
+    W(T.uu_t)[k] = -0.0 - EV * uzz23;
+    W(T.uu_cv)[k] = EV * uzz5;
+    double tzz14 = h2 * rdz2i, tzz23 = (k <= l - 1) ? h1 * rdz2i : 0.0, tzz5 = -(tzz14 + tzz23); // tderiv(5)
+    W(T.tt_b)[k] = -0.0 - pv * tzz14;
+    W(T.tt_t)[k] = -0.0 - pv * tzz23;
+    W(T.tt_cv)[k] = pv * tzz5;
+    W(T.wp)[k] = dzi / dfzW[k];   // gradp(3)
+    W(T.pw)[k] = dzi / dfzT[k];   // pderiv(3)
+    W(T.tdzi8)[k] = 1.0 / (8 * dfzT[k] * dz);
+    W(T.dfzT)[k] = dfzT[k];
+    W(T.dzdfzT)[k] = dz * dfzT[k];
+  }
+  for (int k = 0; k <= l; k++) W(T.dzdfzW)[k] = dz * dfzW[k];
+
+  std::memset(&S, 0, sizeof(S));
+  S.n = n; S.m = m; S.l = l; S.periodic = cfg.periodic != 0;
+  S.epsr = par[P_ROSB];
+  S.w_tt = -Ra * (1. + xes * alpt1) * 1.0 / 2.;   // Al(:,WW,TT) = -Ra*(1.+xes*alpt1)*tbc/2.
+  S.w_ss = lambda * Ra * 1.0 / 2.;                // Al(:,WW,SS) = lambda*Ra*tbc/2.
+  S.ra_a2 = Ra * xes * alpt2; S.ra_a3 = Ra * xes * alpt3;
+  S.tt_surf = cfg.tres * bi * 1.0; S.ss_surf = cfg.sres * bi * 1.0;
+  if (cfg.coupled_T == 1) { // Ooa*tc with msi=0, lvsc=0 (usrc.F90:711-722, atmos_coef :1175-1213)
+    const double rhoa = 1.25, ce = 1.3e-03, ch = 0.94 * ce, cpa = 1000., uw = 8.5;
+    double muoa = rhoa * ch * cpa * uw, dzne = dz * dfzT[l];
+    double QTnd = r0dim / (udim * cp0 * rhodim * cfg.hdim * dzne);
+    S.tt_surf = (muoa * QTnd) * 1.0;
+  }
+  S.dyi = 1. / (2 * dy); S.dzi = dzi; S.tdzi2 = 1.0 / (2 * dz);
+  S.kvc = par[P_P_VC]; S.lambda = lambda; S.xes = xes;
+  S.fac = cfg.alphaT * par[P_SPL1];
+  S.vmix_on = cfg.vmix >= 1;
+  S.rho_mixing = (cfg.rho_mixing != 0) && (xes == 0.0);
+  S.dz = dz;
+}
+
+namespace {
+// forcing.F90:489-534
+double wfun(double yy, int v1) {
+  if (v1 == 1) return 0.2 - 0.8 * std::sin(6 * std::fabs(yy)) - 0.5 * (1 - std::tanh(10 * std::fabs(yy))) - 0.5 * (1 - std::tanh(10 * (pi / 2 - std::fabs(yy))));
+  return 0.0;
+}
+} // namespace
+
+// forcing.F90:4-218 (idealized, uncoupled salinity) followed by the Frc zeroing of boundary.F90
+void Host::build_forcing() {
+  frc.assign(ndim, 0.0);
+  const int TRES = cfg.tres, SRES = cfg.sres;
+  const double gymin = cfg.ymin, gymax = cfg.ymax;
+  auto row = [&](int i, int j, int k, int X) { return 6 * ((((size_t)k - 1) * m + (j - 1)) * n + (i - 1)) + X - 1; };
+  auto temfun = [&](double yy) {
+    if (cfg.forcing_type == 2) return std::cos(pi * (yy - gymin) / (gymax - gymin));
+    return std::cos(pi * yy / gymax) + par[P_CMPR] * std::sin(pi * yy / gymax);
+  };
+  auto salfun = [&](double yy) {
+    if (cfg.forcing_type == 2) return std::cos(pi * (yy - gymin) / (gymax - gymin));
+    if (cfg.forcing_type == 1) return (std::cos(pi * yy / gymax) + par[P_FPER] * yy / gymax) / std::cos(yy);
+    return std::cos(pi * yy / gymax) + par[P_FPER] * yy / gymax;
+  };
+  auto qint = [&](const std::vector<double>& field) { // thcm_forcing_integral_, THCM.C:2704-2740
+    double lf = 0.0, ls = 0.0;
+    for (int j = 1; j <= m; j++) for (int i = 1; i <= n; i++) {
+      lf = field[(size_t)(i - 1) + (size_t)n * (j - 1)] * std::cos(y[j]) * (1 - lm(i, j, l)) + lf;
+      ls = std::cos(y[j]) * (1 - lm(i, j, l)) + ls;
+    }
+    return lf / ls;
+  };
+  const double sigma = par[P_COMB] * par[P_WIND] * par[P_AL_T];
+  for (int j = 1; j <= m - 1; j++) for (int i = 1; i <= n; i++) {
+    frc[row(i, j, l, UU)] = sigma * wfun(yv[j], 1);
+    frc[row(i, j, l, VV)] = sigma * wfun(yv[j], 2);
+  }
+  std::vector<double> tatm((size_t)n * m, 0.0), emip((size_t)n * m, 0.0), zero2((size_t)n * m, 0.0);
+  const double etabi = par[P_COMB] * par[P_TEMP] * (1 - TRES + TRES * par[P_BIOT]);
+  double temcor = 0.0;
+  if (cfg.coupled_T == 0) {
+    for (int j = 1; j <= m; j++) for (int i = 1; i <= n; i++) tatm[(size_t)(i - 1) + (size_t)n * (j - 1)] = temfun(y[j]);
+    if (TRES == 0) temcor = qint(tatm);
+    for (int j = 1; j <= m; j++) for (int i = 1; i <= n; i++) frc[row(i, j, l, TT)] = etabi * (tatm[(size_t)(i - 1) + (size_t)n * (j - 1)] - temcor);
+  }
+  // coupled_T == 1 with no atmosphere attached: tatm = qatm = albe = msi = 0, lvsc = 0 => Frc(TT) = par(COMB)*par(SUNP)*suno(j)*(1-albe0)
+  // with the unset albe0 = 0; only meaningful once set_atmos_parameters exists, kept at 0 here.
+  const double gamma = par[P_COMB] * par[P_SALT] * (1 - SRES + SRES * par[P_BIOT]);
+  double salcor = 0.0, adapted_salcor = 0.0, spertcor = 0.0;
+  for (int j = 1; j <= m; j++) for (int i = 1; i <= n; i++) emip[(size_t)(i - 1) + (size_t)n * (j - 1)] = salfun(y[j]) * (1 - lm(i, j, l));
+  if (SRES == 0) { salcor = qint(emip); adapted_salcor = qint(zero2); spertcor = qint(zero2); }
+  for (int j = 1; j <= m; j++) for (int i = 1; i <= n; i++)
+    frc[row(i, j, l, SS)] = gamma * (1 - par[P_HMTP]) * (emip[(size_t)(i - 1) + (size_t)n * (j - 1)] - salcor) +
+                            gamma * par[P_HMTP] * (0.0 - adapted_salcor) + par[P_SPER] * (1 - SRES + SRES * par[P_BIOT]) * (0.0 - spertcor);
+  for (int k = 1; k <= l - 1; k++) for (int j = 1; j <= m; j++) for (int i = 1; i <= n; i++) // internal T/S forcing is zero (THCM.C:540-544)
+    frc[row(i, j, k, WW)] = -par[P_COMB] * (1 - lm(i, j, k)) * par[P_RAYL] * (par[P_LAMB] * (0.0 + 0.0) / 2. - (0.0 + 0.0) / 2.);
+  // rows whose forcing `boundaries` resets to zero on every call
+  for (size_t c = 0; c < ncell; c++) {
+    uint64_t g = sig[c];
+    if (frc_masked<UU>(g)) frc[6 * c + 0] = 0.0;
+    if (frc_masked<VV>(g)) frc[6 * c + 1] = 0.0;
+    if (frc_masked<WW>(g)) frc[6 * c + 2] = 0.0;
+    if (frc_masked<PP>(g)) frc[6 * c + 3] = 0.0;
+    if (frc_masked<TT>(g)) frc[6 * c + 4] = 0.0;
+    if (frc_masked<SS>(g)) frc[6 * c + 5] = 0.0;
+  }
+}
+
+// Static pattern of THCM::CreateMaximalGraph (THCM.C:2241-2539): generated from the same RowDef tables the
+// kernels use, so the kernels' emit order and the graph cannot disagree.
+template <int A> static void graph_row(const Scalars& S, const Cell& c, std::vector<int>& col) {
+  int cols[Row<A>::NE], cnt = 0;
+  for (int q = 0; q < Row<A>::NE; q++) {
+    int slot = RowDef<A>::e[q].slot;
+    if (slot_present(slot, S, c)) cols[cnt++] = slot_col(slot, RowDef<A>::e[q].var, S, c);
+  }
+  if (S.periodic && (c.i == 1 || c.i == S.n)) std::sort(cols, cols + cnt);
+  col.insert(col.end(), cols, cols + cnt);
+}
+void Host::build_graph() {
+  Scalars G; std::memset(&G, 0, sizeof(G));
+  G.n = n; G.m = m; G.l = l; G.periodic = cfg.periodic != 0;
+  rowptr.assign(ndim + 1, 0);
+  col.clear();
+  col.reserve(104 * ncell + (rowintcon >= 0 ? ncell : 0));
+  size_t r = 0;
+  for (int k = 1; k <= l; k++) for (int j = 1; j <= m; j++) for (int i = 1; i <= n; i++) {
+    Cell c{i, j, k, 0};
+    rowptr[r++] = (int)col.size(); graph_row<UU>(G, c, col);
+    rowptr[r++] = (int)col.size(); graph_row<VV>(G, c, col);
+    rowptr[r++] = (int)col.size(); graph_row<WW>(G, c, col);
+    rowptr[r++] = (int)col.size(); graph_row<PP>(G, c, col);
+    rowptr[r++] = (int)col.size(); graph_row<TT>(G, c, col);
+    rowptr[r++] = (int)col.size();
+    if ((int)(r - 1) == rowintcon) { // dense integral-condition row (THCM.C:2494-2513), sorted: all S dofs
+      for (size_t cc = 0; cc < ncell; cc++) col.push_back((int)(6 * cc + SS - 1));
+    } else graph_row<SS>(G, c, col);
+  }
+  rowptr[ndim] = (int)col.size();
+}
+
+} // namespace thcm

@@ -1,0 +1,73 @@
+// thcm_host.h -- host-side setup of the B200 THCM path: grid, parameters, coefficient tables, per-cell
+// land signatures, forcing vector and the static CSR graph.  Everything here runs once per model /
+// per parameter change; the per-evaluation arithmetic lives in the CUDA kernels (thcm_kernels.cu).
+//
+// Mirrors, for the hot path only, what the reference does in
+//   src/ocean/THCM.C:176-800 (constructor), src/ocean/usrc.F90:6-139 (init), src/ocean/grid.F90,
+//   src/ocean/usrc.F90:1136-1172 (stpnt), src/ocean/forcing.F90:4-218, src/ocean/THCM.C:2241-2539 (graph).
+#pragma once
+#include <stdint.h>
+#include <string>
+#include <vector>
+#include "thcm_rows.cuh"
+
+namespace thcm {
+
+// Same fields as thcm_b200_config in include/iemic_b200.h (kept layout-compatible).
+struct Config {
+  int n, m, l;
+  double xmin, xmax, ymin, ymax; // radians
+  int periodic;
+  double hdim, qz;
+  double alphaT, alphaS;
+  int ih, vmix, tap, rho_mixing, coriolis_on, forcing_type;
+  int tres, sres, iza, ite, its;
+  int coupled_T, coupled_S;
+  int int_sign;
+  int intcond_i, intcond_j;
+  int fix_pressure_points;
+};
+
+enum { P_AL_T = 1, P_RAYL, P_EK_V, P_EK_H, P_ROSB, P_MIXP, P_RESC, P_SPL1, P_HMTP, P_SUNP, P_PE_H, P_PE_V, P_P_VC, P_LAMB,
+       P_SALT, P_WIND, P_TEMP, P_BIOT, P_COMB, P_ARCL, P_NLES, P_IFRICB, P_CONT, P_ENER, P_ALPC, P_CMPR, P_FPER, P_SPER,
+       P_MKAP, P_SPL2, NPAR = 30 };
+
+class Host {
+ public:
+  Host(const Config& cfg, const int* landm_in); // throws std::runtime_error on unsupported configurations
+  void set_par(int idx1, double value);          // setparcs (usrc.F90:163-181): recomputes forcing + tables
+  double get_par(int idx1) const { return (idx1 >= 1 && idx1 <= NPAR) ? par[idx1] : 0.0; }
+  void set_landmask(const int* landm_in);        // set_landmask (usrc.F90:336-395)
+
+  Config cfg;
+  int n, m, l;
+  size_t ncell, ndim;
+  double par[NPAR + 1];
+  double dx, dy, dz;
+  std::vector<double> x, y, z, xu, yv, zw, dfzT, dfzW; // Fortran index ranges
+  std::vector<int> landm;       // (0:n+1,0:m+1,0:l+1), after the init() border treatment
+  std::vector<uint64_t> sig;    // per cell
+  Scalars S;
+  std::vector<double> tab;      // NJTAB*(m+2) + NKTAB*(l+1) doubles, order of thcm::Tables
+  std::vector<double> frc;      // forcing vector with the rows `boundaries` zeroes already masked
+  std::vector<int> rowptr, col; // static graph, 0-based, sorted columns
+  int rowintcon, rowPfix1, rowPfix2;
+  std::vector<double> intcond;  // integral condition coefficients (ndim, zero except ocean S dofs)
+  double intCorrection;
+  uint64_t version;             // bumped whenever tables/forcing change (device copies refresh lazily)
+  uint64_t mask_version;
+
+  Tables tables(const double* base) const; // pointers into a (host or device) copy of `tab`
+  inline int lm(int i, int j, int k) const { return landm[(size_t)i + (size_t)(n + 2) * (j + (size_t)(m + 2) * k)]; }
+
+ private:
+  void make_grid();
+  void stpnt();
+  void build_signatures();
+  void build_tables();
+  void build_forcing();
+  void build_graph();
+  void check_supported() const;
+};
+
+} // namespace thcm

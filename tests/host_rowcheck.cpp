@@ -1,0 +1,106 @@
+// host_rowcheck.cpp -- TEST HARNESS ONLY.  Compiles the __host__ __device__ row code of the product
+// (iemic_b200/csrc/thcm_rows.cuh, thcm_stage.cuh, thcm_cell.cuh) with the host compiler and evaluates it
+// cell by cell, so that the arithmetic the CUDA kernels execute can be compared against the oracle on a
+// machine without a GPU.  Nothing in the product links this file; the product path is CUDA only.
+#include <cstring>
+#include <stdexcept>
+#include <cstdio>
+#include "../iemic_b200/csrc/thcm_host.h"
+#include "../iemic_b200/csrc/thcm_stage.cuh"
+#include "../iemic_b200/csrc/thcm_cell.cuh"
+
+using namespace thcm;
+
+namespace {
+struct HostFields { // accessor F: direct evaluation of the staging rule
+  const double* x; const uint64_t* sig; const Scalars* S; int i, j, k;
+  double u(int di, int dj, int dk) const { return stage_cell(x, sig, *S, i + di, j + dj, k + dk).u; }
+  double v(int di, int dj, int dk) const { return stage_cell(x, sig, *S, i + di, j + dj, k + dk).v; }
+  double w(int di, int dj, int dk) const { return stage_cell(x, sig, *S, i + di, j + dj, k + dk).w; }
+  double t(int di, int dj, int dk) const { return stage_cell(x, sig, *S, i + di, j + dj, k + dk).t; }
+  double s(int di, int dj, int dk) const { return stage_cell(x, sig, *S, i + di, j + dj, k + dk).s; }
+};
+struct HostRaw { // accessor X: raw neighbour state through shift() (assemble.F90:142-179)
+  const double* x; const Scalars* S; int i, j, k;
+  double raw(int di, int dj, int dk, int var) const {
+    int i2 = i + di, j2 = j + dj, k2 = k + dk;
+    if (S->periodic) { if (i2 == 0) i2 = S->n; else if (i2 == S->n + 1) i2 = 1; }
+    return x[6 * cell_index(*S, i2, j2, k2) + var - 1];
+  }
+};
+} // namespace
+
+extern "C" {
+void* hostcheck_create(const Config* cfg, const int* landm, char* err, int errlen) {
+  try { return new Host(*cfg, landm); }
+  catch (const std::exception& e) { if (err) { strncpy(err, e.what(), errlen - 1); err[errlen - 1] = 0; } return nullptr; }
+}
+void hostcheck_destroy(void* h) { delete (Host*)h; }
+int hostcheck_set_par(void* h, int idx, double v, char* err, int errlen) {
+  try { ((Host*)h)->set_par(idx, v); return 0; }
+  catch (const std::exception& e) { if (err) { strncpy(err, e.what(), errlen - 1); err[errlen - 1] = 0; } return -1; }
+}
+double hostcheck_get_par(void* h, int idx) { return ((Host*)h)->get_par(idx); }
+long long hostcheck_nnz(void* h) { return (long long)((Host*)h)->col.size(); }
+int hostcheck_rowintcon(void* h) { return ((Host*)h)->rowintcon; }
+void hostcheck_graph(void* h, int* rowptr, int* col) {
+  Host* H = (Host*)h;
+  memcpy(rowptr, H->rowptr.data(), sizeof(int) * H->rowptr.size());
+  memcpy(col, H->col.data(), sizeof(int) * H->col.size());
+}
+void hostcheck_frc(void* h, double* frc) { Host* H = (Host*)h; memcpy(frc, H->frc.data(), sizeof(double) * H->ndim); }
+void hostcheck_sig(void* h, unsigned long long* sig) { Host* H = (Host*)h; memcpy(sig, H->sig.data(), 8 * H->ncell); }
+void hostcheck_intcond(void* h, double* c) { Host* H = (Host*)h; memcpy(c, H->intcond.data(), sizeof(double) * H->ndim); }
+
+void hostcheck_jac(void* h, const double* x, double* val, double* diagB) {
+  Host* H = (Host*)h;
+  const Scalars& S = H->S;
+  Tables T = H->tables(H->tab.data());
+  SpecialRows sp{H->rowintcon, H->rowPfix1, H->rowPfix2};
+  for (size_t q = 0; q < H->col.size(); q++) val[q] = 0.0;
+  for (int k = 1; k <= S.l; k++) for (int j = 1; j <= S.m; j++) for (int i = 1; i <= S.n; i++) {
+    size_t ci = cell_index(S, i, j, k);
+    Cell c{i, j, k, H->sig[ci]};
+    HostFields f{x, H->sig.data(), &S, i, j, k};
+    int row = (int)(6 * ci);
+    diagB[row + 0] = jac_row<UU>(S, T, c, f, sp, row + 0, val + H->rowptr[row + 0]);
+    diagB[row + 1] = jac_row<VV>(S, T, c, f, sp, row + 1, val + H->rowptr[row + 1]);
+    diagB[row + 2] = jac_row<WW>(S, T, c, f, sp, row + 2, val + H->rowptr[row + 2]);
+    diagB[row + 3] = jac_row<PP>(S, T, c, f, sp, row + 3, val + H->rowptr[row + 3]);
+    diagB[row + 4] = jac_row<TT>(S, T, c, f, sp, row + 4, val + H->rowptr[row + 4]);
+    diagB[row + 5] = jac_row<SS>(S, T, c, f, sp, row + 5, val + H->rowptr[row + 5]);
+  }
+  if (H->rowintcon >= 0) { // intcond_S (THCM.C:2121-2198)
+    int r = H->rowintcon;
+    for (int p = H->rowptr[r]; p < H->rowptr[r + 1]; p++) val[p] = H->cfg.int_sign * H->intcond[H->col[p]];
+  }
+}
+
+void hostcheck_rhs(void* h, const double* x, double* Fo) {
+  Host* H = (Host*)h;
+  const Scalars& S = H->S;
+  Tables T = H->tables(H->tab.data());
+  for (int k = 1; k <= S.l; k++) for (int j = 1; j <= S.m; j++) for (int i = 1; i <= S.n; i++) {
+    size_t ci = cell_index(S, i, j, k);
+    Cell c{i, j, k, H->sig[ci]};
+    HostFields f{x, H->sig.data(), &S, i, j, k};
+    HostRaw xr{x, &S, i, j, k};
+    size_t row = 6 * ci;
+    double mt = 0.0, ms = 0.0;
+    if (S.vmix_on) thcm_mix(S, T, c, f.t(0, 0, -1), f.s(0, 0, -1), f.t(0, 0, 0), f.s(0, 0, 0), f.t(0, 0, 1), f.s(0, 0, 1), mt, ms);
+    Fo[row + 0] = rhs_row<UU>(S, T, c, f, xr, H->frc[row + 0], 0.0);
+    Fo[row + 1] = rhs_row<VV>(S, T, c, f, xr, H->frc[row + 1], 0.0);
+    Fo[row + 2] = rhs_row<WW>(S, T, c, f, xr, H->frc[row + 2], 0.0);
+    Fo[row + 3] = rhs_row<PP>(S, T, c, f, xr, H->frc[row + 3], 0.0);
+    Fo[row + 4] = rhs_row<TT>(S, T, c, f, xr, H->frc[row + 4], mt);
+    Fo[row + 5] = rhs_row<SS>(S, T, c, f, xr, H->frc[row + 5], ms);
+  }
+  if (H->cfg.sres == 0 && H->rowintcon >= 0) { // THCM.C:1006-1018
+    double d = 0.0;
+    for (size_t q = 0; q < H->ndim; q++) d += H->intcond[q] * x[q];
+    Fo[H->rowintcon] = H->cfg.int_sign * (d - H->intCorrection);
+  }
+  if (H->rowPfix1 >= 0) Fo[H->rowPfix1] = 0.0;
+  if (H->rowPfix2 >= 0) Fo[H->rowPfix2] = 0.0;
+}
+}

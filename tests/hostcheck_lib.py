@@ -1,0 +1,109 @@
+"""ctypes binding of tests/host_rowcheck.cpp: the product's __host__ __device__ row code compiled for the CPU.
+
+Test harness only -- lets the CPU test-suite check the arithmetic the CUDA kernels run against the oracle.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from oracle_lib import Config, PAR, ROOT
+
+_LIB = None
+_SO = os.path.join(ROOT, "tests", "_build", "libhostcheck.so")
+_SRCS = [os.path.join(ROOT, "tests", "host_rowcheck.cpp"), os.path.join(ROOT, "iemic_b200", "csrc", "thcm_host.cpp")]
+_DEPS = _SRCS + [os.path.join(ROOT, "iemic_b200", "csrc", f) for f in
+                 ("thcm_rows.cuh", "thcm_stage.cuh", "thcm_cell.cuh", "thcm_host.h")]
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        os.makedirs(os.path.dirname(_SO), exist_ok=True)
+        if (not os.path.exists(_SO)) or any(os.path.getmtime(d) > os.path.getmtime(_SO) for d in _DEPS):
+            subprocess.run(["g++", "-std=c++17", "-O1", "-ffp-contract=off", "-fPIC", "-shared", "-o", _SO] + _SRCS,
+                           check=True)
+        L = C.CDLL(_SO)
+        dp, ip = C.POINTER(C.c_double), C.POINTER(C.c_int)
+        L.hostcheck_create.restype = C.c_void_p
+        L.hostcheck_create.argtypes = [C.POINTER(Config), ip, C.c_char_p, C.c_int]
+        L.hostcheck_destroy.argtypes = [C.c_void_p]
+        L.hostcheck_set_par.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_char_p, C.c_int]
+        L.hostcheck_get_par.argtypes = [C.c_void_p, C.c_int]
+        L.hostcheck_get_par.restype = C.c_double
+        L.hostcheck_nnz.argtypes = [C.c_void_p]
+        L.hostcheck_nnz.restype = C.c_longlong
+        L.hostcheck_rowintcon.argtypes = [C.c_void_p]
+        L.hostcheck_graph.argtypes = [C.c_void_p, ip, ip]
+        L.hostcheck_frc.argtypes = [C.c_void_p, dp]
+        L.hostcheck_sig.argtypes = [C.c_void_p, C.POINTER(C.c_ulonglong)]
+        L.hostcheck_intcond.argtypes = [C.c_void_p, dp]
+        L.hostcheck_jac.argtypes = [C.c_void_p, dp, dp, dp]
+        L.hostcheck_rhs.argtypes = [C.c_void_p, dp, dp]
+        _LIB = L
+    return _LIB
+
+
+def _dp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_double))
+
+
+def _ip(a):
+    return a.ctypes.data_as(C.POINTER(C.c_int))
+
+
+class HostCheck:
+    def __init__(self, cfg, landm):
+        self.c = Config(**cfg)
+        self.landm = np.ascontiguousarray(landm, dtype=np.int32).ravel()
+        err = C.create_string_buffer(512)
+        self.h = lib().hostcheck_create(C.byref(self.c), _ip(self.landm), err, 512)
+        if not self.h:
+            raise RuntimeError(err.value.decode())
+        self.ndim = 6 * cfg["n"] * cfg["m"] * cfg["l"]
+        self._graph = None
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().hostcheck_destroy(self.h)
+            self.h = None
+
+    def set_par(self, name, value):
+        err = C.create_string_buffer(512)
+        if lib().hostcheck_set_par(self.h, PAR[name] if isinstance(name, str) else name, float(value), err, 512) != 0:
+            raise RuntimeError(err.value.decode())
+
+    def get_par(self, name):
+        return lib().hostcheck_get_par(self.h, PAR[name] if isinstance(name, str) else name)
+
+    def graph(self):
+        if self._graph is None:
+            nnz = lib().hostcheck_nnz(self.h)
+            rp = np.zeros(self.ndim + 1, np.int32)
+            col = np.zeros(nnz, np.int32)
+            lib().hostcheck_graph(self.h, _ip(rp), _ip(col))
+            self._graph = (rp, col)
+        return self._graph
+
+    def jac(self, x):
+        x = np.ascontiguousarray(x, np.float64)
+        rp, col = self.graph()
+        val = np.zeros(col.size)
+        diagB = np.zeros(self.ndim)
+        lib().hostcheck_jac(self.h, _dp(x), _dp(val), _dp(diagB))
+        return val, diagB
+
+    def rhs(self, x):
+        x = np.ascontiguousarray(x, np.float64)
+        F = np.zeros(self.ndim)
+        lib().hostcheck_rhs(self.h, _dp(x), _dp(F))
+        return F
+
+    def frc(self):
+        f = np.zeros(self.ndim)
+        lib().hostcheck_frc(self.h, _dp(f))
+        return f
+
+    def rowintcon(self):
+        return lib().hostcheck_rowintcon(self.h)
