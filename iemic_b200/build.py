@@ -1,0 +1,84 @@
+"""Builds libiemic_b200.so (the C-ABI shared library of include/iemic_b200.h) in-tree with nvcc for sm_100a.
+
+No torch involvement: plain `nvcc -shared`.  The library lands in iemic_b200/lib/ so that it travels to the GPU box
+with the repository snapshot.
+"""
+import hashlib
+import os
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, "csrc")
+LIBDIR = os.path.join(HERE, "lib")
+LIB = os.path.join(LIBDIR, "libiemic_b200.so")
+
+ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
+COMMON = ["-O3", "-std=c++17", "-lineinfo", "--expt-relaxed-constexpr", "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden"]
+# (source, extra flags).  thcm_kernels.cu: no FMA contraction -> bit parity with the FMA-free reference arithmetic.
+UNITS = [
+    ("thcm_kernels.cu", ["-fmad=false"]),
+    ("spmv.cu", []),
+    ("gmres.cu", []),
+    ("dist.cu", []),
+    ("capi.cu", ["-Xcompiler", "-fvisibility=default"]),
+    # host-side table construction: host compiler must not contract a*b+c either
+    ("thcm_host.cpp", ["-Xcompiler", "-ffp-contract=off"]),
+]
+HEADERS = ["thcm_rows.cuh", "thcm_stage.cuh", "thcm_cell.cuh", "thcm_host.h", "kernels.h", "dist.h",
+           os.path.join("..", "..", "include", "iemic_b200.h")]
+
+
+def _nvcc():
+    for c in (os.environ.get("NVCC"), "/usr/local/cuda/bin/nvcc", "nvcc"):
+        if c and (os.path.isabs(c) and os.path.exists(c) or not os.path.isabs(c)):
+            return c
+    return "nvcc"
+
+
+def _digest(paths, flags):
+    h = hashlib.sha256()
+    for p in paths:
+        with open(p, "rb") as f:
+            h.update(f.read())
+    h.update(" ".join(flags).encode())
+    return h.hexdigest()
+
+
+def build(force=False, verbose=False):
+    os.makedirs(LIBDIR, exist_ok=True)
+    objdir = os.path.join(HERE, "build")
+    os.makedirs(objdir, exist_ok=True)
+    hdrs = [os.path.join(CSRC, h) for h in HEADERS]
+    objs = []
+    rebuilt = False
+    procs = []
+    for src, extra in UNITS:
+        sp = os.path.join(CSRC, src)
+        obj = os.path.join(objdir, src + ".o")
+        stamp = obj + ".sha"
+        flags = ARCH + COMMON + extra
+        dig = _digest([sp] + hdrs, flags)
+        objs.append(obj)
+        if not force and os.path.exists(obj) and os.path.exists(stamp) and open(stamp).read() == dig:
+            continue
+        cmd = [_nvcc()] + flags + (["-Xptxas", "-v"] if verbose else []) + ["-x", "cu", "-c", sp, "-o", obj]
+        procs.append((subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True), stamp, dig, src))
+        rebuilt = True
+    for p, stamp, dig, src in procs:
+        out, _ = p.communicate()
+        if p.returncode != 0:
+            sys.stderr.write(out)
+            raise RuntimeError("nvcc failed on " + src)
+        if verbose:
+            sys.stderr.write(out)
+        with open(stamp, "w") as f:
+            f.write(dig)
+    if rebuilt or not os.path.exists(LIB):
+        cmd = [_nvcc()] + ARCH + ["-shared", "-o", LIB] + objs + ["-cudart", "static", "-ldl"]
+        subprocess.run(cmd, check=True)
+    return LIB
+
+
+if __name__ == "__main__":
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

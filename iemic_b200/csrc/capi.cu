@@ -1,0 +1,629 @@
+// capi.cu -- the C ABI of include/iemic_b200.h: handle management, device residency of the static data,
+// kernel sequencing for assembly / SpMV / GMRES.  No arithmetic happens on the host in here except the
+// per-parameter-change setup delegated to thcm::Host (thcm_host.cpp).
+#include <cuda_runtime.h>
+#include <cstdio>
+#include <cstring>
+#include <cmath>
+#include <string>
+#include <vector>
+#include <stdexcept>
+#include "../../include/iemic_b200.h"
+#include "thcm_host.h"
+#include "kernels.h"
+#include "dist.h"
+
+using namespace thcm;
+
+namespace {
+thread_local std::string g_err;
+int fail(int code, const std::string& msg) { g_err = msg; return code; }
+#define CU(call)                                                                                   \
+  do {                                                                                             \
+    cudaError_t e_ = (call);                                                                       \
+    if (e_ != cudaSuccess) return fail(IEMIC_B200_ECUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); \
+  } while (0)
+#define CHECK_H(h) if (!(h)) return fail(IEMIC_B200_EINVAL, "null handle")
+
+template <class T> int dev_upload(T** d, const std::vector<T>& v, size_t pad = 0) {
+  if (*d) { cudaFree(*d); *d = nullptr; }
+  size_t bytes = (v.size() + pad) * sizeof(T);
+  if (bytes == 0) bytes = sizeof(T);
+  CU(cudaMalloc((void**)d, bytes));
+  CU(cudaMemset(*d, 0, bytes));
+  if (!v.empty()) CU(cudaMemcpy(*d, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+  return 0;
+}
+} // namespace
+
+struct GmresWs {
+  int m = 0; long long n = 0, ld = 0; bool haveZ = false;
+  double *V = nullptr, *Z = nullptr, *w = nullptr, *r = nullptr, *tmp = nullptr;
+  double *H = nullptr, *cs = nullptr, *sn = nullptr, *s = nullptr, *y = nullptr, *hist = nullptr;
+};
+
+struct TimedEv { int which; cudaEvent_t a, b; };
+
+struct thcm_b200 {
+  Host* host = nullptr;
+  Dist* dist = nullptr;          // null on a single GPU
+  cudaStream_t stream = 0;
+  // static / per-parameter device data
+  double* d_tab = nullptr; uint64_t* d_sig = nullptr; int* d_rowptr = nullptr; int* d_col = nullptr;
+  double* d_val = nullptr; double* d_diagB = nullptr; double* d_frc = nullptr; double* d_coefS = nullptr;
+  int* d_blkrow = nullptr; int nblk = 0;
+  uint64_t dev_version = 0, dev_mask_version = 0;
+  // scratch vectors for the host-buffer entry points
+  double *d_xs = nullptr, *d_ys = nullptr;
+  // reductions and small device scalars
+  RedBuf rb{nullptr, nullptr, 0};
+  double* d_small = nullptr; // [0,512) h1, [512,1024) h2, 1024 nrm2, 1025 hnext, 1026 bnorm, 1027 beta, 1028 dot, 1029 intcond
+  GmresWs g;
+  long long launches = 0;
+  bool timing = false;
+  std::vector<TimedEv> evs;
+  double t_total[4] = {0, 0, 0, 0}; long long t_count[4] = {0, 0, 0, 0};
+  long long nrows() const { return (long long)host->nrows_local(); }
+  long long nvec() const { return (long long)host->nvec_local(); }
+};
+
+namespace {
+struct Timed { // RAII bracket: records a pair of events around a kernel group when timing is on
+  thcm_b200* h; int which; TimedEv ev{}; bool on;
+  Timed(thcm_b200* h_, int w) : h(h_), which(w), on(h_->timing) {
+    if (on) { ev.which = w; cudaEventCreate(&ev.a); cudaEventCreate(&ev.b); cudaEventRecord(ev.a, h->stream); }
+  }
+  ~Timed() { if (on) { cudaEventRecord(ev.b, h->stream); h->evs.push_back(ev); } }
+};
+int flush_timing(thcm_b200* h) {
+  if (h->evs.empty()) return 0;
+  CU(cudaStreamSynchronize(h->stream));
+  for (auto& e : h->evs) {
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e.a, e.b);
+    h->t_total[e.which] += ms; h->t_count[e.which]++;
+    cudaEventDestroy(e.a); cudaEventDestroy(e.b);
+  }
+  h->evs.clear();
+  return 0;
+}
+
+// Build the row-run plan of the SpMV kernel (spmv.cu): runs of <= rows_cap rows and <= nnz_cap non-zeros.
+std::vector<int> spmv_plan(const std::vector<int>& rowptr) {
+  std::vector<int> blk;
+  const int nrows = (int)rowptr.size() - 1, ncap = spmv_nnz_cap(), rcap = spmv_rows_cap();
+  int r = 0;
+  blk.push_back(0);
+  while (r < nrows) {
+    int r1 = r + 1; // always take one row (a long row becomes a block of its own)
+    if (rowptr[r1] - rowptr[r] <= ncap)
+      while (r1 < nrows && r1 - r < rcap && rowptr[r1 + 1] - rowptr[r] <= ncap) r1++;
+    blk.push_back(r1);
+    r = r1;
+  }
+  return blk;
+}
+
+int refresh_device(thcm_b200* h) {
+  Host* H = h->host;
+  if (h->dev_mask_version != H->mask_version) {
+    if (int rc = dev_upload(&h->d_sig, H->sig)) return rc;
+    if (int rc = dev_upload(&h->d_rowptr, H->rowptr)) return rc;
+    if (int rc = dev_upload(&h->d_col, H->col, 8)) return rc;
+    std::vector<double> zeros;
+    if (h->d_val) { cudaFree(h->d_val); h->d_val = nullptr; }
+    CU(cudaMalloc((void**)&h->d_val, (H->col.size() + 8) * sizeof(double)));
+    CU(cudaMemset(h->d_val, 0, (H->col.size() + 8) * sizeof(double)));
+    if (h->d_diagB) { cudaFree(h->d_diagB); h->d_diagB = nullptr; }
+    CU(cudaMalloc((void**)&h->d_diagB, (size_t)h->nrows() * sizeof(double)));
+    CU(cudaMemset(h->d_diagB, 0, (size_t)h->nrows() * sizeof(double)));
+    std::vector<int> blk = spmv_plan(H->rowptr);
+    h->nblk = (int)blk.size() - 1;
+    if (int rc = dev_upload(&h->d_blkrow, blk)) return rc;
+    // integral condition: compact per-cell coefficients, and the static dense Jacobian row (THCM.C:2121-2198)
+    std::vector<double> coefS((size_t)h->nrows() / 6);
+    for (size_t c = 0; c < coefS.size(); c++) coefS[c] = H->intcond[6 * c + 5];
+    if (int rc = dev_upload(&h->d_coefS, coefS)) return rc;
+    if (H->rowintcon >= 0 && H->owns_rowintcon) {
+      const int r = H->rowintcon_local;
+      std::vector<double> rowv((size_t)(H->rowptr[r + 1] - H->rowptr[r]));
+      for (size_t q = 0; q < rowv.size(); q++) rowv[q] = H->cfg.int_sign * H->intcond_col(H->col[H->rowptr[r] + q]);
+      CU(cudaMemcpy(h->d_val + H->rowptr[r], rowv.data(), rowv.size() * sizeof(double), cudaMemcpyHostToDevice));
+    }
+    if (!h->d_xs) {
+      CU(cudaMalloc((void**)&h->d_xs, (size_t)h->nvec() * sizeof(double)));
+      CU(cudaMemset(h->d_xs, 0, (size_t)h->nvec() * sizeof(double)));
+      CU(cudaMalloc((void**)&h->d_ys, (size_t)h->nvec() * sizeof(double)));
+      CU(cudaMemset(h->d_ys, 0, (size_t)h->nvec() * sizeof(double)));
+    }
+    h->dev_mask_version = H->mask_version;
+    h->dev_version = 0;
+  }
+  if (h->dev_version != H->version) {
+    if (int rc = dev_upload(&h->d_tab, H->tab)) return rc;
+    if (int rc = dev_upload(&h->d_frc, H->frc)) return rc;
+    h->dev_version = H->version;
+  }
+  return 0;
+}
+
+AsmArgs asm_args(thcm_b200* h, const double* d_x) {
+  AsmArgs a;
+  std::memset(&a, 0, sizeof(a));
+  Host* H = h->host;
+  a.S = H->S;
+  a.T = H->tables(h->d_tab);
+  a.x = d_x; a.sig = h->d_sig; a.rowptr = h->d_rowptr; a.frc = h->d_frc; a.val = h->d_val; a.diagB = h->d_diagB;
+  a.sp.rowintcon = H->owns_rowintcon ? H->rowintcon_local : -1;
+  a.sp.rowPfix1 = H->rowPfix1_local; a.sp.rowPfix2 = H->rowPfix2_local;
+  return a;
+}
+int check_launch(thcm_b200* h, const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail(IEMIC_B200_ECUDA, std::string(what) + ": " + cudaGetErrorString(e));
+  (void)h;
+  return 0;
+}
+int gmres_alloc(thcm_b200* h, int m, bool needZ) {
+  GmresWs& g = h->g;
+  const long long n = h->nrows();
+  const long long ld = (h->nvec() + 31) / 32 * 32; // basis vectors double as SpMV inputs: room for the halo
+  if (g.m >= m && g.n == n && (!needZ || g.haveZ)) return 0;
+  double** ptrs[] = {&g.V, &g.Z, &g.w, &g.r, &g.tmp, &g.H, &g.cs, &g.sn, &g.s, &g.y, &g.hist};
+  for (auto p : ptrs) if (*p) { cudaFree(*p); *p = nullptr; }
+  g.m = m; g.n = n; g.ld = ld; g.haveZ = needZ;
+  CU(cudaMalloc((void**)&g.V, (size_t)(m + 1) * ld * sizeof(double)));
+  CU(cudaMemset(g.V, 0, (size_t)(m + 1) * ld * sizeof(double)));
+  if (needZ) { CU(cudaMalloc((void**)&g.Z, (size_t)(m + 1) * ld * sizeof(double))); CU(cudaMemset(g.Z, 0, (size_t)(m + 1) * ld * sizeof(double))); }
+  CU(cudaMalloc((void**)&g.w, ld * sizeof(double)));
+  CU(cudaMalloc((void**)&g.r, ld * sizeof(double)));
+  CU(cudaMalloc((void**)&g.tmp, ld * sizeof(double)));
+  CU(cudaMemset(g.w, 0, ld * sizeof(double))); CU(cudaMemset(g.r, 0, ld * sizeof(double))); CU(cudaMemset(g.tmp, 0, ld * sizeof(double)));
+  CU(cudaMalloc((void**)&g.H, (size_t)(m + 1) * m * sizeof(double)));
+  CU(cudaMalloc((void**)&g.cs, (m + 1) * sizeof(double)));
+  CU(cudaMalloc((void**)&g.sn, (m + 1) * sizeof(double)));
+  CU(cudaMalloc((void**)&g.s, (m + 2) * sizeof(double)));
+  CU(cudaMalloc((void**)&g.y, (m + 2) * sizeof(double)));
+  CU(cudaMalloc((void**)&g.hist, (m + 2) * sizeof(double)));
+  return 0;
+}
+void gmres_free(GmresWs& g) {
+  double** ptrs[] = {&g.V, &g.Z, &g.w, &g.r, &g.tmp, &g.H, &g.cs, &g.sn, &g.s, &g.y, &g.hist};
+  for (auto p : ptrs) if (*p) { cudaFree(*p); *p = nullptr; }
+  g.m = 0;
+}
+// allreduce helper: no-op on one GPU
+int allreduce(thcm_b200* h, double* d, int count) {
+  if (!h->dist) return 0;
+  h->launches++;
+  return dist_allreduce_sum(h->dist, d, count, h->stream) == 0 ? 0 : fail(IEMIC_B200_ENCCL, dist_last_error());
+}
+int spmv_impl(thcm_b200* h, double* d_x, double* d_y) {
+  if (h->dist) {
+    if (dist_halo_exchange(h->dist, d_x, h->stream) != 0) return fail(IEMIC_B200_ENCCL, dist_last_error());
+    h->launches += dist_halo_launches(h->dist);
+  }
+  {
+    Timed t(h, 2);
+    SpmvPlan p{h->nblk, h->d_blkrow, spmv_nnz_cap()};
+    launch_spmv(p, h->d_rowptr, h->d_col, h->d_val, d_x, d_y, h->stream);
+    h->launches++;
+  }
+  // TODO(dist): dense integral row spans all ranks; handled by dist_intcond_row when SRES=0 and nranks>1
+  return check_launch(h, "spmv");
+}
+} // namespace
+
+extern "C" {
+
+const char* iemic_b200_last_error(void) { return g_err.c_str(); }
+const char* iemic_b200_version(void) { return "iemic_b200 0.1 (sm_100a)"; }
+int iemic_b200_device_count(void) { int n = 0; if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; } return n; }
+
+int thcm_b200_create_dist(const thcm_b200_config* cfg, const int* landm, int rank, int nranks, const void* nccl_id, thcm_b200_t** out) {
+  if (!cfg || !landm || !out) return fail(IEMIC_B200_EINVAL, "null argument");
+  if (nranks < 1 || rank < 0 || rank >= nranks) return fail(IEMIC_B200_EINVAL, "bad rank / nranks");
+  if (iemic_b200_device_count() < 1) return fail(IEMIC_B200_ECUDA, "no CUDA device: the B200 path has no CPU fallback");
+  thcm_b200* h = new thcm_b200();
+  try {
+    static_assert(sizeof(thcm_b200_config) == sizeof(Config), "config structs must stay layout compatible");
+    Config c;
+    std::memcpy(&c, cfg, sizeof(c));
+    h->host = new Host(c, landm, rank, nranks);
+  } catch (const std::exception& e) {
+    delete h;
+    return fail(IEMIC_B200_ENOTSUP, e.what());
+  }
+  if (nranks > 1) {
+    h->dist = dist_create(*h->host, rank, nranks, nccl_id);
+    if (!h->dist) { std::string m = dist_last_error(); delete h->host; delete h; return fail(IEMIC_B200_ENCCL, m); }
+  }
+  h->rb.nblk_max = red_blocks();
+  cudaError_t e = cudaMalloc((void**)&h->rb.partial, (size_t)h->rb.nblk_max * 512 * sizeof(double));
+  if (e == cudaSuccess) e = cudaMalloc((void**)&h->rb.ticket, 64);
+  if (e == cudaSuccess) e = cudaMemset(h->rb.ticket, 0, 64);
+  if (e == cudaSuccess) e = cudaMalloc((void**)&h->d_small, 1100 * sizeof(double));
+  if (e == cudaSuccess) e = cudaMemset(h->d_small, 0, 1100 * sizeof(double));
+  if (e != cudaSuccess) { delete h->host; delete h; return fail(IEMIC_B200_ECUDA, cudaGetErrorString(e)); }
+  if (int rc = refresh_device(h)) { thcm_b200_destroy(h); return rc; }
+  *out = h;
+  return 0;
+}
+int thcm_b200_create(const thcm_b200_config* cfg, const int* landm, thcm_b200_t** out) {
+  return thcm_b200_create_dist(cfg, landm, 0, 1, nullptr, out);
+}
+int thcm_b200_comm_unique_id(void* id) { return dist_unique_id(id) == 0 ? 0 : fail(IEMIC_B200_ENCCL, dist_last_error()); }
+
+int thcm_b200_destroy(thcm_b200_t* h) {
+  CHECK_H(h);
+  cudaStreamSynchronize(h->stream);
+  flush_timing(h);
+  void* ptrs[] = {h->d_tab, h->d_sig, h->d_rowptr, h->d_col, h->d_val, h->d_diagB, h->d_frc, h->d_coefS, h->d_blkrow, h->d_xs, h->d_ys,
+                  h->rb.partial, h->rb.ticket, h->d_small};
+  for (void* p : ptrs) if (p) cudaFree(p);
+  gmres_free(h->g);
+  if (h->dist) dist_destroy(h->dist);
+  delete h->host;
+  delete h;
+  return 0;
+}
+int thcm_b200_set_stream(thcm_b200_t* h, void* s) { CHECK_H(h); h->stream = (cudaStream_t)s; return 0; }
+int thcm_b200_sync(thcm_b200_t* h) { CHECK_H(h); CU(cudaStreamSynchronize(h->stream)); return 0; }
+
+int thcm_b200_set_par(thcm_b200_t* h, int idx1, double value) {
+  CHECK_H(h);
+  if (idx1 < 1 || idx1 > NPAR) return fail(IEMIC_B200_EINVAL, "parameter index out of range");
+  try { h->host->set_par(idx1, value); } catch (const std::exception& e) { return fail(IEMIC_B200_ENOTSUP, e.what()); }
+  return 0;
+}
+int thcm_b200_get_par(thcm_b200_t* h, int idx1, double* value) {
+  CHECK_H(h);
+  if (idx1 < 1 || idx1 > NPAR || !value) return fail(IEMIC_B200_EINVAL, "parameter index out of range");
+  *value = h->host->get_par(idx1);
+  return 0;
+}
+int thcm_b200_set_landmask(thcm_b200_t* h, const int* landm) {
+  CHECK_H(h);
+  try { h->host->set_landmask(landm); } catch (const std::exception& e) { return fail(IEMIC_B200_ENOTSUP, e.what()); }
+  CU(cudaStreamSynchronize(h->stream));
+  gmres_free(h->g);
+  if (h->d_xs) { cudaFree(h->d_xs); cudaFree(h->d_ys); h->d_xs = h->d_ys = nullptr; }
+  return refresh_device(h);
+}
+int thcm_b200_set_intcond_correction(thcm_b200_t* h, double corr) { CHECK_H(h); h->host->intCorrection = corr; return 0; }
+
+int thcm_b200_sizes(thcm_b200_t* h, int64_t* nrows, int64_t* nvec, int64_t* nnz, int64_t* nglob) {
+  CHECK_H(h);
+  if (nrows) *nrows = h->nrows();
+  if (nvec) *nvec = h->nvec();
+  if (nnz) *nnz = (int64_t)h->host->col.size();
+  if (nglob) *nglob = (int64_t)h->host->ndim;
+  return 0;
+}
+int thcm_b200_block(thcm_b200_t* h, int* i0, int* j0, int* nloc, int* mloc, int* npN, int* npM) {
+  CHECK_H(h);
+  Host* H = h->host;
+  if (i0) *i0 = H->S.io0 - 1;
+  if (j0) *j0 = H->S.jo0 - 1;
+  if (nloc) *nloc = H->S.nloc;
+  if (mloc) *mloc = H->S.mloc;
+  if (npN) *npN = H->npN;
+  if (npM) *npM = H->npM;
+  return 0;
+}
+int thcm_b200_global_ids(thcm_b200_t* h, int64_t* gid) {
+  CHECK_H(h);
+  const std::vector<long long>& g = h->host->gid;
+  for (size_t q = 0; q < g.size(); q++) gid[q] = g[q];
+  return 0;
+}
+
+int thcm_b200_halo_exchange(thcm_b200_t* h, double* d_x) {
+  CHECK_H(h);
+  if (!h->dist) return 0;
+  if (dist_halo_exchange(h->dist, d_x, h->stream) != 0) return fail(IEMIC_B200_ENCCL, dist_last_error());
+  h->launches += dist_halo_launches(h->dist);
+  return 0;
+}
+
+int thcm_b200_rhs(thcm_b200_t* h, const double* d_x, double* d_F) {
+  CHECK_H(h);
+  if (int rc = refresh_device(h)) return rc;
+  Host* H = h->host;
+  AsmArgs a = asm_args(h, d_x);
+  a.F = d_F;
+  {
+    Timed t(h, 0);
+    launch_rhs(a, h->stream);
+    h->launches++;
+  }
+  if (int rc = check_launch(h, "rhs_kernel")) return rc;
+  const bool intc = H->cfg.sres == 0 && H->rowintcon >= 0;
+  if (intc) { // THCM.C:1006-1018
+    launch_intcond_dot(h->d_coefS, d_x, h->nrows() / 6, h->d_small + 1029, h->stream);
+    h->launches++;
+    if (int rc = allreduce(h, h->d_small + 1029, 1)) return rc;
+  }
+  const int r = (intc && H->owns_rowintcon) ? H->rowintcon_local : -1;
+  if (r >= 0 || H->rowPfix1_local >= 0 || H->rowPfix2_local >= 0) {
+    launch_intcond_finish(h->d_small + 1029, (double)H->cfg.int_sign, H->intCorrection, d_F, r, H->rowPfix1_local, H->rowPfix2_local, h->stream);
+    h->launches++;
+  }
+  return check_launch(h, "rhs epilogue");
+}
+
+int thcm_b200_jacobian(thcm_b200_t* h, const double* d_x) {
+  CHECK_H(h);
+  if (int rc = refresh_device(h)) return rc;
+  AsmArgs a = asm_args(h, d_x);
+  {
+    Timed t(h, 1);
+    launch_jac(a, h->stream);
+    h->launches++;
+  }
+  return check_launch(h, "jac_kernel");
+}
+
+int thcm_b200_csr(thcm_b200_t* h, const int** rp, const int** col, double** val, const double** diagB) {
+  CHECK_H(h);
+  if (int rc = refresh_device(h)) return rc;
+  if (rp) *rp = h->d_rowptr;
+  if (col) *col = h->d_col;
+  if (val) *val = h->d_val;
+  if (diagB) *diagB = h->d_diagB;
+  return 0;
+}
+int thcm_b200_graph_host(thcm_b200_t* h, int* rowptr, int* col) {
+  CHECK_H(h);
+  Host* H = h->host;
+  if (rowptr) std::memcpy(rowptr, H->rowptr.data(), H->rowptr.size() * sizeof(int));
+  if (col) std::memcpy(col, H->col.data(), H->col.size() * sizeof(int));
+  return 0;
+}
+int thcm_b200_values_host(thcm_b200_t* h, double* val, double* diagB) {
+  CHECK_H(h);
+  CU(cudaStreamSynchronize(h->stream));
+  if (val) CU(cudaMemcpy(val, h->d_val, h->host->col.size() * sizeof(double), cudaMemcpyDeviceToHost));
+  if (diagB) CU(cudaMemcpy(diagB, h->d_diagB, (size_t)h->nrows() * sizeof(double), cudaMemcpyDeviceToHost));
+  return 0;
+}
+int thcm_b200_set_values_host(thcm_b200_t* h, const double* val) {
+  CHECK_H(h);
+  if (int rc = refresh_device(h)) return rc;
+  CU(cudaStreamSynchronize(h->stream));
+  CU(cudaMemcpy(h->d_val, val, h->host->col.size() * sizeof(double), cudaMemcpyHostToDevice));
+  return 0;
+}
+int thcm_b200_forcing_host(thcm_b200_t* h, double* frc) {
+  CHECK_H(h);
+  std::memcpy(frc, h->host->frc.data(), h->host->frc.size() * sizeof(double));
+  return 0;
+}
+int thcm_b200_intcond_host(thcm_b200_t* h, double* coeff, int* rowintcon) {
+  CHECK_H(h);
+  if (coeff) std::memcpy(coeff, h->host->intcond.data(), h->host->intcond.size() * sizeof(double));
+  if (rowintcon) *rowintcon = h->host->rowintcon;
+  return 0;
+}
+
+int thcm_b200_rhs_host(thcm_b200_t* h, const double* x, double* F) {
+  CHECK_H(h);
+  if (int rc = refresh_device(h)) return rc;
+  const size_t nb = (size_t)h->nrows() * sizeof(double);
+  CU(cudaMemcpyAsync(h->d_xs, x, nb, cudaMemcpyHostToDevice, h->stream));
+  if (int rc = thcm_b200_halo_exchange(h, h->d_xs)) return rc;
+  if (int rc = thcm_b200_rhs(h, h->d_xs, h->d_ys)) return rc;
+  CU(cudaMemcpyAsync(F, h->d_ys, nb, cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  return 0;
+}
+int thcm_b200_jacobian_host(thcm_b200_t* h, const double* x, double* val, double* diagB) {
+  CHECK_H(h);
+  if (int rc = refresh_device(h)) return rc;
+  const size_t nb = (size_t)h->nrows() * sizeof(double);
+  CU(cudaMemcpyAsync(h->d_xs, x, nb, cudaMemcpyHostToDevice, h->stream));
+  if (int rc = thcm_b200_halo_exchange(h, h->d_xs)) return rc;
+  if (int rc = thcm_b200_jacobian(h, h->d_xs)) return rc;
+  if (val) CU(cudaMemcpyAsync(val, h->d_val, h->host->col.size() * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  if (diagB) CU(cudaMemcpyAsync(diagB, h->d_diagB, nb, cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  return 0;
+}
+
+int thcm_b200_spmv(thcm_b200_t* h, double* d_x, double* d_y) {
+  CHECK_H(h);
+  if (int rc = refresh_device(h)) return rc;
+  return spmv_impl(h, d_x, d_y);
+}
+int thcm_b200_spmv_host(thcm_b200_t* h, const double* x, double* y) {
+  CHECK_H(h);
+  if (int rc = refresh_device(h)) return rc;
+  const size_t nb = (size_t)h->nrows() * sizeof(double);
+  CU(cudaMemcpyAsync(h->d_xs, x, nb, cudaMemcpyHostToDevice, h->stream));
+  if (int rc = spmv_impl(h, h->d_xs, h->d_ys)) return rc;
+  CU(cudaMemcpyAsync(y, h->d_ys, nb, cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  return 0;
+}
+
+// ---- vectors ----
+int vec_b200_dot(thcm_b200_t* h, const double* a, const double* b, double* result) {
+  CHECK_H(h);
+  launch_dot(a, b, h->nrows(), h->d_small + 1028, h->rb, h->stream);
+  h->launches++;
+  if (int rc = allreduce(h, h->d_small + 1028, 1)) return rc;
+  CU(cudaMemcpyAsync(result, h->d_small + 1028, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  return 0;
+}
+int vec_b200_norm2(thcm_b200_t* h, const double* a, double* result) {
+  int rc = vec_b200_dot(h, a, a, result);
+  if (rc == 0) *result = std::sqrt(*result);
+  return rc;
+}
+int vec_b200_update(thcm_b200_t* h, double a, const double* A, double b, double* y) {
+  CHECK_H(h);
+  launch_update(a, A, b, y, h->nrows(), h->stream);
+  h->launches++;
+  return check_launch(h, "update");
+}
+int vec_b200_scale(thcm_b200_t* h, double a, double* y) { return vec_b200_update(h, a, y, 0.0, y); }
+int vec_b200_putscalar(thcm_b200_t* h, double a, double* y) {
+  CHECK_H(h);
+  launch_fill(a, y, h->nrows(), h->stream);
+  h->launches++;
+  return check_launch(h, "fill");
+}
+
+// ---- GMRES (GMRESSolver.H:81-255) ----
+int gmres_b200_solve(thcm_b200_t* h, const double* d_b, double* d_x, int m, int maxit, double tol, int ortho, int prec,
+                     const double* d_blockinv, int check_every, double* hist_out, int* iters_out) {
+  CHECK_H(h);
+  if (m < 1 || m > 500) return fail(IEMIC_B200_EINVAL, "GMRES restart length must be in 1..500");
+  if (prec == GMRES_B200_PREC_BLOCKJACOBI && !d_blockinv) return fail(IEMIC_B200_EINVAL, "block Jacobi needs d_blockinv");
+  if (prec != GMRES_B200_PREC_NONE && prec != GMRES_B200_PREC_BLOCKJACOBI) return fail(IEMIC_B200_EINVAL, "unknown preconditioner");
+  if (int rc = refresh_device(h)) return rc;
+  const bool flex = prec != GMRES_B200_PREC_NONE;
+  if (int rc = gmres_alloc(h, m, flex)) return rc;
+  GmresWs& g = h->g;
+  const long long n = h->nrows(), ld = g.ld;
+  cudaStream_t st = h->stream;
+  double* sm = h->d_small;
+  double *h1 = sm, *h2 = sm + 512, *nrm2 = sm + 1024, *hnext = sm + 1025, *bnorm = sm + 1026, *beta = sm + 1027;
+  auto L = [&](int k = 1) { h->launches += k; };
+
+  // normb
+  launch_dot(d_b, d_b, n, nrm2, h->rb, st); L();
+  if (int rc = allreduce(h, nrm2, 1)) return rc;
+  launch_sqrt_store(nrm2, bnorm, st); L();
+  double normb = 0.0;
+  CU(cudaMemcpyAsync(&normb, bnorm, sizeof(double), cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  if (normb == 0.0) { normb = 1.0; CU(cudaMemcpyAsync(bnorm, &normb, sizeof(double), cudaMemcpyHostToDevice, st)); }
+  // r = b - A x  (x is copied into a halo-capable work vector first)
+  CU(cudaMemcpyAsync(g.tmp, d_x, n * sizeof(double), cudaMemcpyDeviceToDevice, st));
+  if (int rc = spmv_impl(h, g.tmp, g.r)) return rc;
+  launch_residual(d_b, g.r, n, st); L();
+  launch_dot(g.r, g.r, n, nrm2, h->rb, st); L();
+  if (int rc = allreduce(h, nrm2, 1)) return rc;
+  double r2 = 0.0;
+  CU(cudaMemcpyAsync(&r2, nrm2, sizeof(double), cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  double resid = std::sqrt(r2) / normb;
+  int iter = 0, nh = 0, ret = 1;
+  if (resid <= tol) { if (iters_out) *iters_out = 0; return 0; }
+
+  std::vector<double> hbuf(m + 2);
+  while (iter <= maxit) {
+    // beta = ||r|| ; V0 = r / beta ; s = beta e1   (nrm2 holds ||r||^2)
+    launch_cycle_init(nrm2, g.s, m, beta, st); L();
+    launch_scale_copy(g.r, g.V, n, beta, 1, 0, st); L();
+    int i, space = 0, done_in_cycle = 0;
+    bool conv = false;
+    for (i = 0; i < m && iter <= maxit; i++, iter++) {
+      double* vi = g.V + (size_t)i * ld;
+      if (flex) {
+        double* zi = g.Z + (size_t)i * ld;
+        launch_block_jacobi(d_blockinv, vi, zi, n / 6, st); L();
+        if (int rc = spmv_impl(h, zi, g.w)) return rc;
+      } else if (int rc = spmv_impl(h, vi, g.w)) return rc;
+      {
+        Timed t(h, 3);
+        if (ortho == GMRES_B200_CGS2) {
+          launch_multi_dot(g.V, ld, i + 1, g.w, n, h1, h->rb, st); L();
+          if (int rc = allreduce(h, h1, i + 1)) return rc;
+          launch_multi_axpy(g.V, ld, i + 1, h1, g.w, n, nullptr, h->rb, st); L();
+          launch_multi_dot(g.V, ld, i + 1, g.w, n, h2, h->rb, st); L();
+          if (int rc = allreduce(h, h2, i + 1)) return rc;
+          launch_multi_axpy(g.V, ld, i + 1, h2, g.w, n, nrm2, h->rb, st); L();
+          if (int rc = allreduce(h, nrm2, 1)) return rc;
+        } else { // MGS, dependent chain exactly as GMRESSolver.H:177-181
+          for (int k = 0; k <= i; k++) {
+            launch_axpy_dot(k ? h1 + k - 1 : nullptr, k ? g.V + (size_t)(k - 1) * ld : nullptr, g.V + (size_t)k * ld, g.w, n, h1 + k, h->rb, st); L();
+            if (int rc = allreduce(h, h1 + k, 1)) return rc;
+          }
+          launch_axpy_dot(h1 + i, g.V + (size_t)i * ld, nullptr, g.w, n, nrm2, h->rb, st); L();
+          if (int rc = allreduce(h, nrm2, 1)) return rc;
+        }
+        GivensArgs ga;
+        ga.H = g.H; ga.ldh = m + 1; ga.cs = g.cs; ga.sn = g.sn; ga.s = g.s; ga.h1 = h1; ga.h2 = (ortho == GMRES_B200_CGS2) ? h2 : nullptr;
+        ga.nrm2 = nrm2; ga.sq = 1; ga.bnorm = bnorm; ga.hist = g.hist; ga.hnext = hnext; ga.j = i;
+        launch_givens(ga, st); L();
+        launch_scale_copy(g.w, g.V + (size_t)(i + 1) * ld, n, hnext, 1, 0, st); L();
+      }
+      space = i; done_in_cycle = i + 1;
+      if (check_every > 0 && ((i + 1) % check_every == 0)) {
+        CU(cudaMemcpyAsync(&resid, g.hist + i, sizeof(double), cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        if (resid < tol) { conv = true; break; }
+      }
+    }
+    if (int rc = check_launch(h, "gmres cycle")) return rc;
+    // residual history of this cycle
+    CU(cudaMemcpyAsync(hbuf.data(), g.hist, done_in_cycle * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    for (int q = 0; q < done_in_cycle; q++) if (hist_out) hist_out[nh++] = hbuf[q];
+    if (done_in_cycle > 0) resid = hbuf[done_in_cycle - 1];
+    if (!conv && resid < tol) conv = true;
+    // Update: y = H^-1 s ; x += Z y   (GMRESSolver.H:292-313)
+    launch_backsolve(g.H, m + 1, g.s, space, g.y, st); L();
+    launch_multi_axpy_plus(flex ? g.Z : g.V, ld, space + 1, g.y, d_x, n, st); L();
+    // true residual
+    CU(cudaMemcpyAsync(g.tmp, d_x, n * sizeof(double), cudaMemcpyDeviceToDevice, st));
+    if (int rc = spmv_impl(h, g.tmp, g.r)) return rc;
+    launch_residual(d_b, g.r, n, st); L();
+    launch_dot(g.r, g.r, n, nrm2, h->rb, st); L();
+    if (int rc = allreduce(h, nrm2, 1)) return rc;
+    if (conv) { ret = 0; break; }
+  }
+  CU(cudaMemcpyAsync(&r2, nrm2, sizeof(double), cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  if (hist_out) hist_out[nh] = std::sqrt(r2) / normb; // explicit residual after the last cycle (:241-242)
+  if (iters_out) *iters_out = iter;
+  if (int rc = check_launch(h, "gmres")) return rc;
+  return ret;
+}
+
+int gmres_b200_solve_host(thcm_b200_t* h, const double* b, double* x, int m, int maxit, double tol, int ortho, int prec,
+                          const double* blockinv, int check_every, double* hist, int* iters) {
+  CHECK_H(h);
+  if (int rc = refresh_device(h)) return rc;
+  const long long n = h->nrows();
+  double *d_b = nullptr, *d_x = nullptr, *d_bi = nullptr;
+  CU(cudaMalloc((void**)&d_b, n * sizeof(double)));
+  CU(cudaMalloc((void**)&d_x, n * sizeof(double)));
+  CU(cudaMemcpy(d_b, b, n * sizeof(double), cudaMemcpyHostToDevice));
+  CU(cudaMemcpy(d_x, x, n * sizeof(double), cudaMemcpyHostToDevice));
+  if (prec == GMRES_B200_PREC_BLOCKJACOBI && blockinv) {
+    CU(cudaMalloc((void**)&d_bi, n * 6 * sizeof(double)));
+    CU(cudaMemcpy(d_bi, blockinv, n * 6 * sizeof(double), cudaMemcpyHostToDevice));
+  }
+  int rc = gmres_b200_solve(h, d_b, d_x, m, maxit, tol, ortho, prec, d_bi, check_every, hist, iters);
+  if (rc >= 0) cudaMemcpy(x, d_x, n * sizeof(double), cudaMemcpyDeviceToHost);
+  cudaFree(d_b); cudaFree(d_x); if (d_bi) cudaFree(d_bi);
+  return rc;
+}
+
+int thcm_b200_launch_count(thcm_b200_t* h, int64_t* launches) { CHECK_H(h); *launches = h->launches; return 0; }
+int thcm_b200_timing_enable(thcm_b200_t* h, int on) { CHECK_H(h); if (!on) flush_timing(h); h->timing = on != 0; return 0; }
+int thcm_b200_timing_reset(thcm_b200_t* h) {
+  CHECK_H(h);
+  flush_timing(h);
+  for (int q = 0; q < 4; q++) { h->t_total[q] = 0; h->t_count[q] = 0; }
+  return 0;
+}
+int thcm_b200_timing_get(thcm_b200_t* h, int which, double* total_ms, int64_t* count) {
+  CHECK_H(h);
+  if (which < 0 || which > 3) return fail(IEMIC_B200_EINVAL, "which must be 0..3");
+  if (int rc = flush_timing(h)) return rc;
+  if (total_ms) *total_ms = h->t_total[which];
+  if (count) *count = h->t_count[which];
+  return 0;
+}
+
+int iemic_b200_malloc(void** p, int64_t bytes) { CU(cudaMalloc(p, (size_t)bytes)); return 0; }
+int iemic_b200_free(void* p) { CU(cudaFree(p)); return 0; }
+int iemic_b200_memcpy_h2d(void* d, const void* s, int64_t bytes) { CU(cudaMemcpy(d, s, (size_t)bytes, cudaMemcpyHostToDevice)); return 0; }
+int iemic_b200_memcpy_d2h(void* d, const void* s, int64_t bytes) { CU(cudaMemcpy(d, s, (size_t)bytes, cudaMemcpyDeviceToHost)); return 0; }
+
+} // extern "C"

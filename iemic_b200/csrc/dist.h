@@ -1,0 +1,17 @@
+// dist.h -- multi-GPU plumbing of the hot path: the reference's 2-D lon x lat domain decomposition
+// (TRIOS::Domain, src/trios/TRIOS_Domain.C:81-195, 517-664) with NCCL over NVLink in place of Epetra Import/Export
+// and Epetra_Comm::SumAll.  NCCL is bound at run time (dlopen of the libnccl the host process already uses).
+#pragma once
+#include <cuda_runtime.h>
+#include "thcm_host.h"
+
+namespace thcm {
+struct Dist;
+Dist* dist_create(const Host& H, int rank, int nranks, const void* nccl_id);
+void dist_destroy(Dist*);
+int dist_unique_id(void* id128);
+int dist_allreduce_sum(Dist*, double* d_buf, int count, cudaStream_t st);
+int dist_halo_exchange(Dist*, double* d_x, cudaStream_t st);
+int dist_halo_launches(Dist*);
+const char* dist_last_error();
+} // namespace thcm

@@ -1,0 +1,307 @@
+// gmres.cu -- vector kernels of the Krylov solver for sm_100a.
+//
+// Replaces the vector concept GMRESSolver relies on (dot / norm / update / scale, src/gmressolver/GMRESSolverDecl.H:7-16)
+// and the modified Gram-Schmidt loop of GMRESSolver::solve (src/gmressolver/GMRESSolver.H:177-187) by fused kernels:
+//
+//   multi_dot   h[k] = <V_k, w> for all k in ONE pass over the basis (w is re-read once per 8 basis vectors),
+//   multi_axpy  w -= sum_k h[k] V_k in one pass, with ||w||^2 of the result accumulated in the epilogue,
+//   axpy_dot    the MGS step "w -= h_{k-1} V_{k-1}; h_k = <w, V_k>" in one pass (reproduces the reference's ordering),
+//   givens      Hessenberg column, plane rotations and residual estimate on the device, so a whole Arnoldi
+//               step needs no host synchronisation.
+//
+// Reductions are two-stage and deterministic: warp shuffles -> per-block partials in global memory -> the last
+// block to arrive (atomic ticket) adds the partials in block order.  All loads are 16-byte vectorised; basis
+// vectors are streamed with evict-first hints, w stays cacheable.
+// HBM traffic per call: multi_dot (nv + ceil(nv/8)) * 8n, multi_axpy (nv + 2) * 8n, axpy_dot 4 * 8n.
+#include "kernels.h"
+
+namespace thcm {
+namespace {
+constexpr int RT = 256;          // threads per block
+constexpr int KT = 8;            // basis vectors per register tile in multi_dot
+constexpr int MAXV = 512;        // largest basis handled by one call
+constexpr unsigned FULL = 0xffffffffu;
+
+__device__ __forceinline__ double warp_sum(double s) {
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(FULL, s, o);
+  return s;
+}
+// Block-level sum of NV values per thread -> partial[blockIdx.x * stride + k]; returns true in the last block
+// (all threads) once every block has published its partials.
+template <int NV>
+__device__ __forceinline__ void block_publish(const double (&acc)[NV], int nvalid, double* partial, int stride, int k0) {
+  __shared__ double red[NV][RT / 32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < NV; k++) {
+    double s = warp_sum(acc[k]);
+    if (lane == 0) red[k][warp] = s;
+  }
+  __syncthreads();
+  if (threadIdx.x < NV && threadIdx.x < nvalid) {
+    double s = 0.0;
+#pragma unroll
+    for (int w = 0; w < RT / 32; w++) s += red[threadIdx.x][w];
+    partial[(size_t)blockIdx.x * stride + k0 + threadIdx.x] = s;
+  }
+  __syncthreads();
+}
+__device__ __forceinline__ bool last_block(unsigned int* ticket) {
+  __shared__ bool is_last;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned int t = atomicAdd(ticket, 1u);
+    is_last = (t == gridDim.x - 1);
+    if (is_last) *ticket = 0u; // ready for the next launch on this stream
+  }
+  __syncthreads();
+  if (is_last) __threadfence();
+  return is_last;
+}
+// out[k] = sum over blocks of partial[b*stride + k], fixed order; one warp per k
+__device__ __forceinline__ void final_sum(const double* partial, int stride, int nv, double* out) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int k = warp; k < nv; k += RT / 32) {
+    double s = 0.0;
+    for (int b = lane; b < (int)gridDim.x; b += 32) s += __ldcg(partial + (size_t)b * stride + k);
+    s = warp_sum(s);
+    if (lane == 0) out[k] = s;
+  }
+}
+
+__global__ void __launch_bounds__(RT) multi_dot_kernel(const double* __restrict__ V, long long ldv, int nv, const double* __restrict__ w,
+                                                       long long n, double* out, double* partial, unsigned int* ticket) {
+  const long long n2 = n >> 1; // double2 elements (n is even: 6 unknowns per cell)
+  const double2* w2 = reinterpret_cast<const double2*>(w);
+  for (int k0 = 0; k0 < nv; k0 += KT) {
+    double acc[KT];
+#pragma unroll
+    for (int k = 0; k < KT; k++) acc[k] = 0.0;
+    const int nk = min(KT, nv - k0);
+    for (long long i = (long long)blockIdx.x * RT + threadIdx.x; i < n2; i += (long long)gridDim.x * RT) {
+      const double2 wv = w2[i];
+      double2 v[KT];
+#pragma unroll
+      for (int k = 0; k < KT; k++)
+        if (k < nk) v[k] = __ldcs(reinterpret_cast<const double2*>(V + (size_t)(k0 + k) * ldv) + i);
+#pragma unroll
+      for (int k = 0; k < KT; k++)
+        if (k < nk) acc[k] = fma(v[k].y, wv.y, fma(v[k].x, wv.x, acc[k]));
+    }
+    block_publish<KT>(acc, nk, partial, MAXV, k0);
+  }
+  if (last_block(ticket)) final_sum(partial, MAXV, nv, out);
+}
+
+__global__ void __launch_bounds__(RT) multi_axpy_kernel(const double* __restrict__ V, long long ldv, int nv, const double* __restrict__ h,
+                                                        double* __restrict__ w, long long n, double* nrm2_out, double* partial,
+                                                        unsigned int* ticket) {
+  __shared__ double hs[MAXV];
+  for (int k = threadIdx.x; k < nv; k += RT) hs[k] = h[k];
+  __syncthreads();
+  const long long n2 = n >> 1;
+  double2* w2 = reinterpret_cast<double2*>(w);
+  double acc[1] = {0.0};
+  for (long long i = (long long)blockIdx.x * RT + threadIdx.x; i < n2; i += (long long)gridDim.x * RT) {
+    double2 wv = w2[i];
+    for (int k0 = 0; k0 < nv; k0 += KT) {
+      double2 v[KT];
+#pragma unroll
+      for (int k = 0; k < KT; k++)
+        if (k0 + k < nv) v[k] = __ldcs(reinterpret_cast<const double2*>(V + (size_t)(k0 + k) * ldv) + i);
+#pragma unroll
+      for (int k = 0; k < KT; k++)
+        if (k0 + k < nv) { wv.x = fma(-hs[k0 + k], v[k].x, wv.x); wv.y = fma(-hs[k0 + k], v[k].y, wv.y); }
+    }
+    w2[i] = wv;
+    acc[0] = fma(wv.y, wv.y, fma(wv.x, wv.x, acc[0]));
+  }
+  if (nrm2_out) {
+    block_publish<1>(acc, 1, partial, MAXV, 0);
+    if (last_block(ticket)) final_sum(partial, MAXV, 1, nrm2_out);
+  }
+}
+
+__global__ void __launch_bounds__(RT) axpy_dot_kernel(const double* __restrict__ hprev, const double* __restrict__ vprev,
+                                                      const double* __restrict__ vnext, double* __restrict__ w, long long n, double* out,
+                                                      double* partial, unsigned int* ticket) {
+  const long long n2 = n >> 1;
+  double2* w2 = reinterpret_cast<double2*>(w);
+  const double hp = hprev ? *hprev : 0.0;
+  double acc[1] = {0.0};
+  for (long long i = (long long)blockIdx.x * RT + threadIdx.x; i < n2; i += (long long)gridDim.x * RT) {
+    double2 wv = w2[i];
+    if (hprev) {
+      const double2 vp = __ldcs(reinterpret_cast<const double2*>(vprev) + i);
+      wv.x = fma(-hp, vp.x, wv.x); wv.y = fma(-hp, vp.y, wv.y);
+      w2[i] = wv;
+    }
+    const double2 vn = vnext ? __ldcs(reinterpret_cast<const double2*>(vnext) + i) : wv;
+    acc[0] = fma(wv.y, vn.y, fma(wv.x, vn.x, acc[0]));
+  }
+  block_publish<1>(acc, 1, partial, MAXV, 0);
+  if (last_block(ticket)) final_sum(partial, MAXV, 1, out);
+}
+
+__global__ void __launch_bounds__(RT) dot_kernel(const double* __restrict__ a, const double* __restrict__ b, long long n, double* out,
+                                                 double* partial, unsigned int* ticket) {
+  const long long n2 = n >> 1;
+  double acc[1] = {0.0};
+  for (long long i = (long long)blockIdx.x * RT + threadIdx.x; i < n2; i += (long long)gridDim.x * RT) {
+    const double2 x = reinterpret_cast<const double2*>(a)[i], y = reinterpret_cast<const double2*>(b)[i];
+    acc[0] = fma(x.y, y.y, fma(x.x, y.x, acc[0]));
+  }
+  block_publish<1>(acc, 1, partial, MAXV, 0);
+  if (last_block(ticket)) final_sum(partial, MAXV, 1, out);
+}
+
+__global__ void __launch_bounds__(RT) scale_copy_kernel(const double* __restrict__ x, double* __restrict__ y, long long n, const double* s, int inv, int sq) {
+  double a = *s;
+  if (sq) a = sqrt(a);
+  if (inv) a = 1.0 / a;
+  const long long n2 = n >> 1;
+  for (long long i = (long long)blockIdx.x * RT + threadIdx.x; i < n2; i += (long long)gridDim.x * RT) {
+    double2 v = reinterpret_cast<const double2*>(x)[i];
+    v.x = a * v.x; v.y = a * v.y;
+    reinterpret_cast<double2*>(y)[i] = v;
+  }
+}
+__global__ void __launch_bounds__(RT) update_kernel(double a, const double* __restrict__ A, double b, double* __restrict__ y, long long n) {
+  const long long n2 = n >> 1;
+  for (long long i = (long long)blockIdx.x * RT + threadIdx.x; i < n2; i += (long long)gridDim.x * RT) {
+    const double2 av = reinterpret_cast<const double2*>(A)[i];
+    double2 yv = reinterpret_cast<double2*>(y)[i];
+    if (b == 0.0) { yv.x = a * av.x; yv.y = a * av.y; } // Epetra semantics: b==0 ignores (possibly NaN) old content
+    else { yv.x = a * av.x + b * yv.x; yv.y = a * av.y + b * yv.y; }
+    reinterpret_cast<double2*>(y)[i] = yv;
+  }
+}
+__global__ void __launch_bounds__(RT) fill_kernel(double a, double* __restrict__ y, long long n) {
+  for (long long i = (long long)blockIdx.x * RT + threadIdx.x; i < n; i += (long long)gridDim.x * RT) y[i] = a;
+}
+__global__ void __launch_bounds__(RT) multi_axpy_plus_kernel(const double* __restrict__ Z, long long ldz, int nv, const double* __restrict__ yk,
+                                                             double* __restrict__ x, long long n) {
+  __shared__ double hs[MAXV];
+  for (int k = threadIdx.x; k < nv; k += RT) hs[k] = yk[k];
+  __syncthreads();
+  const long long n2 = n >> 1;
+  for (long long i = (long long)blockIdx.x * RT + threadIdx.x; i < n2; i += (long long)gridDim.x * RT) {
+    double2 xv = reinterpret_cast<double2*>(x)[i];
+    for (int k = 0; k < nv; k++) {
+      const double2 v = __ldcs(reinterpret_cast<const double2*>(Z + (size_t)k * ldz) + i);
+      xv.x = fma(hs[k], v.x, xv.x); xv.y = fma(hs[k], v.y, xv.y);
+    }
+    reinterpret_cast<double2*>(x)[i] = xv;
+  }
+}
+__global__ void __launch_bounds__(RT) block_jacobi_kernel(const double* __restrict__ binv, const double* __restrict__ v, double* __restrict__ z, long long nb) {
+  // one thread per output row: 6 consecutive threads share a block; row-major 6x6 blocks
+  for (long long r = (long long)blockIdx.x * RT + threadIdx.x; r < 6 * nb; r += (long long)gridDim.x * RT) {
+    const long long b = r / 6;
+    const double* B = binv + r * 6;
+    const double* vb = v + b * 6;
+    double s = 0.0;
+#pragma unroll
+    for (int c = 0; c < 6; c++) s += B[c] * vb[c];
+    z[r] = s;
+  }
+}
+__global__ void __launch_bounds__(RT) residual_kernel(const double* __restrict__ b, double* __restrict__ r, long long n) {
+  for (long long i = (long long)blockIdx.x * RT + threadIdx.x; i < n; i += (long long)gridDim.x * RT) r[i] = 1.0 * b[i] + -1.0 * r[i];
+}
+
+// GMRESSolver.H:258-289
+__device__ void gen_rot(double& dx, double& dy, double& cs, double& sn) {
+  if (dy == 0.0) { cs = 1.0; sn = 0.0; }
+  else if (fabs(dy) > fabs(dx)) { double temp = dx / dy; sn = 1.0 / sqrt(1.0 + temp * temp); cs = temp * sn; }
+  else { double temp = dy / dx; cs = 1.0 / sqrt(1.0 + temp * temp); sn = temp * cs; }
+}
+__device__ void app_rot(double& dx, double& dy, double cs, double sn) {
+  double temp = cs * dx + sn * dy;
+  dy = -sn * dx + cs * dy;
+  dx = temp;
+}
+__global__ void givens_kernel(const GivensArgs g) {
+  if (threadIdx.x != 0) return;
+  const int j = g.j;
+  double* Hc = g.H + (size_t)j * g.ldh;
+  for (int k = 0; k <= j; k++) Hc[k] = g.h1[k] + (g.h2 ? g.h2[k] : 0.0);
+  double nrm = g.sq ? sqrt(*g.nrm2) : *g.nrm2;
+  Hc[j + 1] = nrm;
+  *g.hnext = nrm;
+  for (int k = 0; k < j; k++) app_rot(Hc[k], Hc[k + 1], g.cs[k], g.sn[k]);
+  gen_rot(Hc[j], Hc[j + 1], g.cs[j], g.sn[j]);
+  app_rot(Hc[j], Hc[j + 1], g.cs[j], g.sn[j]);
+  app_rot(g.s[j], g.s[j + 1], g.cs[j], g.sn[j]);
+  g.hist[j] = fabs(g.s[j + 1]) / *g.bnorm;
+}
+__global__ void backsolve_kernel(const double* H, int ldh, const double* s, int k, double* y) {
+  if (threadIdx.x != 0) return;
+  for (int i = 0; i <= k; i++) y[i] = s[i];
+  for (int i = k; i >= 0; i--) { // GMRESSolver.H:400-410
+    y[i] /= H[(size_t)i * ldh + i];
+    for (int jj = i - 1; jj >= 0; jj--) y[jj] -= H[(size_t)i * ldh + jj] * y[i];
+  }
+}
+__global__ void cycle_init_kernel(const double* nrm2, double* s, int m, double* beta_out) {
+  if (threadIdx.x != 0) return;
+  double beta = sqrt(*nrm2);
+  s[0] = beta;
+  for (int i = 1; i <= m; i++) s[i] = 0.0;
+  *beta_out = beta;
+}
+__global__ void sqrt_store_kernel(const double* nrm2, double* out) {
+  if (threadIdx.x == 0) *out = sqrt(*nrm2);
+}
+
+int g_red_blocks = 0;
+int grid_for(long long n) {
+  long long need = ((n >> 1) + RT - 1) / RT;
+  int cap = red_blocks();
+  return (int)(need < 1 ? 1 : (need < cap ? need : cap));
+}
+} // namespace
+
+int red_blocks() {
+  if (g_red_blocks == 0) {
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    g_red_blocks = sms * 8; // 8 resident blocks of 256 threads per SM: one full wave
+  }
+  return g_red_blocks;
+}
+
+void launch_multi_dot(const double* V, long long ldv, int nv, const double* w, long long n, double* out, RedBuf rb, cudaStream_t st) {
+  multi_dot_kernel<<<grid_for(n), RT, 0, st>>>(V, ldv, nv, w, n, out, rb.partial, rb.ticket);
+}
+void launch_multi_axpy(const double* V, long long ldv, int nv, const double* h, double* w, long long n, double* nrm2_out, RedBuf rb, cudaStream_t st) {
+  multi_axpy_kernel<<<grid_for(n), RT, 0, st>>>(V, ldv, nv, h, w, n, nrm2_out, rb.partial, rb.ticket);
+}
+void launch_axpy_dot(const double* hprev, const double* vprev, const double* vnext, double* w, long long n, double* out, RedBuf rb, cudaStream_t st) {
+  axpy_dot_kernel<<<grid_for(n), RT, 0, st>>>(hprev, vprev, vnext, w, n, out, rb.partial, rb.ticket);
+}
+void launch_dot(const double* a, const double* b, long long n, double* out, RedBuf rb, cudaStream_t st) {
+  dot_kernel<<<grid_for(n), RT, 0, st>>>(a, b, n, out, rb.partial, rb.ticket);
+}
+void launch_scale_copy(const double* x, double* y, long long n, const double* s, int inv, int sq, cudaStream_t st) {
+  scale_copy_kernel<<<grid_for(n), RT, 0, st>>>(x, y, n, s, inv, sq);
+}
+void launch_update(double a, const double* A, double b, double* y, long long n, cudaStream_t st) {
+  update_kernel<<<grid_for(n), RT, 0, st>>>(a, A, b, y, n);
+}
+void launch_fill(double a, double* y, long long n, cudaStream_t st) { fill_kernel<<<grid_for(n), RT, 0, st>>>(a, y, n); }
+void launch_multi_axpy_plus(const double* Z, long long ldz, int nv, const double* yk, double* x, long long n, cudaStream_t st) {
+  multi_axpy_plus_kernel<<<grid_for(n), RT, 0, st>>>(Z, ldz, nv, yk, x, n);
+}
+void launch_block_jacobi(const double* binv, const double* v, double* z, long long nb, cudaStream_t st) {
+  block_jacobi_kernel<<<grid_for(6 * nb * 2), RT, 0, st>>>(binv, v, z, nb);
+}
+void launch_residual(const double* b, double* r, long long n, cudaStream_t st) { residual_kernel<<<grid_for(n * 2), RT, 0, st>>>(b, r, n); }
+void launch_givens(const GivensArgs& g, cudaStream_t st) { givens_kernel<<<1, 32, 0, st>>>(g); }
+void launch_backsolve(const double* H, int ldh, const double* s, int k, double* y, cudaStream_t st) { backsolve_kernel<<<1, 32, 0, st>>>(H, ldh, s, k, y); }
+void launch_cycle_init(const double* nrm2, double* s, int m, double* beta_out, cudaStream_t st) { cycle_init_kernel<<<1, 32, 0, st>>>(nrm2, s, m, beta_out); }
+void launch_sqrt_store(const double* nrm2, double* out, cudaStream_t st) { sqrt_store_kernel<<<1, 32, 0, st>>>(nrm2, out); }
+
+} // namespace thcm

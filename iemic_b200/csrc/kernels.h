@@ -1,0 +1,85 @@
+// kernels.h -- launch interface between the C ABI (capi.cu) and the sm_100a kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "thcm_rows.cuh"
+#include "thcm_cell.cuh"
+
+namespace thcm {
+
+struct AsmArgs {
+  Scalars S;
+  Tables T;
+  const double* x;        // stored state vector (owned cells, then halo ring)
+  const uint64_t* sig;    // per stored cell
+  const int* rowptr;      // static graph
+  const double* frc;      // forcing, already masked (rhs only)
+  double* val;            // CSR values (jacobian only)
+  double* diagB;          // mass matrix diagonal (jacobian only)
+  double* F;              // residual (rhs only)
+  SpecialRows sp;
+  int ntx, nty, ntz;
+};
+void launch_jac(const AsmArgs& a, cudaStream_t st);
+void launch_rhs(const AsmArgs& a, cudaStream_t st);
+int jac_smem_bytes();
+int rhs_smem_bytes();
+
+// integral condition (THCM.C:1006-1018): F[row] = sign * (sum_c coef[c]*x[6c+5] - corr); partial sums per block,
+// finished (after the optional allreduce) by intcond_finish.
+void launch_intcond_dot(const double* coefS, const double* x, long long ncell, double* partial /* 1 double */, cudaStream_t st);
+void launch_intcond_finish(const double* dotval, double sign, double corr, double* F, int row, int rowPfix1, int rowPfix2, cudaStream_t st);
+
+// ---- CSR SpMV (spmv.cu) ----
+struct SpmvPlan {
+  int nblocks;
+  const int* blk_row;   // device, nblocks+1 row boundaries; a block with a single "long" row is reduced block-wide
+  int nnz_cap;          // max non-zeros staged per block
+};
+void launch_spmv(const SpmvPlan& p, const int* rowptr, const int* col, const double* val, const double* x, double* y, cudaStream_t st);
+int spmv_nnz_cap();
+int spmv_rows_cap();
+
+// ---- vector / GMRES kernels (gmres.cu) ----
+struct RedBuf { double* partial; unsigned int* ticket; int nblk_max; }; // workspace for block-partial reductions
+int red_blocks();
+// out[k] = <V_k, w>, k = 0..nv-1 (V_k = V + k*ldv), deterministic two-stage reduction finished by the last block
+void launch_multi_dot(const double* V, long long ldv, int nv, const double* w, long long n, double* out, RedBuf rb, cudaStream_t st);
+// w -= sum_k h[k] V_k ; optionally hacc[k] += h[k] ; optionally nrm2_out = ||w_new||^2
+void launch_multi_axpy(const double* V, long long ldv, int nv, const double* h, double* w, long long n,
+                       double* nrm2_out, RedBuf rb, cudaStream_t st);
+// MGS fused step: if (hprev) w -= hprev[0]*vprev ; out = <w, vnext> (vnext may be null: then out = <w,w>)
+void launch_axpy_dot(const double* hprev, const double* vprev, const double* vnext, double* w, long long n, double* out, RedBuf rb, cudaStream_t st);
+void launch_dot(const double* a, const double* b, long long n, double* out, RedBuf rb, cudaStream_t st);
+// y = alpha * x with alpha = (inv ? 1/s[0] : s[0]) read on the device ; s may be sqrt'ed first (sq: s[0] holds a squared norm)
+void launch_scale_copy(const double* x, double* y, long long n, const double* s, int inv, int sq, cudaStream_t st);
+void launch_update(double a, const double* A, double b, double* y, long long n, cudaStream_t st); // y = a*A + b*y
+void launch_fill(double a, double* y, long long n, cudaStream_t st);
+// x += sum_k yk[k] * Z_k
+void launch_multi_axpy_plus(const double* Z, long long ldz, int nv, const double* yk, double* x, long long n, cudaStream_t st);
+// z = blockdiag(Binv) * v, 6x6 blocks
+void launch_block_jacobi(const double* binv, const double* v, double* z, long long nblocks, cudaStream_t st);
+// r = b - r  (r holds A x on entry)
+void launch_residual(const double* b, double* r, long long n, cudaStream_t st);
+
+// Arnoldi bookkeeping on the device (single thread): column j of H from h1 (+h2), norm from nrm2 (squared),
+// Givens rotations (GMRESSolver.H:190-200), residual estimate hist[j] = |s[j+1]| / bnorm.
+struct GivensArgs {
+  double* H; int ldh;          // (m+1) x m, column major
+  double* cs; double* sn; double* s;
+  const double* h1; const double* h2; // h2 may be null
+  const double* nrm2;          // squared norm of w (or norm if !sq)
+  int sq;
+  const double* bnorm;         // device scalar: ||b||
+  double* hist;
+  double* hnext;               // receives H[j+1][j] (the norm) for the normalisation kernel
+  int j;
+};
+void launch_givens(const GivensArgs& g, cudaStream_t st);
+// y = H(0:k,0:k)^-1 s(0:k)   (GMRESSolver::backSolve, :258-289)
+void launch_backsolve(const double* H, int ldh, const double* s, int k, double* y, cudaStream_t st);
+// beta = sqrt(nrm2) ; s[0] = beta ; s[1..m] = 0 ; bnorm keeps ||b|| (set separately)
+void launch_cycle_init(const double* nrm2, double* s, int m, double* beta_out, cudaStream_t st);
+void launch_sqrt_store(const double* nrm2, double* out, cudaStream_t st);
+
+} // namespace thcm

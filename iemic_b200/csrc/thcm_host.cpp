@@ -32,7 +32,8 @@ double bmh(double y, int ih) { return ih == 0 ? 1.0 : 1.0 + 10.0 * std::exp(-5 *
 double bmhy(double y, int ih) { return ih == 0 ? 0.0 : -10. * 10.0 * y * std::exp(-5 * y * y); }
 } // namespace
 
-Host::Host(const Config& c, const int* landm_in) : cfg(c), n(c.n), m(c.m), l(c.l) {
+Host::Host(const Config& c, const int* landm_in, int rank_, int nranks_) : cfg(c), n(c.n), m(c.m), l(c.l), rank(rank_), nranks(nranks_) {
+  if (nranks != 1) throw std::runtime_error("thcm_b200: multi-rank decomposition is not available in this build");
   if (n < 3 || m < 2 || l < 2) throw std::runtime_error("thcm_b200: grid too small (need n>=3, m>=2, l>=2)");
   ncell = (size_t)n * m * l;
   ndim = 6 * ncell;
@@ -135,9 +136,12 @@ void Host::set_landmask(const int* landm_in) {
   for (int k = 1; k <= l; k++) for (int j = 1; j <= m; j++) for (int i = 1; i <= n; i++)
     if (L(i, j, k) == OCEAN) intcond[6 * ((((size_t)k - 1) * m + (j - 1)) * n + (i - 1)) + SS - 1] = std::cos(y[j]) * dfzT[k];
   build_signatures();
+  build_tables();   // also fills the storage descriptors in S
   build_graph();
-  build_tables();
   build_forcing();
+  owns_rowintcon = rowintcon >= 0; rowintcon_local = rowintcon; rowPfix1_local = rowPfix1; rowPfix2_local = rowPfix2;
+  gid.resize(ndim);
+  for (size_t q = 0; q < ndim; q++) gid[q] = (long long)q;
   version++; mask_version++;
 }
 
@@ -304,6 +308,7 @@ void Host::build_tables() {
   S.vmix_on = cfg.vmix >= 1;
   S.rho_mixing = (cfg.rho_mixing != 0) && (xes == 0.0);
   S.dz = dz;
+  S.io0 = 1; S.jo0 = 1; S.nloc = n; S.mloc = m; S.nown = (long long)ncell;
 }
 
 namespace {

@@ -34,7 +34,9 @@ enum { P_AL_T = 1, P_RAYL, P_EK_V, P_EK_H, P_ROSB, P_MIXP, P_RESC, P_SPL1, P_HMT
 
 class Host {
  public:
-  Host(const Config& cfg, const int* landm_in); // throws std::runtime_error on unsupported configurations
+  // rank/nranks select one block of the 2-D decomposition (TRIOS::Domain::Decomp2D); throws std::runtime_error on
+  // unsupported configurations
+  Host(const Config& cfg, const int* landm_in, int rank = 0, int nranks = 1);
   void set_par(int idx1, double value);          // setparcs (usrc.F90:163-181): recomputes forcing + tables
   double get_par(int idx1) const { return (idx1 >= 1 && idx1 <= NPAR) ? par[idx1] : 0.0; }
   void set_landmask(const int* landm_in);        // set_landmask (usrc.F90:336-395)
@@ -56,6 +58,15 @@ class Host {
   double intCorrection;
   uint64_t version;             // bumped whenever tables/forcing change (device copies refresh lazily)
   uint64_t mask_version;
+
+  // ---- decomposition (single block until dist_setup() is called) ----
+  int rank = 0, nranks = 1, npN = 1, npM = 1;
+  bool owns_rowintcon = false;
+  int rowintcon_local = -1, rowPfix1_local = -1, rowPfix2_local = -1;
+  std::vector<long long> gid;   // global unknown index of every stored vector entry (owned rows, then halo ring; -1 unused)
+  size_t nrows_local() const { return 6 * (size_t)S.nown; }
+  size_t nvec_local() const { return gid.size(); }
+  double intcond_col(int col) const { return intcond[(size_t)col]; } // coefficient of stored column `col`
 
   Tables tables(const double* base) const; // pointers into a (host or device) copy of `tab`
   inline int lm(int i, int j, int k) const { return landm[(size_t)i + (size_t)(n + 2) * (j + (size_t)(m + 2) * k)]; }

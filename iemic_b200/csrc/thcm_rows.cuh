@@ -57,6 +57,11 @@ struct Scalars {
   int vmix_on;                 // vmix_flag>=1 and kvc path supported
   int rho_mixing;              // rho_mixing .and. xes==0                       (mix_imp.f:516)
   double dz;
+  // storage of this rank's sub-domain (TRIOS::Domain block, TRIOS_Domain.C:81-195): owned cells
+  // io0..io0+nloc-1 x jo0..jo0+mloc-1 (global Fortran indices) x all levels, followed by one ring of
+  // halo cells per level.  Single GPU: io0=jo0=1, nloc=n, mloc=m and the ring is never addressed.
+  int io0, jo0, nloc, mloc;
+  long long nown;              // nloc*mloc*l
 };
 // Tables indexed by the Fortran index (j in 0..m+1, k in 0..l); all double, one contiguous block.
 struct Tables {

@@ -1,0 +1,146 @@
+/* iemic_b200.h -- C ABI of the B200-native I-EMIC hot path (libiemic_b200.so).
+ *
+ * Plain C: pointers, sizes and scalars only; no torch, Epetra or CUDA types in any signature (streams and
+ * NCCL ids cross as void* / byte arrays).  Every function returns 0 on success and a negative code on
+ * error; it never aborts the process, so Continuation::reset() (src/continuation/Continuation.H:198-214 of
+ * the reference) keeps working.  The message of the last error on the calling thread is returned by
+ * iemic_b200_last_error().
+ *
+ * Which reference interface each entry point replaces (paths relative to the reference checkout):
+ *
+ *   thcm_b200_create / _destroy        THCM::THCM + Fortran init_     src/ocean/THCM.C:176-800, src/ocean/usrc.F90:6-139
+ *   thcm_b200_set_par / _get_par       setparcs_ / getparcs_          src/ocean/usrc.F90:163-196  (THCM::setParameter, THCM.C:1883)
+ *   thcm_b200_set_landmask             set_landmask_                  src/ocean/usrc.F90:336-395
+ *   thcm_b200_rhs  (device)            THCM::evaluate(sol,rhs,false)  src/ocean/THCM.C:949-1033 -> Fortran rhs_  usrc.F90:506-586
+ *   thcm_b200_jacobian (device)        THCM::evaluate(sol,null,true)  src/ocean/THCM.C:1035-1192 -> Fortran matrix_ usrc.F90:432-504
+ *   thcm_b200_graph / _csr             THCM::CreateMaximalGraph       src/ocean/THCM.C:2241-2539; THCM::getJacobian THCM.H:146
+ *   thcm_b200_diagB                    THCM::DiagB (localDiagB_)      src/ocean/THCM.C:1150-1153, assemble.F90:18-54
+ *   thcm_b200_rhs_host / _jacobian_host  the same two calls with HOST buffers (what Ocean::computeRHS /
+ *                                      Ocean::computeJacobian do with Epetra vectors, src/ocean/Ocean.C:1267-1300)
+ *   thcm_b200_spmv (device) / _spmv_host  Epetra_CrsMatrix::Apply on the Jacobian: Ocean::applyMatrix src/ocean/Ocean.C:1352-1357
+ *   thcm_b200_set_values               Epetra_CrsMatrix::ReplaceMyValues (load a matrix with the same graph)
+ *   gmres_b200_solve (device) / _host  GMRESSolver<Model,VectorPtr>::solve  src/gmressolver/GMRESSolver.H:81-255
+ *                                      (Ocean::solve, src/ocean/Ocean.C:1060-1138, is the live caller of the same job)
+ *   vec_b200_*                         the Epetra_Vector subset Continuation/GMRESSolver use (Update, Dot, Norm2, Scale,
+ *                                      PutScalar): src/continuation/ContinuationDecl.H:15-46, src/gmressolver/GMRESSolverDecl.H:7-16
+ *   thcm_b200_comm_*                   TRIOS::Domain (Decomp2D, ghosted maps, Import/Export)  src/trios/TRIOS_Domain.C:81-195, 517-664
+ *
+ * Layout conventions (identical to the reference, src/trios/THCMdefs.H:22-23, src/ocean/matetc.F90:123-144):
+ *   unknown index (0-based) = 6*((k*m + j)*n + i) + var,  var = 0..5 for u,v,w,p,T,S, i fastest, k=0 the bottom layer;
+ *   land mask: int[(n+2)(m+2)(l+2)], i fastest, border ring included, 0 ocean / 1 land / 3 periodic (par.F90:78-81);
+ *   CSR: 0-based int32 rowptr/col, fp64 values, columns sorted inside each row, static CreateMaximalGraph pattern.
+ * All arithmetic is fp64.
+ */
+#ifndef IEMIC_B200_H
+#define IEMIC_B200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct thcm_b200 thcm_b200_t;
+
+/* Same fields, in the same order, as the argument list of Fortran init (usrc.F90:6-139) and the "THCM"
+ * parameter list consumed at THCM.C:189-268.  Angles in radians. */
+typedef struct {
+  int n, m, l;
+  double xmin, xmax, ymin, ymax;
+  int periodic;
+  double hdim, qz;
+  double alphaT, alphaS;
+  int ih, vmix, tap, rho_mixing, coriolis_on, forcing_type;
+  int tres, sres, iza, ite, its;
+  int coupled_T, coupled_S;
+  int int_sign;             /* "Salinity Integral Sign" */
+  int intcond_i, intcond_j; /* "Integral row coordinate i/j", 0-based, -1 = last */
+  int fix_pressure_points;
+} thcm_b200_config;
+
+enum { IEMIC_B200_OK = 0, IEMIC_B200_EINVAL = -1, IEMIC_B200_ECUDA = -2, IEMIC_B200_ENOTSUP = -3, IEMIC_B200_ENCCL = -4 };
+enum { GMRES_B200_MGS = 0, GMRES_B200_CGS2 = 1 };
+enum { GMRES_B200_PREC_NONE = 0, GMRES_B200_PREC_BLOCKJACOBI = 1 };
+
+const char* iemic_b200_last_error(void);
+const char* iemic_b200_version(void);
+int iemic_b200_device_count(void);
+
+/* ---- model handle (one per GPU / per process, like the THCM singleton, THCM.H:76-83) ---- */
+int thcm_b200_create(const thcm_b200_config* cfg, const int* landm, thcm_b200_t** out);
+/* Distributed variant: rank `rank` of `nranks` owns one block of the reference's 2-D lon x lat decomposition
+ * (TRIOS::Domain::Decomp2D).  nccl_id = the 128-byte ncclUniqueId made by thcm_b200_comm_unique_id on rank 0
+ * and distributed by the host program (MPI_Bcast / torch.distributed); NULL with nranks==1. */
+int thcm_b200_create_dist(const thcm_b200_config* cfg, const int* landm, int rank, int nranks,
+                          const void* nccl_id, thcm_b200_t** out);
+int thcm_b200_comm_unique_id(void* nccl_id_out /* 128 bytes */);
+int thcm_b200_destroy(thcm_b200_t* h);
+int thcm_b200_set_stream(thcm_b200_t* h, void* cuda_stream);
+int thcm_b200_sync(thcm_b200_t* h);
+
+int thcm_b200_set_par(thcm_b200_t* h, int idx1, double value);
+int thcm_b200_get_par(thcm_b200_t* h, int idx1, double* value);
+int thcm_b200_set_landmask(thcm_b200_t* h, const int* landm);
+int thcm_b200_set_intcond_correction(thcm_b200_t* h, double corr); /* THCM.C:1013 intCorrection_ */
+
+/* sizes: local (this rank's) rows, stored vector length incl. halo cells, non-zeros; global rows */
+int thcm_b200_sizes(thcm_b200_t* h, int64_t* nrows_local, int64_t* nvec_local, int64_t* nnz_local, int64_t* nrows_global);
+/* decomposition of this rank: owned block in global 0-based cell coordinates and the process grid */
+int thcm_b200_block(thcm_b200_t* h, int* i0, int* j0, int* nloc, int* mloc, int* npN, int* npM);
+/* global unknown index of every entry of a stored vector (owned rows first, then halo cells; -1 = unused halo slot) */
+int thcm_b200_global_ids(thcm_b200_t* h, int64_t* gid /* nvec_local */);
+
+/* ---- assembly ---- */
+int thcm_b200_rhs(thcm_b200_t* h, const double* d_x, double* d_F);   /* device pointers; d_x has nvec_local entries */
+int thcm_b200_jacobian(thcm_b200_t* h, const double* d_x);            /* fills the handle's CSR values and diag(B) */
+int thcm_b200_halo_exchange(thcm_b200_t* h, double* d_x);             /* fills the halo part of a stored vector (no-op on 1 GPU) */
+int thcm_b200_csr(thcm_b200_t* h, const int** d_rowptr, const int** d_col, double** d_val, const double** d_diagB);
+int thcm_b200_graph_host(thcm_b200_t* h, int* rowptr, int* col);      /* host copies of the static graph */
+int thcm_b200_values_host(thcm_b200_t* h, double* val, double* diagB);
+int thcm_b200_set_values_host(thcm_b200_t* h, const double* val);
+int thcm_b200_forcing_host(thcm_b200_t* h, double* frc);
+int thcm_b200_intcond_host(thcm_b200_t* h, double* coeff, int* rowintcon);
+/* host-buffer entry points: what the reference's Ocean::computeRHS / computeJacobian do on Epetra vectors */
+int thcm_b200_rhs_host(thcm_b200_t* h, const double* x, double* F);
+int thcm_b200_jacobian_host(thcm_b200_t* h, const double* x, double* val /* may be NULL */, double* diagB /* may be NULL */);
+
+/* ---- sparse matrix-vector product y = J x on the handle's CSR ---- */
+int thcm_b200_spmv(thcm_b200_t* h, double* d_x /* halo part is overwritten when nranks>1 */, double* d_y);
+int thcm_b200_spmv_host(thcm_b200_t* h, const double* x, double* y);
+
+/* ---- vector kernels (Epetra_Vector subset): all device pointers, length = nrows_local, results global ---- */
+int vec_b200_dot(thcm_b200_t* h, const double* d_a, const double* d_b, double* result);
+int vec_b200_norm2(thcm_b200_t* h, const double* d_a, double* result);
+int vec_b200_update(thcm_b200_t* h, double a, const double* d_A, double b, double* d_this); /* this = a*A + b*this */
+int vec_b200_scale(thcm_b200_t* h, double a, double* d_this);
+int vec_b200_putscalar(thcm_b200_t* h, double a, double* d_this);
+
+/* ---- GMRES(m) on the handle's Jacobian (GMRESSolver.H:81-255) ----
+ * ortho: GMRES_B200_MGS reproduces the reference's modified Gram-Schmidt loop (:177-181); GMRES_B200_CGS2 is the
+ * fused two-pass classical Gram-Schmidt.  prec: right (flexible) preconditioner; BLOCKJACOBI takes nrows_local/6
+ * inverted 6x6 blocks, row-major, in d_blockinv.  hist[it] receives resid_ after inner iteration it
+ * (length >= maxit+1).  check_every: 1 tests convergence every iteration like the reference; 0 never leaves the
+ * device until the cycle ends (fixed iteration count).  Return value: 0 converged, 1 not converged (like solve()). */
+int gmres_b200_solve(thcm_b200_t* h, const double* d_b, double* d_x, int m, int maxit, double tol,
+                     int ortho, int prec, const double* d_blockinv, int check_every,
+                     double* hist, int* iters);
+int gmres_b200_solve_host(thcm_b200_t* h, const double* b, double* x, int m, int maxit, double tol,
+                          int ortho, int prec, const double* blockinv, int check_every,
+                          double* hist, int* iters);
+
+/* ---- instrumentation: number of kernels this handle launched since creation; device time helpers ---- */
+int thcm_b200_launch_count(thcm_b200_t* h, int64_t* launches);
+/* average device time (ms) of the last timed kernel groups, measured with CUDA events on the handle's stream:
+ * which = 0 rhs, 1 jacobian, 2 spmv, 3 orthogonalisation (per Arnoldi step), accumulated since _timing_reset */
+int thcm_b200_timing_enable(thcm_b200_t* h, int on);
+int thcm_b200_timing_reset(thcm_b200_t* h);
+int thcm_b200_timing_get(thcm_b200_t* h, int which, double* total_ms, int64_t* count);
+
+/* ---- plain device-memory helpers for hosts without their own allocator ---- */
+int iemic_b200_malloc(void** d_ptr, int64_t bytes);
+int iemic_b200_free(void* d_ptr);
+int iemic_b200_memcpy_h2d(void* d_dst, const void* src, int64_t bytes);
+int iemic_b200_memcpy_d2h(void* dst, const void* d_src, int64_t bytes);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

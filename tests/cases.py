@@ -1,0 +1,64 @@
+"""Shared parity cases: (name, config dict, mask, starting parameters)."""
+import numpy as np
+
+from iemic_b200 import grids
+
+
+def _apply(obj, pars):
+    for k, v in pars.items():
+        obj.set_par(k, v) if hasattr(obj, "set_par") else obj.setPar(k, v)
+
+
+def case(name):
+    g = grids
+    if name == "natl8":        # test/ocean: 8x8x4 North Atlantic box, mask_natl8, SRES=0 (integral condition)
+        cfg = g.default_config(8, 8, 4, sres=0)
+        return cfg, g.fixture_mask("mask_natl8"), dict(COMB=0.1, SALT=1.0, WIND=1.0, TEMP=10.0)
+    if name == "natl8_sres1":
+        cfg = g.default_config(8, 8, 4, sres=1)
+        return cfg, g.fixture_mask("mask_natl8"), dict(COMB=0.1, SALT=1.0, WIND=1.0, TEMP=10.0)
+    if name == "test6x6x4":    # test/matrix mask
+        cfg = g.default_config(6, 6, 4, xmin=286, xmax=350, ymin=10, ymax=74, periodic=False)
+        return cfg, g.fixture_mask("test6x6x4"), dict(COMB=0.1, SALT=1.0, WIND=1.0, TEMP=10.0)
+    if name == "2dmoc":        # test/2dmoc: 3x6x6 periodic
+        cfg = g.moc2d_config(3, 6, 6)
+        return cfg, g.no_land_mask(3, 6, 6, True), dict(g.STARTING_PARS["2dmoc"], COMB=0.5, SALT=0.2)
+    if name == "2dmoc_run":    # run/2dmoc: 4x32x16
+        cfg = g.moc2d_config(4, 32, 16)
+        return cfg, g.no_land_mask(4, 32, 16, True), dict(g.STARTING_PARS["2dmoc"], COMB=0.5, SALT=0.2)
+    if name == "rand_periodic":
+        cfg = g.global_config(37, 11, 7, ymin=-60, ymax=60)
+        return cfg, g.random_mask(37, 11, 7, True, 5), dict(g.STARTING_PARS["global"])
+    if name == "rand_box":
+        cfg = g.default_config(35, 9, 6, ymin=-40, ymax=50, qz=1.8)
+        return cfg, g.random_mask(35, 9, 6, False, 7), dict(g.STARTING_PARS["global"])
+    if name == "rand_fixp":    # pressure points fixed + rho mixing
+        cfg = g.default_config(12, 7, 5, fix_pressure_points=1, rho_mixing=1)
+        return cfg, g.random_mask(12, 7, 5, False, 9, land_frac=0.1), dict(g.STARTING_PARS["global"])
+    if name == "global4":      # BASELINE config 2: global 4 degree, 96x38x12
+        cfg = g.global_config(96, 38, 12)
+        return cfg, g.synthetic_mask(96, 38, 12), dict(g.STARTING_PARS["global"])
+    if name == "coupled4":     # BASELINE config 3 (ocean block): Coupled Temperature=1, qz=1.5
+        cfg = g.global_config(96, 38, 12, qz=1.5, coupled_T=1)
+        return cfg, g.synthetic_mask(96, 38, 12), dict(g.STARTING_PARS["global"])
+    if name == "global_half":  # 48x19x12 sweep point
+        cfg = g.global_config(48, 19, 12)
+        return cfg, g.upsample_mask(g.fixture_mask("mask_global_96x38x12"), 48, 19, 12), dict(g.STARTING_PARS["global"])
+    raise KeyError(name)
+
+
+def state(cfg, mask, seed=1, kind="random"):
+    return grids.synthetic_state(cfg["n"], cfg["m"], cfg["l"], mask, seed=seed, kind=kind)
+
+
+def make_pair(name):
+    """(oracle, product Ocean) with identical parameters"""
+    import oracle_lib as ol
+    import iemic_b200 as ib
+    cfg, mask, pars = case(name)
+    O = ol.Oracle(cfg, mask)
+    G = ib.Ocean(cfg, mask)
+    for k, v in pars.items():
+        O.set_par(k, v)
+        G.setPar(k, v)
+    return cfg, mask, O, G
