@@ -26,14 +26,17 @@ def default_config(n, m, l, xmin=286.0, xmax=350.0, ymin=10.0, ymax=74.0, period
 
 def global_config(n, m, l, qz=2.25, **kw):
     """run/ocean/global/ocean_params.xml: periodic globe, 85.5S-85.5N, 5000 m, stretched grid."""
-    return default_config(n, m, l, xmin=0.0, xmax=360.0, ymin=-85.5, ymax=85.5, periodic=True, hdim=5000.0, qz=qz, **kw)
+    d = dict(xmin=0.0, xmax=360.0, ymin=-85.5, ymax=85.5, periodic=True, hdim=5000.0, qz=qz)
+    d.update(kw)
+    return default_config(n, m, l, **d)
 
 
 def moc2d_config(n=3, m=6, l=6, **kw):
     """test/2dmoc/ocean_params.xml (run/2dmoc uses 4x32x16): periodic lat-depth box, no Coriolis, forcing type 1,
     salinity flux forcing with the integral condition."""
-    return default_config(n, m, l, xmin=286.0, xmax=350.0, ymin=-60.0, ymax=60.0, periodic=True, hdim=4000.0, qz=1.0,
-                          coriolis_on=0, forcing_type=1, sres=0, **kw)
+    d = dict(xmin=286.0, xmax=350.0, ymin=-60.0, ymax=60.0, periodic=True, hdim=4000.0, qz=1.0, coriolis_on=0, forcing_type=1, sres=0)
+    d.update(kw)
+    return default_config(n, m, l, **d)
 
 
 # parameters set by the "Starting Parameters" lists
