@@ -1,6 +1,7 @@
 // thcm_host.cpp -- see thcm_host.h.  Compiled by the host compiler with -ffp-contract=off so that the
 // coefficient tables carry exactly the roundings of the reference's (FMA-free) Fortran expressions.
 #include "thcm_host.h"
+#include "thcm_stage.cuh"
 #include <cmath>
 #include <cstring>
 #include <stdexcept>
@@ -33,16 +34,129 @@ double bmhy(double y, int ih) { return ih == 0 ? 0.0 : -10. * 10.0 * y * std::ex
 } // namespace
 
 Host::Host(const Config& c, const int* landm_in, int rank_, int nranks_) : cfg(c), n(c.n), m(c.m), l(c.l), rank(rank_), nranks(nranks_) {
-  if (nranks != 1) throw std::runtime_error("thcm_b200: multi-rank decomposition is not available in this build");
   if (n < 3 || m < 2 || l < 2) throw std::runtime_error("thcm_b200: grid too small (need n>=3, m>=2, l>=2)");
+  if (nranks < 1 || rank < 0 || rank >= nranks) throw std::runtime_error("thcm_b200: bad rank / nranks");
   ncell = (size_t)n * m * l;
   ndim = 6 * ncell;
-  if (105ull * ncell > 0x7fffffffull) throw std::runtime_error("thcm_b200: grid too large for 32-bit CSR offsets");
+  decompose();
+  if (105ull * (size_t)nloc * mloc * l > 0x7fffffffull) throw std::runtime_error("thcm_b200: sub-domain too large for 32-bit CSR offsets");
+  if (nranks > 1 && cfg.sres == 0) throw std::runtime_error("thcm_b200: the dense salinity-integral row (SRES=0) is only supported on a single GPU");
   version = 1; mask_version = 0; intCorrection = 0.0;
   make_grid();
   stpnt();
   check_supported();
   set_landmask(landm_in); // signatures, graph, tables, forcing
+}
+
+// TRIOS::Domain::Decomp2D (TRIOS_Domain.C:81-153): factor nranks = npN*npM, row-major rank grid, remainders to the first ranks
+void Host::decompose() {
+  int t1 = nranks, t2 = 1;
+  npM = t1; npN = t2;
+  double r_min = 100;
+  while (t1 > 0) {
+    t2 = nranks / t1;
+    double r = std::abs(m / t1 - n / t2);
+    if (t1 * t2 == nranks && r <= r_min) { r_min = r; npM = t1; npN = t2; }
+    t1--;
+  }
+  pidN = rank % npN; pidM = (rank - pidN) / npN;
+  mloc = m / npM; nloc = n / npN;
+  int Moff = pidM * (m / npM), Noff = pidN * (n / npN);
+  const int remM = m % npM, remN = n % npN;
+  if (pidM < remM) mloc++;
+  if (pidN < remN) nloc++;
+  Moff += std::min(remM, pidM); Noff += std::min(remN, pidN);
+  io0 = Noff + 1; jo0 = Moff + 1;
+  if (nloc < 2 || mloc < 2) throw std::runtime_error("thcm_b200: sub-domain smaller than 2x2 columns");
+  if (npN > 1 && nloc > n - 2) throw std::runtime_error("thcm_b200: too few columns per rank for the periodic halo");
+}
+
+namespace {
+struct Block { int io0, jo0, nloc, mloc; };
+// block of rank r (TRIOS_Domain.C:120-153)
+Block block_of(int n, int m, int npN, int npM, int r) {
+  const int pN = r % npN, pM = (r - pN) / npN;
+  Block b;
+  b.mloc = m / npM; b.nloc = n / npN;
+  int Moff = pM * (m / npM), Noff = pN * (n / npN);
+  const int remM = m % npM, remN = n % npN;
+  if (pM < remM) b.mloc++;
+  if (pN < remN) b.nloc++;
+  Moff += std::min(remM, pM); Noff += std::min(remN, pN);
+  b.io0 = Noff + 1; b.jo0 = Moff + 1;
+  return b;
+}
+// global (fi,fj,fk) of stored cell c of block b; false for an unused ring slot
+bool stored_cell_of(const Block& b, int n, int m, int l, bool wrap, size_t c, int& fi, int& fj, int& fk) {
+  const size_t nown = (size_t)b.nloc * b.mloc * l;
+  int li, lj;
+  if (c < nown) {
+    li = (int)(c % b.nloc); lj = (int)((c / b.nloc) % b.mloc); fk = (int)(c / ((size_t)b.nloc * b.mloc)) + 1;
+  } else {
+    const int R = 2 * (b.nloc + 2) + 2 * b.mloc;
+    const size_t q = c - nown;
+    fk = (int)(q / R) + 1;
+    const int r = (int)(q % R);
+    if (r < b.nloc + 2) { lj = -1; li = r - 1; }
+    else if (r < 2 * (b.nloc + 2)) { lj = b.mloc; li = r - (b.nloc + 2) - 1; }
+    else if (r < 2 * (b.nloc + 2) + b.mloc) { li = -1; lj = r - 2 * (b.nloc + 2); }
+    else { li = b.nloc; lj = r - 2 * (b.nloc + 2) - b.mloc; }
+  }
+  fi = b.io0 + li; fj = b.jo0 + lj;
+  if (fj < 1 || fj > m) return false;
+  if (fi < 1 || fi > n) {
+    if (!wrap) return false; // with one rank in x the kernels wrap by themselves
+    fi = fi < 1 ? fi + n : fi - n;
+  }
+  return true;
+}
+} // namespace
+
+bool Host::stored_cell(size_t c, int& fi, int& fj, int& fk) const {
+  Block b{io0, jo0, nloc, mloc};
+  return stored_cell_of(b, n, m, l, cfg.periodic && npN > 1, c, fi, fj, fk);
+}
+
+std::vector<Host::HaloPeer> Host::halo_plan() const {
+  std::vector<HaloPeer> plan;
+  if (nranks == 1) return plan;
+  const bool wrap = cfg.periodic && npN > 1;
+  const Block me{io0, jo0, nloc, mloc};
+  auto owner = [&](int fi, int fj) {
+    for (int r = 0; r < nranks; r++) {
+      Block b = block_of(n, m, npN, npM, r);
+      if (fi >= b.io0 && fi < b.io0 + b.nloc && fj >= b.jo0 && fj < b.jo0 + b.mloc) return r;
+    }
+    return -1;
+  };
+  std::vector<HaloPeer> byrank(nranks);
+  for (int r = 0; r < nranks; r++) byrank[r].rank = r;
+  Scalars Sm; std::memset(&Sm, 0, sizeof(Sm));
+  Sm.n = n; Sm.m = m; Sm.l = l; Sm.periodic = cfg.periodic != 0; Sm.io0 = io0; Sm.jo0 = jo0; Sm.nloc = nloc; Sm.mloc = mloc; Sm.nown = (long long)nloc * mloc * l;
+  // what I receive: my ring cells, in my ring order
+  {
+    const size_t nown = (size_t)nloc * mloc * l, R = 2 * (nloc + 2) + 2 * mloc;
+    for (size_t c = nown; c < nown + R * l; c++) {
+      int fi, fj, fk;
+      if (!stored_cell_of(me, n, m, l, wrap, c, fi, fj, fk)) continue;
+      int o = owner(fi, fj);
+      if (o >= 0 && o != rank) byrank[o].recv_cells.push_back((int)c);
+      else if (o == rank) byrank[o].recv_cells.push_back((int)c); // periodic image of my own cell (npN == 2 corner cases)
+    }
+  }
+  // what I send: for every other rank, its ring cells that I own, in ITS ring order
+  for (int r = 0; r < nranks; r++) {
+    Block b = block_of(n, m, npN, npM, r);
+    const size_t nown = (size_t)b.nloc * b.mloc * l, R = 2 * (b.nloc + 2) + 2 * b.mloc;
+    for (size_t c = nown; c < nown + R * l; c++) {
+      int fi, fj, fk;
+      if (!stored_cell_of(b, n, m, l, wrap, c, fi, fj, fk)) continue;
+      if (fi >= io0 && fi < io0 + nloc && fj >= jo0 && fj < jo0 + mloc) byrank[r].send_cells.push_back((int)cell_index(Sm, fi, fj, fk));
+    }
+  }
+  for (int r = 0; r < nranks; r++)
+    if (!byrank[r].send_cells.empty() || !byrank[r].recv_cells.empty()) plan.push_back(byrank[r]);
+  return plan;
 }
 
 // grid.F90:2-60
@@ -119,38 +233,55 @@ void Host::set_landmask(const int* landm_in) {
   for (int j = 0; j <= m + 1; j++) for (int i = 0; i <= n + 1; i++) { L(i, j, 0) = LAND; L(i, j, l + 1) = LAND; }
   for (int k = 1; k <= l; k++) for (int j = 1; j <= m; j++) for (int i = 1; i <= n; i++)
     if (L(i, j, k) != OCEAN && L(i, j, k) != LAND) throw std::runtime_error("thcm_b200: interior land mask values must be 0 (ocean) or 1 (land)");
+  // storage descriptors first: everything below indexes through cell_index()
+  std::memset(&S, 0, sizeof(S));
+  S.n = n; S.m = m; S.l = l; S.periodic = cfg.periodic != 0;
+  S.io0 = io0; S.jo0 = jo0; S.nloc = nloc; S.mloc = mloc; S.nown = (long long)nloc * mloc * l;
+  const size_t nstored = (size_t)S.nown + (nranks > 1 ? (size_t)l * ring_size(S) : 0);
+  auto owned = [&](int gi, int gj) { return gi >= io0 && gi < io0 + nloc && gj >= jo0 && gj < jo0 + mloc; };
+  auto lrow = [&](int gi, int gj, int gk, int X) { return (int)(6 * cell_index(S, gi, gj, gk)) + X - 1; };
   // THCM.C:647-704 integral condition row
-  rowintcon = -1;
+  rowintcon = -1; rowintcon_local = -1; owns_rowintcon = false;
   if (cfg.sres == 0) {
     int Nic = cfg.intcond_i == -1 ? n - 1 : cfg.intcond_i, Mic = cfg.intcond_j == -1 ? m - 1 : cfg.intcond_j;
     if (Nic < 0 || Nic >= n || Mic < 0 || Mic >= m || L(Nic + 1, Mic + 1, l) != OCEAN)
       throw std::runtime_error("thcm_b200: integral row coordinates give a land point"); // THCM.C:678-682
     rowintcon = 6 * (((l - 1) * m + Mic) * n + Nic) + SS - 1;
+    if (owned(Nic + 1, Mic + 1)) { owns_rowintcon = true; rowintcon_local = lrow(Nic + 1, Mic + 1, l, SS); }
   }
+  rowPfix1 = -1; rowPfix2 = -1; rowPfix1_local = -1; rowPfix2_local = -1;
   if (cfg.fix_pressure_points) { // THCM.C:763-772
     rowPfix1 = 6 * (((l - 1) * m + (m - 1)) * n + (n - 1)) + PP - 1;
     rowPfix2 = 6 * (((l - 1) * m + (m - 1)) * n + (n - 2)) + PP - 1;
-  } else { rowPfix1 = -1; rowPfix2 = -1; }
-  // thcm_utils.F90:285-323
-  intcond.assign(ndim, 0.0);
-  for (int k = 1; k <= l; k++) for (int j = 1; j <= m; j++) for (int i = 1; i <= n; i++)
-    if (L(i, j, k) == OCEAN) intcond[6 * ((((size_t)k - 1) * m + (j - 1)) * n + (i - 1)) + SS - 1] = std::cos(y[j]) * dfzT[k];
+    if (owned(n, m)) rowPfix1_local = lrow(n, m, l, PP);
+    if (owned(n - 1, m)) rowPfix2_local = lrow(n - 1, m, l, PP);
+  }
+  // thcm_utils.F90:285-323: coefficient of every stored S dof
+  intcond.assign(6 * nstored, 0.0);
+  gid.assign(6 * nstored, -1);
+  for (size_t c = 0; c < nstored; c++) {
+    int fi, fj, fk;
+    if (!stored_cell(c, fi, fj, fk)) continue;
+    const long long g = 6 * ((((long long)fk - 1) * m + (fj - 1)) * n + (fi - 1));
+    for (int q = 0; q < 6; q++) gid[6 * c + q] = g + q;
+    if (L(fi, fj, fk) == OCEAN) intcond[6 * c + SS - 1] = std::cos(y[fj]) * dfzT[fk];
+  }
   build_signatures();
-  build_tables();   // also fills the storage descriptors in S
+  build_tables();
   build_graph();
   build_forcing();
-  owns_rowintcon = rowintcon >= 0; rowintcon_local = rowintcon; rowPfix1_local = rowPfix1; rowPfix2_local = rowPfix2;
-  gid.resize(ndim);
-  for (size_t q = 0; q < ndim; q++) gid[q] = (long long)q;
   version++; mask_version++;
 }
 
 void Host::build_signatures() {
-  sig.assign(ncell, 0);
+  const size_t nstored = gid.size() / 6;
+  sig.assign(nstored, 0);
   const bool per = cfg.periodic != 0;
   auto isLand = [&](int i, int j, int k) { return lm(i, j, k) == LAND; };
   auto isoc = [&](int i, int j, int k) { int v = lm(i, j, k); return v == OCEAN || v == PERIO; };
-  for (int k = 1; k <= l; k++) for (int j = 1; j <= m; j++) for (int i = 1; i <= n; i++) {
+  for (size_t c = 0; c < nstored; c++) {
+    int i, j, k;
+    if (!stored_cell(c, i, j, k)) continue;
     uint64_t g = 0;
     for (int s = 1; s <= 27; s++)
       if (isLand(i + slot_di(s), j + slot_dj(s), k + slot_dk(s))) g |= 1ull << (s - 1);
@@ -179,7 +310,7 @@ void Host::build_signatures() {
     if (isoc(i, j, k) && isoc(i, j, k - 1)) g |= 1ull << SIG_FACE_DN;
     if (!isLand(i + 1, j, k)) g |= 1ull << SIG_BU;
     if (!isLand(i, j + 1, k)) g |= 1ull << SIG_BV;
-    sig[(((size_t)k - 1) * m + (j - 1)) * n + (i - 1)] = g;
+    sig[c] = g;
   }
 }
 
@@ -291,6 +422,7 @@ void Host::build_tables() {
 
   std::memset(&S, 0, sizeof(S));
   S.n = n; S.m = m; S.l = l; S.periodic = cfg.periodic != 0;
+  S.io0 = io0; S.jo0 = jo0; S.nloc = nloc; S.mloc = mloc; S.nown = (long long)nloc * mloc * l;
   S.epsr = par[P_ROSB];
   S.w_tt = -Ra * (1. + xes * alpt1) * 1.0 / 2.;   // Al(:,WW,TT) = -Ra*(1.+xes*alpt1)*tbc/2.
   S.w_ss = lambda * Ra * 1.0 / 2.;                // Al(:,WW,SS) = lambda*Ra*tbc/2.
@@ -308,7 +440,6 @@ void Host::build_tables() {
   S.vmix_on = cfg.vmix >= 1;
   S.rho_mixing = (cfg.rho_mixing != 0) && (xes == 0.0);
   S.dz = dz;
-  S.io0 = 1; S.jo0 = 1; S.nloc = n; S.mloc = m; S.nown = (long long)ncell;
 }
 
 namespace {
@@ -321,10 +452,12 @@ double wfun(double yy, int v1) {
 
 // forcing.F90:4-218 (idealized, uncoupled salinity) followed by the Frc zeroing of boundary.F90
 void Host::build_forcing() {
-  frc.assign(ndim, 0.0);
+  const size_t nrows = 6 * (size_t)S.nown;
+  frc.assign(nrows, 0.0);
   const int TRES = cfg.tres, SRES = cfg.sres;
   const double gymin = cfg.ymin, gymax = cfg.ymax;
-  auto row = [&](int i, int j, int k, int X) { return 6 * ((((size_t)k - 1) * m + (j - 1)) * n + (i - 1)) + X - 1; };
+  const int i1 = io0, i2 = io0 + nloc - 1, j1 = jo0, j2 = jo0 + mloc - 1; // owned block, global Fortran indices
+  auto row = [&](int i, int j, int k, int X) { return 6 * cell_index(S, i, j, k) + X - 1; };
   auto temfun = [&](double yy) {
     if (cfg.forcing_type == 2) return std::cos(pi * (yy - gymin) / (gymax - gymin));
     return std::cos(pi * yy / gymax) + par[P_CMPR] * std::sin(pi * yy / gymax);
@@ -334,7 +467,9 @@ void Host::build_forcing() {
     if (cfg.forcing_type == 1) return (std::cos(pi * yy / gymax) + par[P_FPER] * yy / gymax) / std::cos(yy);
     return std::cos(pi * yy / gymax) + par[P_FPER] * yy / gymax;
   };
-  auto qint = [&](const std::vector<double>& field) { // thcm_forcing_integral_, THCM.C:2704-2740
+  // thcm_forcing_integral_ (THCM.C:2704-2740): a GLOBAL surface integral; every rank holds the global mask, so it is
+  // evaluated redundantly in the reference's summation order instead of through an allreduce
+  auto qint = [&](const std::vector<double>& field) {
     double lf = 0.0, ls = 0.0;
     for (int j = 1; j <= m; j++) for (int i = 1; i <= n; i++) {
       lf = field[(size_t)(i - 1) + (size_t)n * (j - 1)] * std::cos(y[j]) * (1 - lm(i, j, l)) + lf;
@@ -343,7 +478,7 @@ void Host::build_forcing() {
     return lf / ls;
   };
   const double sigma = par[P_COMB] * par[P_WIND] * par[P_AL_T];
-  for (int j = 1; j <= m - 1; j++) for (int i = 1; i <= n; i++) {
+  for (int j = j1; j <= std::min(j2, m - 1); j++) for (int i = i1; i <= i2; i++) {
     frc[row(i, j, l, UU)] = sigma * wfun(yv[j], 1);
     frc[row(i, j, l, VV)] = sigma * wfun(yv[j], 2);
   }
@@ -353,7 +488,7 @@ void Host::build_forcing() {
   if (cfg.coupled_T == 0) {
     for (int j = 1; j <= m; j++) for (int i = 1; i <= n; i++) tatm[(size_t)(i - 1) + (size_t)n * (j - 1)] = temfun(y[j]);
     if (TRES == 0) temcor = qint(tatm);
-    for (int j = 1; j <= m; j++) for (int i = 1; i <= n; i++) frc[row(i, j, l, TT)] = etabi * (tatm[(size_t)(i - 1) + (size_t)n * (j - 1)] - temcor);
+    for (int j = j1; j <= j2; j++) for (int i = i1; i <= i2; i++) frc[row(i, j, l, TT)] = etabi * (tatm[(size_t)(i - 1) + (size_t)n * (j - 1)] - temcor);
   }
   // coupled_T == 1 with no atmosphere attached: tatm = qatm = albe = msi = 0, lvsc = 0 => Frc(TT) = par(COMB)*par(SUNP)*suno(j)*(1-albe0)
   // with the unset albe0 = 0; only meaningful once set_atmos_parameters exists, kept at 0 here.
@@ -361,13 +496,13 @@ void Host::build_forcing() {
   double salcor = 0.0, adapted_salcor = 0.0, spertcor = 0.0;
   for (int j = 1; j <= m; j++) for (int i = 1; i <= n; i++) emip[(size_t)(i - 1) + (size_t)n * (j - 1)] = salfun(y[j]) * (1 - lm(i, j, l));
   if (SRES == 0) { salcor = qint(emip); adapted_salcor = qint(zero2); spertcor = qint(zero2); }
-  for (int j = 1; j <= m; j++) for (int i = 1; i <= n; i++)
+  for (int j = j1; j <= j2; j++) for (int i = i1; i <= i2; i++)
     frc[row(i, j, l, SS)] = gamma * (1 - par[P_HMTP]) * (emip[(size_t)(i - 1) + (size_t)n * (j - 1)] - salcor) +
                             gamma * par[P_HMTP] * (0.0 - adapted_salcor) + par[P_SPER] * (1 - SRES + SRES * par[P_BIOT]) * (0.0 - spertcor);
-  for (int k = 1; k <= l - 1; k++) for (int j = 1; j <= m; j++) for (int i = 1; i <= n; i++) // internal T/S forcing is zero (THCM.C:540-544)
+  for (int k = 1; k <= l - 1; k++) for (int j = j1; j <= j2; j++) for (int i = i1; i <= i2; i++) // internal T/S forcing is zero (THCM.C:540-544)
     frc[row(i, j, k, WW)] = -par[P_COMB] * (1 - lm(i, j, k)) * par[P_RAYL] * (par[P_LAMB] * (0.0 + 0.0) / 2. - (0.0 + 0.0) / 2.);
   // rows whose forcing `boundaries` resets to zero on every call
-  for (size_t c = 0; c < ncell; c++) {
+  for (size_t c = 0; c < (size_t)S.nown; c++) {
     uint64_t g = sig[c];
     if (frc_masked<UU>(g)) frc[6 * c + 0] = 0.0;
     if (frc_masked<VV>(g)) frc[6 * c + 1] = 0.0;
@@ -379,36 +514,45 @@ void Host::build_forcing() {
 }
 
 // Static pattern of THCM::CreateMaximalGraph (THCM.C:2241-2539): generated from the same RowDef tables the
-// kernels use, so the kernels' emit order and the graph cannot disagree.
+// kernels use, so the kernels' emit order and the graph cannot disagree.  Column = stored index of the neighbour cell
+// (cell_index) * 6 + var; entry order inside a row = emit_row's order.
 template <int A> static void graph_row(const Scalars& S, const Cell& c, std::vector<int>& col) {
-  int cols[Row<A>::NE], cnt = 0;
+  int cols[Row<A>::NE], gcols[Row<A>::NE], cnt = 0;
   for (int q = 0; q < Row<A>::NE; q++) {
     int slot = RowDef<A>::e[q].slot;
-    if (slot_present(slot, S, c)) cols[cnt++] = slot_col(slot, RowDef<A>::e[q].var, S, c);
+    if (slot_present(slot, S, c)) {
+      gcols[cnt] = slot_col(slot, RowDef<A>::e[q].var, S, c);
+      int i2 = c.i + slot_di(slot), j2 = c.j + slot_dj(slot), k2 = c.k + slot_dk(slot);
+      if (S.periodic) { if (i2 == 0) i2 = S.n; else if (i2 == S.n + 1) i2 = 1; }
+      cols[cnt] = (int)(6 * cell_index(S, i2, j2, k2)) + RowDef<A>::e[q].var - 1;
+      cnt++;
+    }
   }
-  if (S.periodic && (c.i == 1 || c.i == S.n)) std::sort(cols, cols + cnt);
+  if (row_has_seam(S, c)) { // single rank in x: stored index == global index order, sort like the global graph
+    std::sort(cols, cols + cnt);
+  }
+  (void)gcols;
   col.insert(col.end(), cols, cols + cnt);
 }
 void Host::build_graph() {
-  Scalars G; std::memset(&G, 0, sizeof(G));
-  G.n = n; G.m = m; G.l = l; G.periodic = cfg.periodic != 0;
-  rowptr.assign(ndim + 1, 0);
+  const size_t nrows = 6 * (size_t)S.nown;
+  rowptr.assign(nrows + 1, 0);
   col.clear();
-  col.reserve(104 * ncell + (rowintcon >= 0 ? ncell : 0));
+  col.reserve(104 * (size_t)S.nown + (rowintcon_local >= 0 ? (size_t)S.nown : 0));
   size_t r = 0;
-  for (int k = 1; k <= l; k++) for (int j = 1; j <= m; j++) for (int i = 1; i <= n; i++) {
+  for (int k = 1; k <= l; k++) for (int j = jo0; j < jo0 + mloc; j++) for (int i = io0; i < io0 + nloc; i++) {
     Cell c{i, j, k, 0};
-    rowptr[r++] = (int)col.size(); graph_row<UU>(G, c, col);
-    rowptr[r++] = (int)col.size(); graph_row<VV>(G, c, col);
-    rowptr[r++] = (int)col.size(); graph_row<WW>(G, c, col);
-    rowptr[r++] = (int)col.size(); graph_row<PP>(G, c, col);
-    rowptr[r++] = (int)col.size(); graph_row<TT>(G, c, col);
+    rowptr[r++] = (int)col.size(); graph_row<UU>(S, c, col);
+    rowptr[r++] = (int)col.size(); graph_row<VV>(S, c, col);
+    rowptr[r++] = (int)col.size(); graph_row<WW>(S, c, col);
+    rowptr[r++] = (int)col.size(); graph_row<PP>(S, c, col);
+    rowptr[r++] = (int)col.size(); graph_row<TT>(S, c, col);
     rowptr[r++] = (int)col.size();
-    if ((int)(r - 1) == rowintcon) { // dense integral-condition row (THCM.C:2494-2513), sorted: all S dofs
-      for (size_t cc = 0; cc < ncell; cc++) col.push_back((int)(6 * cc + SS - 1));
-    } else graph_row<SS>(G, c, col);
+    if ((int)(r - 1) == rowintcon_local) { // dense integral-condition row (THCM.C:2494-2513), sorted: all S dofs
+      for (size_t cc = 0; cc < (size_t)S.nown; cc++) col.push_back((int)(6 * cc + SS - 1));
+    } else graph_row<SS>(S, c, col);
   }
-  rowptr[ndim] = (int)col.size();
+  rowptr[nrows] = (int)col.size();
 }
 
 } // namespace thcm

@@ -60,7 +60,14 @@ class Host {
   uint64_t mask_version;
 
   // ---- decomposition (single block until dist_setup() is called) ----
-  int rank = 0, nranks = 1, npN = 1, npM = 1;
+  int rank = 0, nranks = 1, npN = 1, npM = 1, pidN = 0, pidM = 0;
+  int io0 = 1, jo0 = 1, nloc = 0, mloc = 0;   // owned block: global Fortran index of its first cell, extent
+  bool stored_cell(size_t c, int& fi, int& fj, int& fk) const;
+  // halo exchange plan (the Epetra_Import of TRIOS::Domain, TRIOS_Domain.C:220-225, 517-664, as index lists):
+  // for every peer rank the owned cells to pack for it and the halo-ring cells its data lands in, both in the
+  // receiver's ring order so that the two sides agree without any handshake.
+  struct HaloPeer { int rank; std::vector<int> send_cells, recv_cells; };
+  std::vector<HaloPeer> halo_plan() const;
   bool owns_rowintcon = false;
   int rowintcon_local = -1, rowPfix1_local = -1, rowPfix2_local = -1;
   std::vector<long long> gid;   // global unknown index of every stored vector entry (owned rows, then halo ring; -1 unused)
@@ -72,6 +79,7 @@ class Host {
   inline int lm(int i, int j, int k) const { return landm[(size_t)i + (size_t)(n + 2) * (j + (size_t)(m + 2) * k)]; }
 
  private:
+  void decompose();
   void make_grid();
   void stpnt();
   void build_signatures();

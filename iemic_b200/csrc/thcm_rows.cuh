@@ -590,6 +590,11 @@ THCM_HD int slot_col(int slot, int var, const Scalars& S, const Cell& c) {
   return 6 * (((k2 - 1) * S.m + (j2 - 1)) * S.n + (i2 - 1)) + var - 1;
 }
 
+// Rows whose stencil crosses the periodic seam inside ONE rank: their stored (= global) column order differs from the
+// static (dk,dj,di,var) order and is sorted explicitly.  With several ranks in x the seam lies between ranks and the
+// static order is kept everywhere.
+THCM_HD bool row_has_seam(const Scalars& S, const Cell& c) { return S.periodic && S.nloc == S.n && (c.i == 1 || c.i == S.n); }
+
 // Au(row) = sum coA*un(jcoA) in the reference's storage order (matAvec, matetc.F90:147-166).
 // X::raw(di,dj,dk,var) returns the raw state of the neighbour cell.
 template <int A, class X> THCM_HD double row_dot(const Row<A>& r, const X& x) {
@@ -606,7 +611,7 @@ template <int A, class X> THCM_HD double row_dot(const Row<A>& r, const X& x) {
 // Store the row into the static CSR.  `out` points at the first value of this row (rowptr[row]).
 // Fast path: no periodic seam inside the stencil => the static (dk,dj,di,var) order is the column order.
 template <int A, class Out> THCM_HD void emit_row(const Row<A>& r, const Scalars& S, const Cell& c, Out out) {
-  const bool seam = S.periodic && (c.i == 1 || c.i == S.n);
+  const bool seam = row_has_seam(S, c);
   if (!seam) {
     int pos = 0;
     static_for<0, Row<A>::NE>([&](auto q) {

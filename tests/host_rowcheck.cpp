@@ -31,6 +31,24 @@ struct HostRaw { // accessor X: raw neighbour state through shift() (assemble.F9
 } // namespace
 
 extern "C" {
+void* hostcheck_create_dist(const Config* cfg, const int* landm, int rank, int nranks, char* err, int errlen) {
+  try { return new Host(*cfg, landm, rank, nranks); }
+  catch (const std::exception& e) { if (err) { strncpy(err, e.what(), errlen - 1); err[errlen - 1] = 0; } return nullptr; }
+}
+long long hostcheck_nrows(void* h) { return (long long)((Host*)h)->nrows_local(); }
+long long hostcheck_nvec(void* h) { return (long long)((Host*)h)->nvec_local(); }
+void hostcheck_gid(void* h, long long* g) { Host* H = (Host*)h; memcpy(g, H->gid.data(), sizeof(long long) * H->gid.size()); }
+void hostcheck_block(void* h, int* out) { Host* H = (Host*)h; out[0] = H->io0 - 1; out[1] = H->jo0 - 1; out[2] = H->nloc; out[3] = H->mloc; out[4] = H->npN; out[5] = H->npM; }
+int hostcheck_halo_npeers(void* h) { return (int)((Host*)h)->halo_plan().size(); }
+void hostcheck_halo_peer(void* h, int idx, int* info) {
+  auto plan = ((Host*)h)->halo_plan();
+  info[0] = plan[idx].rank; info[1] = (int)plan[idx].send_cells.size(); info[2] = (int)plan[idx].recv_cells.size();
+}
+void hostcheck_halo_lists(void* h, int idx, int* send, int* recv) {
+  auto plan = ((Host*)h)->halo_plan();
+  memcpy(send, plan[idx].send_cells.data(), sizeof(int) * plan[idx].send_cells.size());
+  memcpy(recv, plan[idx].recv_cells.data(), sizeof(int) * plan[idx].recv_cells.size());
+}
 void* hostcheck_create(const Config* cfg, const int* landm, char* err, int errlen) {
   try { return new Host(*cfg, landm); }
   catch (const std::exception& e) { if (err) { strncpy(err, e.what(), errlen - 1); err[errlen - 1] = 0; } return nullptr; }
@@ -48,17 +66,17 @@ void hostcheck_graph(void* h, int* rowptr, int* col) {
   memcpy(rowptr, H->rowptr.data(), sizeof(int) * H->rowptr.size());
   memcpy(col, H->col.data(), sizeof(int) * H->col.size());
 }
-void hostcheck_frc(void* h, double* frc) { Host* H = (Host*)h; memcpy(frc, H->frc.data(), sizeof(double) * H->ndim); }
-void hostcheck_sig(void* h, unsigned long long* sig) { Host* H = (Host*)h; memcpy(sig, H->sig.data(), 8 * H->ncell); }
-void hostcheck_intcond(void* h, double* c) { Host* H = (Host*)h; memcpy(c, H->intcond.data(), sizeof(double) * H->ndim); }
+void hostcheck_frc(void* h, double* frc) { Host* H = (Host*)h; memcpy(frc, H->frc.data(), sizeof(double) * H->frc.size()); }
+void hostcheck_sig(void* h, unsigned long long* sig) { Host* H = (Host*)h; memcpy(sig, H->sig.data(), 8 * H->sig.size()); }
+void hostcheck_intcond(void* h, double* c) { Host* H = (Host*)h; memcpy(c, H->intcond.data(), sizeof(double) * H->nrows_local()); }
 
 void hostcheck_jac(void* h, const double* x, double* val, double* diagB) {
   Host* H = (Host*)h;
   const Scalars& S = H->S;
   Tables T = H->tables(H->tab.data());
-  SpecialRows sp{H->rowintcon, H->rowPfix1, H->rowPfix2};
+  SpecialRows sp{H->owns_rowintcon ? H->rowintcon_local : -1, H->rowPfix1_local, H->rowPfix2_local};
   for (size_t q = 0; q < H->col.size(); q++) val[q] = 0.0;
-  for (int k = 1; k <= S.l; k++) for (int j = 1; j <= S.m; j++) for (int i = 1; i <= S.n; i++) {
+  for (int k = 1; k <= S.l; k++) for (int j = S.jo0; j < S.jo0 + S.mloc; j++) for (int i = S.io0; i < S.io0 + S.nloc; i++) {
     size_t ci = cell_index(S, i, j, k);
     Cell c{i, j, k, H->sig[ci]};
     HostFields f{x, H->sig.data(), &S, i, j, k};
@@ -70,8 +88,8 @@ void hostcheck_jac(void* h, const double* x, double* val, double* diagB) {
     diagB[row + 4] = jac_row<TT>(S, T, c, f, sp, row + 4, val + H->rowptr[row + 4]);
     diagB[row + 5] = jac_row<SS>(S, T, c, f, sp, row + 5, val + H->rowptr[row + 5]);
   }
-  if (H->rowintcon >= 0) { // intcond_S (THCM.C:2121-2198)
-    int r = H->rowintcon;
+  if (H->owns_rowintcon) { // intcond_S (THCM.C:2121-2198)
+    int r = H->rowintcon_local;
     for (int p = H->rowptr[r]; p < H->rowptr[r + 1]; p++) val[p] = H->cfg.int_sign * H->intcond[H->col[p]];
   }
 }
@@ -80,7 +98,7 @@ void hostcheck_rhs(void* h, const double* x, double* Fo) {
   Host* H = (Host*)h;
   const Scalars& S = H->S;
   Tables T = H->tables(H->tab.data());
-  for (int k = 1; k <= S.l; k++) for (int j = 1; j <= S.m; j++) for (int i = 1; i <= S.n; i++) {
+  for (int k = 1; k <= S.l; k++) for (int j = S.jo0; j < S.jo0 + S.mloc; j++) for (int i = S.io0; i < S.io0 + S.nloc; i++) {
     size_t ci = cell_index(S, i, j, k);
     Cell c{i, j, k, H->sig[ci]};
     HostFields f{x, H->sig.data(), &S, i, j, k};
@@ -95,12 +113,12 @@ void hostcheck_rhs(void* h, const double* x, double* Fo) {
     Fo[row + 4] = rhs_row<TT>(S, T, c, f, xr, H->frc[row + 4], mt);
     Fo[row + 5] = rhs_row<SS>(S, T, c, f, xr, H->frc[row + 5], ms);
   }
-  if (H->cfg.sres == 0 && H->rowintcon >= 0) { // THCM.C:1006-1018
+  if (H->cfg.sres == 0 && H->owns_rowintcon) { // THCM.C:1006-1018 (single rank: the dot is local)
     double d = 0.0;
-    for (size_t q = 0; q < H->ndim; q++) d += H->intcond[q] * x[q];
-    Fo[H->rowintcon] = H->cfg.int_sign * (d - H->intCorrection);
+    for (size_t q = 0; q < H->nrows_local(); q++) d += H->intcond[q] * x[q];
+    Fo[H->rowintcon_local] = H->cfg.int_sign * (d - H->intCorrection);
   }
-  if (H->rowPfix1 >= 0) Fo[H->rowPfix1] = 0.0;
-  if (H->rowPfix2 >= 0) Fo[H->rowPfix2] = 0.0;
+  if (H->rowPfix1_local >= 0) Fo[H->rowPfix1_local] = 0.0;
+  if (H->rowPfix2_local >= 0) Fo[H->rowPfix2_local] = 0.0;
 }
 }

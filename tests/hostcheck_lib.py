@@ -28,6 +28,17 @@ def lib():
         dp, ip = C.POINTER(C.c_double), C.POINTER(C.c_int)
         L.hostcheck_create.restype = C.c_void_p
         L.hostcheck_create.argtypes = [C.POINTER(Config), ip, C.c_char_p, C.c_int]
+        L.hostcheck_create_dist.restype = C.c_void_p
+        L.hostcheck_create_dist.argtypes = [C.POINTER(Config), ip, C.c_int, C.c_int, C.c_char_p, C.c_int]
+        L.hostcheck_nrows.argtypes = [C.c_void_p]
+        L.hostcheck_nrows.restype = C.c_longlong
+        L.hostcheck_nvec.argtypes = [C.c_void_p]
+        L.hostcheck_nvec.restype = C.c_longlong
+        L.hostcheck_gid.argtypes = [C.c_void_p, C.POINTER(C.c_longlong)]
+        L.hostcheck_block.argtypes = [C.c_void_p, ip]
+        L.hostcheck_halo_npeers.argtypes = [C.c_void_p]
+        L.hostcheck_halo_peer.argtypes = [C.c_void_p, C.c_int, ip]
+        L.hostcheck_halo_lists.argtypes = [C.c_void_p, C.c_int, ip, ip]
         L.hostcheck_destroy.argtypes = [C.c_void_p]
         L.hostcheck_set_par.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_char_p, C.c_int]
         L.hostcheck_get_par.argtypes = [C.c_void_p, C.c_int]
@@ -54,15 +65,37 @@ def _ip(a):
 
 
 class HostCheck:
-    def __init__(self, cfg, landm):
+    def __init__(self, cfg, landm, rank=0, nranks=1):
         self.c = Config(**cfg)
         self.landm = np.ascontiguousarray(landm, dtype=np.int32).ravel()
         err = C.create_string_buffer(512)
-        self.h = lib().hostcheck_create(C.byref(self.c), _ip(self.landm), err, 512)
+        self.h = lib().hostcheck_create_dist(C.byref(self.c), _ip(self.landm), rank, nranks, err, 512)
         if not self.h:
             raise RuntimeError(err.value.decode())
-        self.ndim = 6 * cfg["n"] * cfg["m"] * cfg["l"]
+        self.ndim = lib().hostcheck_nrows(self.h)       # local rows
+        self.nvec = lib().hostcheck_nvec(self.h)        # stored vector length (owned + halo ring)
         self._graph = None
+
+    def gid(self):
+        g = np.zeros(self.nvec, np.int64)
+        lib().hostcheck_gid(self.h, g.ctypes.data_as(C.POINTER(C.c_longlong)))
+        return g
+
+    def halo_plan(self):
+        """[(peer rank, send cell indices, recv cell indices)]"""
+        out = []
+        for q in range(lib().hostcheck_halo_npeers(self.h)):
+            info = np.zeros(3, np.int32)
+            lib().hostcheck_halo_peer(self.h, q, _ip(info))
+            send, recv = np.zeros(info[1], np.int32), np.zeros(info[2], np.int32)
+            lib().hostcheck_halo_lists(self.h, q, _ip(send), _ip(recv))
+            out.append((int(info[0]), send, recv))
+        return out
+
+    def block(self):
+        b = np.zeros(6, np.int32)
+        lib().hostcheck_block(self.h, _ip(b))
+        return tuple(int(v) for v in b)
 
     def __del__(self):
         if getattr(self, "h", None):

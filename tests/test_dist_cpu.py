@@ -1,0 +1,103 @@
+"""Domain decomposition on the CPU: every rank's host-side setup (thcm_host.cpp: Decomp2D blocks, halo ring storage,
+local graph, forcing, signatures) and the row arithmetic evaluated on its local storage must reproduce the single-domain
+oracle exactly -- the `||J*1||` rank-count invariance idiom of src/tests/test_matrix.C:148-192, sharpened to bit level.
+Also runs a real world_size-2 gloo exchange using the halo plan."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import scipy.sparse as sp
+
+import cases
+import hostcheck_lib as hl
+import oracle_lib as ol
+
+
+def _assemble(name, nranks):
+    cfg, mask, pars = cases.case(name)
+    O = ol.Oracle(cfg, mask)
+    for k, v in pars.items():
+        O.set_par(k, v)
+    x = cases.state(cfg, mask, seed=7)
+    N = O.ndim
+    F = np.full(N, np.nan)
+    B = np.full(N, np.nan)
+    rows_g, cols_g, vals_g = [], [], []
+    seen = np.zeros(N, int)
+    for r in range(nranks):
+        H = hl.HostCheck(cfg, mask, rank=r, nranks=nranks)
+        for k, v in pars.items():
+            H.set_par(k, v)
+        gid = H.gid()
+        assert np.all(gid[:H.ndim] >= 0)
+        seen[gid[:H.ndim]] += 1
+        xloc = np.where(gid >= 0, x[np.maximum(gid, 0)], 0.0)
+        Fl = H.rhs(xloc)
+        F[gid[:H.ndim]] = Fl
+        val, diagB = H.jac(xloc)
+        B[gid[:H.ndim]] = diagB
+        rp, col = H.graph()
+        lr = np.repeat(np.arange(H.ndim), np.diff(rp))
+        assert np.all(gid[col] >= 0), "a stored column points at an unused halo slot"
+        rows_g.append(gid[lr]); cols_g.append(gid[col]); vals_g.append(val)
+        frc = H.frc()
+        O.rhs(x)
+        assert np.array_equal(frc, O.frc()[gid[:H.ndim]])
+    assert np.all(seen == 1), "every global row is owned by exactly one rank"
+    rows_g, cols_g, vals_g = np.concatenate(rows_g), np.concatenate(cols_g), np.concatenate(vals_g)
+    return cfg, O, x, F, B, rows_g, cols_g, vals_g
+
+
+@pytest.mark.parametrize("name,nranks", [("rand_periodic", 2), ("rand_periodic", 4), ("rand_periodic", 8), ("rand_box", 2), ("rand_box", 6),
+                                         ("global_half", 8), ("coupled4", 4), ("natl8_sres1", 4)])
+def test_rank_pieces_reproduce_the_global_problem(name, nranks):
+    cfg, O, x, F, B, rows_g, cols_g, vals_g = _assemble(name, nranks)
+    assert np.array_equal(F, O.rhs(x))
+    vo, bo = O.jac(x)
+    assert np.array_equal(B, bo)
+    rp, col = O.graph()
+    ro = np.repeat(np.arange(O.ndim), np.diff(rp))
+    # same pattern and values: sort both by (row, col)
+    ko = np.lexsort((col, ro))
+    kg = np.lexsort((cols_g, rows_g))
+    assert rows_g.size == ro.size
+    assert np.array_equal(rows_g[kg], ro[ko]) and np.array_equal(cols_g[kg], col[ko])
+    assert np.array_equal(vals_g[kg], vo[ko])
+    # the test_matrix.C idiom
+    J = sp.csr_matrix((vals_g, (rows_g, cols_g)), shape=(O.ndim, O.ndim))
+    Jo = sp.csr_matrix((vo, col, rp), shape=(O.ndim, O.ndim))
+    assert abs(np.linalg.norm(J @ np.ones(O.ndim)) - np.linalg.norm(Jo @ np.ones(O.ndim))) < 1e-8
+
+
+def test_decomposition_matches_reference_rule():
+    from iemic_b200 import grids
+    cfg, mask, pars = cases.case("global_half")
+    for nranks in (1, 2, 4, 8):
+        npN, npM = grids.decomp2d(cfg["n"], cfg["m"], nranks)
+        cells = 0
+        for r in range(nranks):
+            H = hl.HostCheck(cfg, mask, rank=r, nranks=nranks)
+            i0, j0, nloc, mloc, pn, pm = H.block()
+            assert (pn, pm) == (npN, npM)
+            assert i0 == (r % npN) * (cfg["n"] // npN) + min(cfg["n"] % npN, r % npN)
+            cells += nloc * mloc
+        assert cells == cfg["n"] * cfg["m"]
+
+
+def test_sres0_multirank_fails_loudly():
+    cfg, mask, pars = cases.case("natl8")
+    with pytest.raises(RuntimeError):
+        hl.HostCheck(cfg, mask, rank=0, nranks=2)
+
+
+def test_gloo_world2_halo_exchange():
+    """Two real processes (gloo): exchange halos using the plan, then assemble; compared with the oracle inside the worker."""
+    here = os.path.dirname(os.path.abspath(__file__))
+    env = dict(os.environ, MASTER_ADDR="127.0.0.1", MASTER_PORT="29541")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", "29541", os.path.join(here, "dist_worker.py")]
+    r = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "rank 0 ok" in r.stdout and "rank 1 ok" in r.stdout
