@@ -11,11 +11,17 @@ struct SpecialRows { int rowintcon, rowPfix1, rowPfix2; };
 // Jacobian row A of cell c -> `out` (first stored value of the row in the static CSR), returns diag(B) entry.
 // The integral-condition row is left untouched (its dense values are static, written by jac_intcond_row).
 template <int A, class F, class Out>
-THCM_HD double jac_row(const Scalars& S, const Tables& T, const Cell& c, const F& f, const SpecialRows& sp, int row, Out out) {
+THCM_HD double jac_row(const Scalars& S, const Tables& T, const Cell& c, const F& f, const SpecialRows& sp, int row, Out out,
+                       const MixFD* fd = nullptr) {
   Row<A> r;
-  JacRow<A, F>::build(r, S, T, c, f);
-  apply_boundaries<A>(r, c.sig);
-  filter_row<A>(r);
+  if (sbit(c.sig, SIG_NOTOCEAN)) { // `boundaries` turns every row of a non-ocean cell into an identity row (boundary.F90:383-391)
+    r.clear();
+    r.template at<5, A>() = 1.0;
+  } else {
+    JacRow<A, F>::build(r, S, T, c, f, fd);
+    if ((uint32_t)c.sig != 0u) apply_boundaries<A>(r, c.sig); // bits 0..31: a land neighbour somewhere in the stencil
+    filter_row<A>(r);
+  }
   // fillcolB (assemble.F90:18-54) times "Mass" = 1 (THCM.C:1150-1153)
   double b = 0.0;
   if (!sbit(c.sig, SIG_NOTOCEAN)) {
@@ -40,9 +46,14 @@ THCM_HD double jac_row(const Scalars& S, const Tables& T, const Cell& c, const F
 template <int A, class F, class X>
 THCM_HD double rhs_row(const Scalars& S, const Tables& T, const Cell& c, const F& f, const X& x, double frc, double mixv) {
   Row<A> r;
-  RhsRow<A, F>::build(r, S, T, c, f);
-  apply_boundaries<A>(r, c.sig);
-  filter_row<A>(r);
+  if (sbit(c.sig, SIG_NOTOCEAN)) {
+    r.clear();
+    r.template at<5, A>() = 1.0;
+  } else {
+    RhsRow<A, F>::build(r, S, T, c, f);
+    if ((uint32_t)c.sig != 0u) apply_boundaries<A>(r, c.sig);
+    filter_row<A>(r);
+  }
   double Au = row_dot<A>(r, x);
   double B = -Au - mixv + frc - 0.0;
   B = B * (sbit(c.sig, SIG_LANDVAL) ? 0.0 : 1.0);

@@ -71,11 +71,11 @@ __device__ __forceinline__ void warp_copy_out(double* __restrict__ val, const do
 
 template <int A>
 __device__ __forceinline__ double do_jac_row(const AsmArgs& a, const Cell& c, const TileFields& f, bool active, int row0,
-                                             const int (&rp)[7], double* scr, int lane) {
+                                             const int (&rp)[7], double* scr, int lane, const MixFD* fd = nullptr) {
   double b = 0.0;
   int len = 0;
   if (active) {
-    b = jac_row<A>(a.S, a.T, c, f, a.sp, row0 + A - 1, scr + lane * STRIDE);
+    b = jac_row<A>(a.S, a.T, c, f, a.sp, row0 + A - 1, scr + lane * STRIDE, fd);
     len = (row0 + A - 1 == a.sp.rowintcon) ? 0 : rp[A] - rp[A - 1];
   }
   __syncwarp();
@@ -128,8 +128,12 @@ __global__ void __launch_bounds__(NTHREADS, 2) jac_kernel(const __grid_constant_
   b[1] = do_jac_row<VV>(a, c, f, active, row0, rp, scr, lane);
   b[2] = do_jac_row<WW>(a, c, f, active, row0, rp, scr, lane);
   b[3] = do_jac_row<PP>(a, c, f, active, row0, rp, scr, lane);
-  b[4] = do_jac_row<TT>(a, c, f, active, row0, rp, scr, lane);
-  b[5] = do_jac_row<SS>(a, c, f, active, row0, rp, scr, lane);
+  // convective-adjustment finite differences: evaluated once, shared by the T and the S row
+  MixFD fd;
+  if (active && S.vmix_on && !sbit(c.sig, SIG_NOTOCEAN))
+    thcm_mix_fd(S, a.T, c, f.t(0, 0, -1), f.s(0, 0, -1), f.t(0, 0, 0), f.s(0, 0, 0), f.t(0, 0, 1), f.s(0, 0, 1), fd);
+  b[4] = do_jac_row<TT>(a, c, f, active, row0, rp, scr, lane, &fd);
+  b[5] = do_jac_row<SS>(a, c, f, active, row0, rp, scr, lane, &fd);
 
   // diag(B): the active cells of a line are consecutive rows -> one contiguous, coalesced run
   if (active) {

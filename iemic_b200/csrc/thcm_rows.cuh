@@ -14,8 +14,10 @@
 
 #ifdef __CUDACC__
 #define THCM_HD __host__ __device__ __forceinline__
+#define THCM_HD_NI static __host__ __device__ __noinline__   // kept out of line on the device: instruction-cache footprint
 #else
 #define THCM_HD inline __attribute__((always_inline))
+#define THCM_HD_NI static inline
 #endif
 
 namespace thcm {
@@ -186,34 +188,59 @@ THCM_HD double thcm_tprstb(const Scalars& S, double grad) {
   if (!(c > 0.0)) return 0.0;   // max(tanh(c),0) == 0 for c <= 0
   return tanh(c);
 }
+// Implicit flux through one cell face between cell a (below) and cell b (above); flag = isoc(a)*isoc(b).
+struct Face { double ft, fs; };
+THCM_HD_NI Face thcm_face(const Scalars& S, double flag, double dzw, double ta, double sa, double tb, double sb) {
+  double dt = flag * (tb - ta) / dzw, ds = flag * (sb - sa) / dzw;
+  double dr = flag * (thcm_rho(S, tb, sb) - thcm_rho(S, ta, sa)) / dzw;
+  double tp = thcm_tprstb(S, -dr);
+  Face f; f.ft = -tp * S.kvc * dt; f.fs = -tp * S.kvc * ds;
+  return f;
+}
+THCM_HD void thcm_mix_combine(const Scalars& S, double dzt, const Face& u, const Face& d, double& mt, double& ms) {
+  if (S.rho_mixing) {
+    mt = ((u.ft - d.ft) - (u.fs - d.fs) * S.lambda) / (2.0 * dzt) + (0.0 + 0.0 + 0.0);
+    ms = ((u.fs - d.fs) - (u.ft - d.ft) / S.lambda) / (2.0 * dzt) + (0.0 + 0.0 + 0.0);
+  } else {
+    mt = (u.ft - d.ft) / dzt + 0.0;
+    ms = (u.fs - d.fs) / dzt + 0.0;
+  }
+}
 // t0,s0: cell k-1; t1,s1: cell k; t2,s2: cell k+1.  Returns mix for the T row in mt and S row in ms.
 THCM_HD void thcm_mix(const Scalars& S, const Tables& T, const Cell& c, double t0, double s0, double t1, double s1,
                       double t2, double s2, double& mt, double& ms) {
   const double up = sbit(c.sig, SIG_FACE_UP) ? 1.0 : 0.0, dn = sbit(c.sig, SIG_FACE_DN) ? 1.0 : 0.0;
-  double ftu = 0.0, fsu = 0.0, ftd = 0.0, fsd = 0.0;
+  Face fu, fd; fu.ft = 0.0; fu.fs = 0.0; fd.ft = 0.0; fd.fs = 0.0;
   if (S.kvc != 0.0) {
-    {
-      double dzw = T.dzdfzW[c.k];
-      double dt = up * (t2 - t1) / dzw, ds = up * (s2 - s1) / dzw;
-      double dr = up * (thcm_rho(S, t2, s2) - thcm_rho(S, t1, s1)) / dzw;
-      double tp = thcm_tprstb(S, -dr);
-      ftu = -tp * S.kvc * dt; fsu = -tp * S.kvc * ds;
-    }
-    if (c.k > 1) {
-      double dzw = T.dzdfzW[c.k - 1];
-      double dt = dn * (t1 - t0) / dzw, ds = dn * (s1 - s0) / dzw;
-      double dr = dn * (thcm_rho(S, t1, s1) - thcm_rho(S, t0, s0)) / dzw;
-      double tp = thcm_tprstb(S, -dr);
-      ftd = -tp * S.kvc * dt; fsd = -tp * S.kvc * ds;
-    }
+    fu = thcm_face(S, up, T.dzdfzW[c.k], t1, s1, t2, s2);
+    if (c.k > 1) fd = thcm_face(S, dn, T.dzdfzW[c.k - 1], t0, s0, t1, s1);
   }
-  double dzt = T.dzdfzT[c.k];
-  if (S.rho_mixing) {
-    mt = ((ftu - ftd) - (fsu - fsd) * S.lambda) / (2.0 * dzt) + (0.0 + 0.0 + 0.0);
-    ms = ((fsu - fsd) - (ftu - ftd) / S.lambda) / (2.0 * dzt) + (0.0 + 0.0 + 0.0);
-  } else {
-    mt = (ftu - ftd) / dzt + 0.0;
-    ms = (fsu - fsd) / dzt + 0.0;
+  thcm_mix_combine(S, T.dzdfzT[c.k], fu, fd, mt, ms);
+}
+// vmix_jac (mix_imp.f:729-815): forward differences of mix with eps = 1e-8 with respect to t0,s0,t1,s1,t2,s2 (p = 0..5).
+// A perturbation of the cell below only changes the lower face and one of the cell above only the upper face, so the
+// unchanged face of the base evaluation is reused: 10 face evaluations instead of 14 full ones, same arithmetic.
+struct MixFD { double bt, bs, mt[6], ms[6]; };
+THCM_HD void thcm_mix_fd(const Scalars& S, const Tables& T, const Cell& c, double t0, double s0, double t1, double s1,
+                         double t2, double s2, MixFD& o) {
+  const double eps = 1.0e-08;
+  const double up = sbit(c.sig, SIG_FACE_UP) ? 1.0 : 0.0, dn = sbit(c.sig, SIG_FACE_DN) ? 1.0 : 0.0;
+  const double dzu = T.dzdfzW[c.k], dzd = T.dzdfzW[c.k > 1 ? c.k - 1 : 0], dzt = T.dzdfzT[c.k];
+  const bool on = S.kvc != 0.0, lower = on && c.k > 1;
+  Face zero; zero.ft = 0.0; zero.fs = 0.0;
+  const Face u0 = on ? thcm_face(S, up, dzu, t1, s1, t2, s2) : zero;
+  const Face d0 = lower ? thcm_face(S, dn, dzd, t0, s0, t1, s1) : zero;
+  thcm_mix_combine(S, dzt, u0, d0, o.bt, o.bs);
+#pragma unroll 1
+  for (int p = 0; p < 6; p++) {
+    const double a0 = (p == 0) ? t0 + eps : t0, b0 = (p == 1) ? s0 + eps : s0;
+    const double a1 = (p == 2) ? t1 + eps : t1, b1 = (p == 3) ? s1 + eps : s1;
+    const double a2 = (p == 4) ? t2 + eps : t2, b2 = (p == 5) ? s2 + eps : s2;
+    const Face u = (on && p >= 2) ? thcm_face(S, up, dzu, a1, b1, a2, b2) : u0;
+    const Face d = (lower && p <= 3) ? thcm_face(S, dn, dzd, a0, b0, a1, b1) : d0;
+    double mt, ms;
+    thcm_mix_combine(S, dzt, u, d, mt, ms);
+    o.mt[p] = mt; o.ms[p] = ms;
   }
 }
 
@@ -221,7 +248,7 @@ THCM_HD void thcm_mix(const Scalars& S, const Tables& T, const Cell& c, double t
 template <int A, class F> struct JacRow;
 
 template <class F> struct JacRow<UU, F> {
-  static THCM_HD void build(Row<UU>& r, const Scalars& S, const Tables& T, const Cell& c, const F& f) {
+  static THCM_HD void build(Row<UU>& r, const Scalars& S, const Tables& T, const Cell& c, const F& f, const MixFD* = nullptr) {
     const int j = c.j, k = c.k;
     const bool iL = c.i >= 2, iR = c.i <= S.n - 1, jS = j >= 2, jN = j <= S.m - 1;
     const double e = S.epsr, cx = T.cdxu[j], cy = T.cdyu[j], t8 = T.tdzi8[k];
@@ -252,7 +279,7 @@ template <class F> struct JacRow<UU, F> {
 };
 
 template <class F> struct JacRow<VV, F> {
-  static THCM_HD void build(Row<VV>& r, const Scalars& S, const Tables& T, const Cell& c, const F& f) {
+  static THCM_HD void build(Row<VV>& r, const Scalars& S, const Tables& T, const Cell& c, const F& f, const MixFD* = nullptr) {
     const int j = c.j, k = c.k;
     const bool iL = c.i >= 2, iR = c.i <= S.n - 1, jS = j >= 2, jN = j <= S.m - 1;
     const double e = S.epsr, cx = T.cdxu[j], cy = T.cdyu[j], t8 = T.tdzi8[k];
@@ -281,7 +308,7 @@ template <class F> struct JacRow<VV, F> {
 };
 
 template <class F> struct JacRow<WW, F> {
-  static THCM_HD void build(Row<WW>& r, const Scalars& S, const Tables& T, const Cell& c, const F& f) {
+  static THCM_HD void build(Row<WW>& r, const Scalars& S, const Tables& T, const Cell& c, const F& f, const MixFD* = nullptr) {
     const int k = c.k;
     r.template at<5, WW>() = 0.0;
     r.template at<5, PP>() = -T.wp[k];
@@ -299,7 +326,7 @@ template <class F> struct JacRow<WW, F> {
 };
 
 template <class F> struct JacRow<PP, F> {
-  static THCM_HD void build(Row<PP>& r, const Scalars& S, const Tables& T, const Cell& c, const F& f) {
+  static THCM_HD void build(Row<PP>& r, const Scalars& S, const Tables& T, const Cell& c, const F& f, const MixFD* = nullptr) {
     const int j = c.j, k = c.k;
     r.template at<5, PP>() = 0.0;
     r.template at<2, UU>() = -T.pu[j]; r.template at<4, UU>() = T.pu[j]; r.template at<1, UU>() = -T.pu[j]; r.template at<5, UU>() = T.pu[j];
@@ -311,7 +338,7 @@ template <class F> struct JacRow<PP, F> {
 // T and S rows share one implementation (X = own tracer, Y = the other one)
 template <int X, class F> struct TracerJac {
   static THCM_HD double c_(const F& f, int di, int dj, int dk) { return X == TT ? f.t(di, dj, dk) : f.s(di, dj, dk); }
-  static THCM_HD void build(Row<X>& r, const Scalars& S, const Tables& T, const Cell& c, const F& f) {
+  static THCM_HD void build(Row<X>& r, const Scalars& S, const Tables& T, const Cell& c, const F& f, const MixFD* fd = nullptr) {
     constexpr int Y = (X == TT) ? SS : TT;
     const int j = c.j, k = c.k;
     const double cx = T.cdxt[j], cy = T.cdyt[j], td = S.tdzi2, dT = T.dfzT[k];
@@ -339,24 +366,23 @@ template <int X, class F> struct TracerJac {
     // vmix_jac: forward differences, eps = 1e-8 (mix_imp.f:745-769), only OCEAN rows carry a pattern (:891)
     if (S.vmix_on && !sbit(c.sig, SIG_NOTOCEAN)) {
       const double eps = 1.0e-08;
-      double t0 = f.t(0, 0, -1), s0 = f.s(0, 0, -1), t1 = f.t(0, 0, 0), s1 = f.s(0, 0, 0), t2 = f.t(0, 0, 1), s2 = f.s(0, 0, 1);
-      double mt, ms, bt, bs;
-      thcm_mix(S, T, c, t0, s0, t1, s1, t2, s2, bt, bs);
-      const double base = (X == TT) ? bt : bs;
-#define THCM_FD(slot, var, T0, S0, T1, S1, T2, S2)                                            \
-  thcm_mix(S, T, c, T0, S0, T1, S1, T2, S2, mt, ms);                                          \
-  r.template at<slot, var>() = r.template at<slot, var>() + (((X == TT) ? mt : ms) - base) / eps;
+      MixFD local;
+      if (!fd) {
+        thcm_mix_fd(S, T, c, f.t(0, 0, -1), f.s(0, 0, -1), f.t(0, 0, 0), f.s(0, 0, 0), f.t(0, 0, 1), f.s(0, 0, 1), local);
+        fd = &local;
+      }
+      const double base = (X == TT) ? fd->bt : fd->bs;
+      const double* mp = (X == TT) ? fd->mt : fd->ms;
       if (sbit(c.sig, SIG_FACE_DN)) { // neighbour k-1 is OCEAN (pattern of vmix_el_1, mix_imp.f:895-907)
-        THCM_FD(14, TT, t0 + eps, s0, t1, s1, t2, s2)
-        THCM_FD(14, SS, t0, s0 + eps, t1, s1, t2, s2)
+        r.template at<14, TT>() = r.template at<14, TT>() + (mp[0] - base) / eps;
+        r.template at<14, SS>() = r.template at<14, SS>() + (mp[1] - base) / eps;
       }
-      THCM_FD(5, TT, t0, s0, t1 + eps, s1, t2, s2)
-      THCM_FD(5, SS, t0, s0, t1, s1 + eps, t2, s2)
+      r.template at<5, TT>() = r.template at<5, TT>() + (mp[2] - base) / eps;
+      r.template at<5, SS>() = r.template at<5, SS>() + (mp[3] - base) / eps;
       if (sbit(c.sig, SIG_FACE_UP)) {
-        THCM_FD(23, TT, t0, s0, t1, s1, t2 + eps, s2)
-        THCM_FD(23, SS, t0, s0, t1, s1, t2, s2 + eps)
+        r.template at<23, TT>() = r.template at<23, TT>() + (mp[4] - base) / eps;
+        r.template at<23, SS>() = r.template at<23, SS>() + (mp[5] - base) / eps;
       }
-#undef THCM_FD
     }
   }
 };
@@ -428,7 +454,7 @@ template <class F> struct RhsRow<WW, F> {
 };
 template <class F> struct RhsRow<PP, F> {
   static THCM_HD void build(Row<PP>& r, const Scalars& S, const Tables& T, const Cell& c, const F& f) {
-    JacRow<PP, F>::build(r, S, T, c, f); // linear row
+    JacRow<PP, F>::build(r, S, T, c, f, nullptr); // linear row
   }
 };
 template <int X, class F> struct TracerRhs {
@@ -608,29 +634,60 @@ template <int A, class X> THCM_HD double row_dot(const Row<A>& r, const X& x) {
   return s;
 }
 
-// Store the row into the static CSR.  `out` points at the first value of this row (rowptr[row]).
-// Fast path: no periodic seam inside the stencil => the static (dk,dj,di,var) order is the column order.
+// ---- storing a row into the static CSR ----
+// Entries sort by (dk, dj) group first (9 groups), then by column inside the group.  At a periodic seam inside one
+// rank the wrapped neighbour changes only the order INSIDE a group: at i=1 the west neighbours (di=-1) wrap to i=n and
+// sort last, at i=n the east neighbours (di=+1) wrap to i=1 and sort first.  A group is present or absent as a whole
+// there (di is never clipped on a periodic domain), so positions are group prefix sums plus compile-time ranks.
+constexpr int slot_group(int s) { return (slot_dk(s) + 1) * 3 + (slot_dj(s) + 1); }
+constexpr int seam_key(int di, int side) { // side 0: i==1, side 1: i==n
+  return side == 0 ? (di == -1 ? 2 : (di == 0 ? 0 : 1)) : (di == 1 ? 0 : (di == -1 ? 1 : 2));
+}
+template <int A> constexpr int group_size(int g) {
+  int cnt = 0;
+  for (int q = 0; q < RowDef<A>::NE; q++) cnt += slot_group(RowDef<A>::e[q].slot) == g ? 1 : 0;
+  return cnt;
+}
+template <int A> constexpr int seam_rank(int e, int side) {
+  const int g = slot_group(RowDef<A>::e[e].slot);
+  const int ke = seam_key(slot_di(RowDef<A>::e[e].slot), side) * 8 + RowDef<A>::e[e].var;
+  int cnt = 0;
+  for (int q = 0; q < RowDef<A>::NE; q++)
+    if (slot_group(RowDef<A>::e[q].slot) == g) {
+      const int kq = seam_key(slot_di(RowDef<A>::e[q].slot), side) * 8 + RowDef<A>::e[q].var;
+      cnt += kq < ke ? 1 : 0;
+    }
+  return cnt;
+}
+// `out` points at the first value of this row (rowptr[row]).
 template <int A, class Out> THCM_HD void emit_row(const Row<A>& r, const Scalars& S, const Cell& c, Out out) {
   const bool seam = row_has_seam(S, c);
-  if (!seam) {
+  const bool inner_jk = c.j > 1 && c.j < S.m && c.k > 1 && c.k < S.l;
+  const bool inner_i = S.periodic || (c.i > 1 && c.i < S.n);
+  if (!seam && inner_jk && inner_i) { // every slot present, static order == column order
+    static_for<0, Row<A>::NE>([&](auto q) { constexpr int e = decltype(q)::value; out[e] = r.a[e]; });
+  } else if (!seam) {
     int pos = 0;
     static_for<0, Row<A>::NE>([&](auto q) {
       constexpr int e = decltype(q)::value;
       if (slot_present(RowDef<A>::e[e].slot, S, c)) { out[pos] = r.a[e]; pos++; }
     });
   } else {
-    int cols[Row<A>::NE];
-    static_for<0, Row<A>::NE>([&](auto q) {
-      constexpr int e = decltype(q)::value;
-      cols[e] = slot_present(RowDef<A>::e[e].slot, S, c) ? slot_col(RowDef<A>::e[e].slot, RowDef<A>::e[e].var, S, c) : 0x7fffffff;
+    int pre[9];
+    int acc = 0;
+    static_for<0, 9>([&](auto gq) {
+      constexpr int g = decltype(gq)::value;
+      constexpr int dk = g / 3 - 1, dj = g % 3 - 1;
+      const bool present = !((dj < 0 && c.j == 1) || (dj > 0 && c.j == S.m) || (dk < 0 && c.k == 1) || (dk > 0 && c.k == S.l));
+      pre[g] = present ? acc : -1;
+      acc += present ? group_size<A>(g) : 0;
     });
+    const bool west = c.i == 1;
     static_for<0, Row<A>::NE>([&](auto q) {
       constexpr int e = decltype(q)::value;
-      if (cols[e] != 0x7fffffff) {
-        int pos = 0;
-        for (int p = 0; p < Row<A>::NE; p++) pos += (cols[p] < cols[e]) ? 1 : 0;
-        out[pos] = r.a[e];
-      }
+      constexpr int g = slot_group(RowDef<A>::e[e].slot);
+      constexpr int rw = seam_rank<A>(e, 0), re = seam_rank<A>(e, 1);
+      if (pre[g] >= 0) out[pre[g] + (west ? rw : re)] = r.a[e];
     });
   }
 }
