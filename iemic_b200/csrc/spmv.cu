@@ -14,15 +14,17 @@
 // and a block-wide tree reduction.
 // HBM traffic: 12 B per non-zero + 4 B rowptr + 8 B y per row + x once.
 #include "kernels.h"
+#include <cstdlib>
 
 namespace thcm {
 namespace {
 constexpr int SP_THREADS = 256;
-constexpr int NNZ_CAP = 4096;  // products staged per block (32 KB of shared memory)
 constexpr int ROWS_CAP = SP_THREADS;
 constexpr unsigned FULL = 0xffffffffu;
 
-__global__ void __launch_bounds__(SP_THREADS) spmv_kernel(const int* __restrict__ blk_row, const int* __restrict__ rowptr,
+// NNZ_CAP: products staged per block (8 B of shared memory each); MINB: resident blocks per SM the register budget allows
+template <int NNZ_CAP, int MINB>
+__global__ void __launch_bounds__(SP_THREADS, MINB) spmv_kernel(const int* __restrict__ blk_row, const int* __restrict__ rowptr,
                                                           const int* __restrict__ col, const double* __restrict__ val,
                                                           const double* __restrict__ x, double* __restrict__ y) {
   __shared__ __align__(16) double prod[NNZ_CAP + 8];
@@ -76,13 +78,84 @@ __global__ void __launch_bounds__(SP_THREADS) spmv_kernel(const int* __restrict_
     y[r0 + threadIdx.x] = s;
   }
 }
+
+// Scalar-lane flavour: lane = consecutive non-zero, so one gather instruction touches the x entries of ~2 adjacent rows
+// (a dozen 32-byte sectors) instead of the ~7 rows a 4-per-thread vector layout spreads it over: the L1 gather
+// wavefronts, not HBM, bound this kernel.
+template <int NNZ_CAP, int MINB, int NT>
+__global__ void __launch_bounds__(NT, MINB) spmv_kernel_s(const int* __restrict__ blk_row, const int* __restrict__ rowptr,
+                                                            const int* __restrict__ col, const double* __restrict__ val,
+                                                            const double* __restrict__ x, double* __restrict__ y) {
+  __shared__ double prod[NNZ_CAP];
+  const int r0 = blk_row[blockIdx.x], r1 = blk_row[blockIdx.x + 1];
+  const int nr = r1 - r0;
+  const int p0 = __ldg(rowptr + r0), p1 = __ldg(rowptr + r1);
+  if (nr == 1 && p1 - p0 > NNZ_CAP) { // long row
+    double s = 0.0;
+    for (int p = p0 + threadIdx.x; p < p1; p += NT) s += __ldcs(val + p) * __ldg(x + __ldcs(col + p));
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(FULL, s, o);
+    if ((threadIdx.x & 31) == 0) prod[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double t = 0.0;
+      for (int w = 0; w < NT / 32; w++) t += prod[w];
+      y[r0] = t;
+    }
+    return;
+  }
+  constexpr int NIT = NNZ_CAP / NT;
+  int c[NIT];
+  double v[NIT];
+#pragma unroll
+  for (int it = 0; it < NIT; it++) {
+    const int p = p0 + threadIdx.x + NT * it;
+    if (p < p1) { c[it] = __ldcs(col + p); v[it] = __ldcs(val + p); }
+  }
+#pragma unroll
+  for (int it = 0; it < NIT; it++) {
+    const int p = p0 + threadIdx.x + NT * it;
+    if (p < p1) prod[p - p0] = v[it] * __ldg(x + c[it]);
+  }
+  __syncthreads();
+  if (threadIdx.x < nr) {
+    const int q0 = __ldg(rowptr + r0 + threadIdx.x) - p0, q1 = __ldg(rowptr + r0 + threadIdx.x + 1) - p0;
+    double s = 0.0;
+    for (int q = q0; q < q1; q++) s = __dadd_rn(s, prod[q]);
+    y[r0 + threadIdx.x] = s;
+  }
+}
+
+// variant table; IEMIC_SPMV_VARIANT selects one at start-up (tuning aid), default = the best measured on B200
+struct Variant { int cap, minb, nt; };
+const Variant kVariants[] = {{4096, 3, 256}, {2048, 4, 256}, {2048, 6, 256}, {1024, 8, 256}, {512, 16, 128}, {1024, 12, 128}, {1024, 8, 256}, {256, 32, 64}, {512, 24, 64}, {256, 16, 128}};
+int g_variant = -1;
+int variant() {
+  if (g_variant < 0) {
+    const char* e = getenv("IEMIC_SPMV_VARIANT");
+    int v = e ? atoi(e) : 4;
+    g_variant = (v >= 0 && v < 10) ? v : 4;
+  }
+  return g_variant;
+}
 } // namespace
 
-int spmv_nnz_cap() { return NNZ_CAP - 4; } // the aligned start may shift the run by up to 3 entries
-int spmv_rows_cap() { return ROWS_CAP; }
+int spmv_nnz_cap() { return kVariants[variant()].cap - 4; } // the aligned start may shift the run by up to 3 entries
+int spmv_rows_cap() { return kVariants[variant()].nt; } // one thread per row in the reduction phase
 
 void launch_spmv(const SpmvPlan& p, const int* rowptr, const int* col, const double* val, const double* x, double* y, cudaStream_t st) {
-  if (p.nblocks > 0) spmv_kernel<<<p.nblocks, SP_THREADS, 0, st>>>(p.blk_row, rowptr, col, val, x, y);
+  if (p.nblocks <= 0) return;
+  switch (variant()) {
+    case 0: spmv_kernel<4096, 3><<<p.nblocks, SP_THREADS, 0, st>>>(p.blk_row, rowptr, col, val, x, y); break;
+    case 1: spmv_kernel<2048, 4><<<p.nblocks, SP_THREADS, 0, st>>>(p.blk_row, rowptr, col, val, x, y); break;
+    case 2: spmv_kernel<2048, 6><<<p.nblocks, SP_THREADS, 0, st>>>(p.blk_row, rowptr, col, val, x, y); break;
+    case 3: spmv_kernel<1024, 8><<<p.nblocks, SP_THREADS, 0, st>>>(p.blk_row, rowptr, col, val, x, y); break;
+    case 4: spmv_kernel_s<512, 16, 128><<<p.nblocks, 128, 0, st>>>(p.blk_row, rowptr, col, val, x, y); break;
+    case 5: spmv_kernel_s<1024, 12, 128><<<p.nblocks, 128, 0, st>>>(p.blk_row, rowptr, col, val, x, y); break;
+    case 6: spmv_kernel_s<1024, 8, 256><<<p.nblocks, 256, 0, st>>>(p.blk_row, rowptr, col, val, x, y); break;
+    case 7: spmv_kernel_s<256, 32, 64><<<p.nblocks, 64, 0, st>>>(p.blk_row, rowptr, col, val, x, y); break;
+    case 8: spmv_kernel_s<512, 24, 64><<<p.nblocks, 64, 0, st>>>(p.blk_row, rowptr, col, val, x, y); break;
+    default: spmv_kernel_s<256, 16, 128><<<p.nblocks, 128, 0, st>>>(p.blk_row, rowptr, col, val, x, y); break;
+  }
 }
 
 } // namespace thcm

@@ -1,0 +1,99 @@
+"""Worker of tests/test_gpu_dist.py (torchrun, one rank per GPU, NCCL): the multi-GPU hot path against the oracle."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, HERE)
+sys.path.insert(0, os.path.dirname(HERE))
+import cases  # noqa: E402
+import oracle_lib as ol  # noqa: E402
+import iemic_b200 as ib  # noqa: E402
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    idbuf = torch.zeros(128, dtype=torch.uint8, device="cuda")
+    if rank == 0:
+        hid = np.zeros(128, np.uint8)
+        ib.capi.check(ib.lib().thcm_b200_comm_unique_id(hid.ctypes.data))
+        idbuf.copy_(torch.from_numpy(hid))
+    dist.broadcast(idbuf, 0)
+    nccl_id = idbuf.cpu().numpy().copy()
+    first = True
+    for name in ("rand_periodic", "rand_box", "global4"):
+        cfg, mask, pars = cases.case(name)
+        if not first:
+            # a fresh communicator per handle
+            if rank == 0:
+                hid = np.zeros(128, np.uint8)
+                ib.capi.check(ib.lib().thcm_b200_comm_unique_id(hid.ctypes.data))
+                idbuf.copy_(torch.from_numpy(hid))
+            dist.broadcast(idbuf, 0)
+            nccl_id = idbuf.cpu().numpy().copy()
+        first = False
+        G = ib.Ocean(cfg, mask, rank=rank, nranks=world, nccl_id=nccl_id)
+        O = ol.Oracle(cfg, mask)
+        for k, v in pars.items():
+            G.setPar(k, v)
+            O.set_par(k, v)
+        xg = cases.state(cfg, mask, seed=21)
+        gid = G.global_ids()
+        own = gid[:G.nrows]
+        # host-buffer API: owned part in, halo exchanged inside
+        Fg = G.computeRHS_host(xg[own])
+        Fo = O.rhs(xg)[own]
+        ts = (np.arange(G.nrows) % 6) >= 4
+        assert np.array_equal(Fo[~ts], Fg[~ts]), name
+        assert np.abs(Fo - Fg).max() <= 1e-12 * max(np.abs(Fo).max(), 1e-300), name
+        vg, bg = G.computeJacobian_host(xg[own])
+        vo, bo = O.jac(xg)
+        assert np.array_equal(bo[own], bg)
+        rp, col = G.graph()
+        rpo, colo = O.graph()
+        # compare row by row through the global ids
+        import scipy.sparse as sp
+        Jo = sp.csr_matrix((vo, colo, rpo), shape=(O.ndim, O.ndim))[own]
+        lr = np.repeat(np.arange(G.nrows), np.diff(rp))
+        Jg = sp.csr_matrix((vg, (lr, gid[col])), shape=(G.nrows, O.ndim))
+        assert (abs(Jo) > 0).sum() <= Jg.nnz
+        d = abs(Jo - Jg)
+        scale = abs(Jo).max()
+        assert d.max() <= 1e-6 * scale, (name, d.max())
+        # halo exchange on a device vector + SpMV
+        v = np.random.default_rng(5).uniform(-1, 1, O.ndim)
+        dv = torch.zeros(G.nvec, dtype=torch.float64, device="cuda")
+        dv[:G.nrows] = torch.from_numpy(v[own]).cuda()
+        y = torch.zeros(G.nvec, dtype=torch.float64, device="cuda")
+        G.applyMatrix(dv, y)
+        G.sync()
+        used = gid >= 0
+        assert np.array_equal(dv.cpu().numpy()[used], v[gid[used]]), "halo exchange"
+        yo = Jo @ v
+        yg = y.cpu().numpy()[:G.nrows]
+        assert np.abs(yo - yg).max() <= 1e-12 * max(np.abs(yo).max(), 1.0), name
+        # distributed dot / norm
+        a = torch.from_numpy(v[own]).cuda()
+        assert abs(G.dot(a, a) - float(np.dot(v, v))) <= 1e-12 * float(np.dot(v, v))
+        # GMRES history against the single-domain oracle (Jacobian assembled by the oracle)
+        b_full = ol.spmv(rpo, colo, vo, np.ones(O.ndim))
+        m = 12
+        rc_o, xo, ho, it_o = ol.gmres(rpo, colo, vo, b_full, np.zeros(O.ndim), m, m - 1, 0.0)
+        db = torch.from_numpy(b_full[own]).cuda()
+        for ortho, tol in ((ib.MGS, 1e-9), (ib.CGS2, 1e-8)):
+            dxs = torch.zeros(G.nvec, dtype=torch.float64, device="cuda")
+            rc, hist, it = G.solve(db, dxs, m=m, maxit=m - 1, tol=0.0, ortho=ortho, check_every=0)
+            assert it == it_o
+            assert np.all(np.abs(hist[:m] - ho[:m]) <= tol * np.abs(ho[:m]) + 1e-13), (name, hist[:m], ho[:m])
+        G.close()
+    print("rank %d ok" % rank, flush=True)
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

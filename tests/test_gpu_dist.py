@@ -1,0 +1,26 @@
+"""Multi-GPU parity (needs >= 2 GPUs; skipped otherwise): NCCL halo exchange + allreduces against the single-domain oracle."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _ngpu():
+    import torch
+    return torch.cuda.device_count()
+
+
+@pytest.mark.parametrize("nproc", [2, 4, 8])
+def test_multi_gpu_parity(nproc):
+    if _ngpu() < nproc:
+        pytest.skip("needs %d GPUs" % nproc)
+    here = os.path.dirname(os.path.abspath(__file__))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(nproc), "--master-addr", "127.0.0.1",
+           "--master-port", str(29600 + nproc), os.path.join(here, "dist_gpu_worker.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    for k in range(nproc):
+        assert "rank %d ok" % k in r.stdout
