@@ -14,12 +14,12 @@ _LIB = None
 
 # THCM::par2int (src/ocean/THCM.C:1754-1869 of the reference) / par.F90:37-66
 PAR_NAMES = {
-    "Time": 0, "AL_T": 1, "Rayleigh-Number": 2, "Vertical Ekman-Number": 3, "Horizontal Ekman-Number": 4,
-    "Rossby-Number": 5, "Mixing": 6, "Rayleigh-Damping": 7, "Nonlinear Factor": 8, "Flux Perturbation": 27,
-    "Heat-Model": 9, "Solar Forcing": 10, "Horizontal Peclet-Number": 11, "Vertical Peclet-Number": 12,
-    "P_VC": 13, "LAMB": 14, "Salinity Forcing": 15, "Wind Forcing": 16, "Temperature Forcing": 17,
-    "Nonlinear Thermal Factor": 18, "Combined Forcing": 19, "ARCL": 20, "IFRICB": 22, "CONT": 23,
-    "Energy": 24, "Alpha-C": 25, "CMPR": 26, "Salinity Perturbation": 28, "Mixing-Kappa": 29, "SPL2": 30,
+    "AL_T": 1, "Rayleigh-Number": 2, "Vertical Ekman-Number": 3, "Horizontal Ekman-Number": 4, "Rossby-Number": 5,
+    "MIXP": 6, "RESC": 7, "SPL1": 8, "Salinity Homotopy": 9, "Solar Forcing": 10, "Horizontal Peclet-Number": 11,
+    "Vertical Peclet-Number": 12, "P_VC": 13, "LAMB": 14, "Salinity Forcing": 15, "Wind Forcing": 16,
+    "Temperature Forcing": 17, "Nonlinear Factor": 18, "Combined Forcing": 19, "ARCL": 20, "NLES": 21, "IFRICB": 22,
+    "CONT": 23, "Energy": 24, "ALPC": 25, "CMPR": 26, "Flux Perturbation": 27, "Salinity Perturbation": 28, "MKAP": 29,
+    "SPL2": 30,
 }
 PAR = dict(AL_T=1, RAYL=2, EK_V=3, EK_H=4, ROSB=5, MIXP=6, RESC=7, SPL1=8, HMTP=9, SUNP=10, PE_H=11,
            PE_V=12, P_VC=13, LAMB=14, SALT=15, WIND=16, TEMP=17, BIOT=18, COMB=19, ARCL=20, NLES=21,
