@@ -45,9 +45,13 @@ def _digest(paths, flags):
     return h.hexdigest()
 
 
-def build(force=False, verbose=False):
+def build(force=False, verbose=False, defines=(), tag=None):
+    """tag/defines: build an experimental variant into lib/variants/libiemic_b200_<tag>.so (tools/ only)"""
+    global LIB
     os.makedirs(LIBDIR, exist_ok=True)
-    objdir = os.path.join(HERE, "build")
+    objdir = os.path.join(HERE, "build" if not tag else os.path.join("build", tag))
+    lib = LIB if not tag else os.path.join(LIBDIR, "variants", "libiemic_b200_%s.so" % tag)
+    os.makedirs(os.path.dirname(lib), exist_ok=True)
     os.makedirs(objdir, exist_ok=True)
     hdrs = [os.path.join(CSRC, h) for h in HEADERS]
     objs = []
@@ -57,7 +61,7 @@ def build(force=False, verbose=False):
         sp = os.path.join(CSRC, src)
         obj = os.path.join(objdir, src + ".o")
         stamp = obj + ".sha"
-        flags = ARCH + COMMON + extra
+        flags = ARCH + COMMON + extra + ["-D" + d for d in defines]
         dig = _digest([sp] + hdrs, flags)
         objs.append(obj)
         if not force and os.path.exists(obj) and os.path.exists(stamp) and open(stamp).read() == dig:
@@ -74,10 +78,10 @@ def build(force=False, verbose=False):
             sys.stderr.write(out)
         with open(stamp, "w") as f:
             f.write(dig)
-    if rebuilt or not os.path.exists(LIB):
-        cmd = [_nvcc()] + ARCH + ["-shared", "-o", LIB] + objs + ["-cudart", "static", "-ldl"]
+    if rebuilt or not os.path.exists(lib):
+        cmd = [_nvcc()] + ARCH + ["-shared", "-o", lib] + objs + ["-cudart", "static", "-ldl"]
         subprocess.run(cmd, check=True)
-    return LIB
+    return lib
 
 
 if __name__ == "__main__":

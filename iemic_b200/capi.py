@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "lib", "libiemic_b200.so")
+LIB_PATH = os.environ.get("IEMIC_B200_LIB") or os.path.join(HERE, "lib", "libiemic_b200.so")  # override: kernel-variant experiments
 _LIB = None
 
 # THCM::par2int (src/ocean/THCM.C:1754-1869 of the reference) / par.F90:37-66
@@ -71,6 +71,7 @@ def lib():
             "thcm_b200_set_values_host": [vp, dp], "thcm_b200_forcing_host": [vp, dp],
             "thcm_b200_intcond_host": [vp, dp, ip],
             "thcm_b200_rhs_host": [vp, vp, vp], "thcm_b200_jacobian_host": [vp, vp, vp, vp],
+            "thcm_b200_assemble_host": [vp, vp, vp, C.c_int],
             "thcm_b200_spmv": [vp, vp, vp], "thcm_b200_spmv_host": [vp, vp, vp],
             "vec_b200_dot": [vp, vp, vp, dp], "vec_b200_norm2": [vp, vp, dp],
             "vec_b200_update": [vp, C.c_double, vp, C.c_double, vp], "vec_b200_scale": [vp, C.c_double, vp],
@@ -97,7 +98,7 @@ EXPORTED = ["iemic_b200_last_error", "iemic_b200_version", "iemic_b200_device_co
             "thcm_b200_set_intcond_correction", "thcm_b200_sizes", "thcm_b200_block", "thcm_b200_global_ids",
             "thcm_b200_rhs", "thcm_b200_jacobian", "thcm_b200_halo_exchange", "thcm_b200_csr", "thcm_b200_graph_host",
             "thcm_b200_values_host", "thcm_b200_set_values_host", "thcm_b200_forcing_host", "thcm_b200_intcond_host",
-            "thcm_b200_rhs_host", "thcm_b200_jacobian_host", "thcm_b200_spmv", "thcm_b200_spmv_host",
+            "thcm_b200_rhs_host", "thcm_b200_jacobian_host", "thcm_b200_assemble_host", "thcm_b200_spmv", "thcm_b200_spmv_host",
             "vec_b200_dot", "vec_b200_norm2", "vec_b200_update", "vec_b200_scale", "vec_b200_putscalar",
             "gmres_b200_solve", "gmres_b200_solve_host", "thcm_b200_launch_count", "thcm_b200_timing_enable",
             "thcm_b200_timing_reset", "thcm_b200_timing_get", "iemic_b200_malloc", "iemic_b200_free",
@@ -211,6 +212,11 @@ class Ocean:
         diagB = np.empty(self.nrows)
         check(lib().thcm_b200_jacobian_host(self.h, _hp(x), _hp(val), _hp(diagB)))
         return val, diagB
+
+    def assemble_host(self, x, F=None, jacobian=True):
+        """computeRHS + computeJacobian on one state: one upload, F downloaded under the Jacobian kernel"""
+        check(lib().thcm_b200_assemble_host(self.h, _hp(x), _hp(F) if F is not None else None, int(jacobian)))
+        return F
 
     def values_host(self):
         val = np.empty(self.nnz)

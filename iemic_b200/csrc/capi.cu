@@ -48,6 +48,7 @@ struct thcm_b200 {
   Host* host = nullptr;
   Dist* dist = nullptr;          // null on a single GPU
   cudaStream_t stream = 0;
+  cudaStream_t copy_stream = nullptr; cudaEvent_t ev_rhs = nullptr, ev_copy = nullptr; // thcm_b200_assemble_host overlap
   // static / per-parameter device data
   double* d_tab = nullptr; uint64_t* d_sig = nullptr; int* d_rowptr = nullptr; int* d_col = nullptr;
   double* d_val = nullptr; double* d_diagB = nullptr; double* d_frc = nullptr; double* d_coefS = nullptr;
@@ -262,6 +263,7 @@ int thcm_b200_destroy(thcm_b200_t* h) {
                   h->rb.partial, h->rb.ticket, h->d_small};
   for (void* p : ptrs) if (p) cudaFree(p);
   gmres_free(h->g);
+  if (h->copy_stream) { cudaStreamDestroy(h->copy_stream); cudaEventDestroy(h->ev_rhs); cudaEventDestroy(h->ev_copy); }
   if (h->dist) dist_destroy(h->dist);
   delete h->host;
   delete h;
@@ -426,6 +428,30 @@ int thcm_b200_jacobian_host(thcm_b200_t* h, const double* x, double* val, double
   if (int rc = thcm_b200_jacobian(h, h->d_xs)) return rc;
   if (val) CU(cudaMemcpyAsync(val, h->d_val, h->host->col.size() * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
   if (diagB) CU(cudaMemcpyAsync(diagB, h->d_diagB, nb, cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  return 0;
+}
+
+int thcm_b200_assemble_host(thcm_b200_t* h, const double* x, double* F, int jacobian) {
+  CHECK_H(h);
+  if (int rc = refresh_device(h)) return rc;
+  const size_t nb = (size_t)h->nrows() * sizeof(double);
+  if (!h->copy_stream) {
+    CU(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+    CU(cudaEventCreateWithFlags(&h->ev_rhs, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&h->ev_copy, cudaEventDisableTiming));
+  }
+  CU(cudaMemcpyAsync(h->d_xs, x, nb, cudaMemcpyHostToDevice, h->stream));
+  if (int rc = thcm_b200_halo_exchange(h, h->d_xs)) return rc;
+  if (F) {
+    if (int rc = thcm_b200_rhs(h, h->d_xs, h->d_ys)) return rc;
+    CU(cudaEventRecord(h->ev_rhs, h->stream));
+    CU(cudaStreamWaitEvent(h->copy_stream, h->ev_rhs, 0));
+    CU(cudaMemcpyAsync(F, h->d_ys, nb, cudaMemcpyDeviceToHost, h->copy_stream)); // overlaps the Jacobian kernel
+    CU(cudaEventRecord(h->ev_copy, h->copy_stream));
+  }
+  if (jacobian) if (int rc = thcm_b200_jacobian(h, h->d_xs)) return rc;
+  if (F) CU(cudaStreamWaitEvent(h->stream, h->ev_copy, 0));
   CU(cudaStreamSynchronize(h->stream));
   return 0;
 }

@@ -324,7 +324,7 @@ Tables Host::tables(const double* base) const {
                               &T.vv_we, &T.vv_s, &T.vv_n, &T.vv_ch, &T.vu_c, &T.vu_w, &T.vu_e,
                               &T.pu, &T.pv_s, &T.pv_n, &T.tt_we, &T.tt_s, &T.tt_n, &T.tt_ch, nullptr, nullptr};
   for (int q = 0; q < NJTAB; q++) { if (jt[q]) *jt[q] = p; p += nj; }
-  const double** kt[NKTAB] = {&T.uu_b, &T.uu_t, &T.uu_cv, &T.tt_b, &T.tt_t, &T.tt_cv, &T.wp, &T.pw, &T.tdzi8, &T.dfzT, &T.dzdfzT, &T.dzdfzW};
+  const double** kt[NKTAB] = {&T.uu_b, &T.uu_t, &T.uu_cv, &T.tt_b, &T.tt_t, &T.tt_cv, &T.wp, &T.pw, &T.tdzi8, &T.dfzT, &T.dzdfzT, &T.dzdfzW, &T.r_dfzT, &T.r_dzdfzT, &T.r_dzdfzW};
   for (int q = 0; q < NKTAB; q++) { *kt[q] = p; p += nk; }
   return T;
 }
@@ -417,8 +417,10 @@ void Host::build_tables() {
     W(T.tdzi8)[k] = 1.0 / (8 * dfzT[k] * dz);
     W(T.dfzT)[k] = dfzT[k];
     W(T.dzdfzT)[k] = dz * dfzT[k];
+    W(T.r_dfzT)[k] = 1.0 / dfzT[k];
+    W(T.r_dzdfzT)[k] = 1.0 / (dz * dfzT[k]);
   }
-  for (int k = 0; k <= l; k++) W(T.dzdfzW)[k] = dz * dfzW[k];
+  for (int k = 0; k <= l; k++) { W(T.dzdfzW)[k] = dz * dfzW[k]; W(T.r_dzdfzW)[k] = 1.0 / (dz * dfzW[k]); }
 
   std::memset(&S, 0, sizeof(S));
   S.n = n; S.m = m; S.l = l; S.periodic = cfg.periodic != 0;

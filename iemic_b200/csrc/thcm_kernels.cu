@@ -29,6 +29,9 @@ constexpr int NWARP = TJ * TK;       // one warp per line of the tile
 constexpr int NTHREADS = NWARP * 32;
 constexpr int STRIDE = 25;           // scratch doubles per lane: odd, so 8-byte accesses are bank-conflict free
 constexpr unsigned FULL = 0xffffffffu;
+#ifndef JAC_MINB
+#define JAC_MINB 2
+#endif
 
 struct TileFields { // accessor concept F of thcm_rows.cuh over the shared-memory tile
   const double *pu, *pv, *pw, *pt, *ps;
@@ -65,13 +68,47 @@ __device__ __forceinline__ void warp_copy_out(double* __restrict__ val, const do
     const int cell = t / NE, q = t - cell * NE;
     const int b = __shfl_sync(FULL, base, cell);
     const int ln = __shfl_sync(FULL, len, cell);
+#ifdef JAC_NO_STORE
+    if (q < ln && scr[cell * STRIDE + q] == 1.2345e300) __stcs(val + (size_t)b + q, 0.0);
+#else
     if (q < ln) __stcs(val + (size_t)b + q, scr[cell * STRIDE + q]);
+#endif
+  }
+}
+
+// Fast flavour for a warp whose 32 cells all carry complete rows (no domain edge, no dense row): the cell blocks are
+// CELL_NNZ apart, so addresses follow from the lane-0 offset alone -- no shuffles, no predicates.
+constexpr int CELL_NNZ = RowDef<UU>::NE + RowDef<VV>::NE + RowDef<WW>::NE + RowDef<PP>::NE + RowDef<TT>::NE + RowDef<SS>::NE; // 104
+template <int A> constexpr int row_offset() {
+  int o = 0;
+  if (A > UU) o += RowDef<UU>::NE;
+  if (A > VV) o += RowDef<VV>::NE;
+  if (A > WW) o += RowDef<WW>::NE;
+  if (A > PP) o += RowDef<PP>::NE;
+  if (A > TT) o += RowDef<TT>::NE;
+  return o;
+}
+// Lanes 0..NE-1 move one cell's row per step: both addresses are "register + compile-time immediate", i.e. one LDS and
+// one STG per cell and no index arithmetic at all.  Each store covers NE*8 contiguous bytes (56..192 B).
+template <int NE, int OFF>
+__device__ __forceinline__ void warp_copy_out_full(double* __restrict__ val, const double* scr, int lane) {
+  if (lane < NE) {
+    const double* src = scr + lane;
+    double* dst = val + OFF + lane;
+#pragma unroll
+    for (int cell = 0; cell < 32; cell++) {
+#ifdef JAC_NO_STORE
+      if (src[cell * STRIDE] == 1.2345e300) __stcs(dst + cell * CELL_NNZ, 0.0);
+#else
+      __stcs(dst + cell * CELL_NNZ, src[cell * STRIDE]);
+#endif
+    }
   }
 }
 
 template <int A>
 __device__ __forceinline__ double do_jac_row(const AsmArgs& a, const Cell& c, const TileFields& f, bool active, int row0,
-                                             const int (&rp)[7], double* scr, int lane, const MixFD* fd = nullptr) {
+                                             const int (&rp)[7], double* scr, int lane, bool full, int b0, const MixFD* fd = nullptr) {
   double b = 0.0;
   int len = 0;
   if (active) {
@@ -79,7 +116,8 @@ __device__ __forceinline__ double do_jac_row(const AsmArgs& a, const Cell& c, co
     len = (row0 + A - 1 == a.sp.rowintcon) ? 0 : rp[A] - rp[A - 1];
   }
   __syncwarp();
-  warp_copy_out<RowDef<A>::NE>(a.val, scr, rp[A - 1], len, lane);
+  if (full) warp_copy_out_full<RowDef<A>::NE, row_offset<A>()>(a.val + (size_t)b0, scr, lane);
+  else warp_copy_out<RowDef<A>::NE>(a.val, scr, rp[A - 1], len, lane);
   __syncwarp();
   return b;
 }
@@ -100,7 +138,7 @@ __device__ __forceinline__ void stage_tile(const AsmArgs& a, double* sm, int gi0
   }
 }
 
-__global__ void __launch_bounds__(NTHREADS, 2) jac_kernel(const __grid_constant__ AsmArgs a) {
+__global__ void __launch_bounds__(NTHREADS, JAC_MINB) jac_kernel(const __grid_constant__ AsmArgs a) {
   extern __shared__ double sm[];
   const Scalars& S = a.S;
   const int bx = blockIdx.x % a.ntx, by = (blockIdx.x / a.ntx) % a.nty, bz = blockIdx.x / (a.ntx * a.nty);
@@ -123,17 +161,20 @@ __global__ void __launch_bounds__(NTHREADS, 2) jac_kernel(const __grid_constant_
   for (int q = 0; q < 7; q++) rp[q] = active ? __ldg(a.rowptr + row0 + q) : 0;
   double* scr = sm + 5 * TCELLS + warp * 32 * STRIDE;
 
+  const int b0 = __shfl_sync(FULL, rp[0], 0);
+  const bool full = __all_sync(FULL, active && rp[0] == b0 + lane * CELL_NNZ && rp[6] - rp[0] == CELL_NNZ &&
+                                         !(a.sp.rowintcon >= row0 && a.sp.rowintcon < row0 + 6));
   double b[6];
-  b[0] = do_jac_row<UU>(a, c, f, active, row0, rp, scr, lane);
-  b[1] = do_jac_row<VV>(a, c, f, active, row0, rp, scr, lane);
-  b[2] = do_jac_row<WW>(a, c, f, active, row0, rp, scr, lane);
-  b[3] = do_jac_row<PP>(a, c, f, active, row0, rp, scr, lane);
+  b[0] = do_jac_row<UU>(a, c, f, active, row0, rp, scr, lane, full, b0);
+  b[1] = do_jac_row<VV>(a, c, f, active, row0, rp, scr, lane, full, b0);
+  b[2] = do_jac_row<WW>(a, c, f, active, row0, rp, scr, lane, full, b0);
+  b[3] = do_jac_row<PP>(a, c, f, active, row0, rp, scr, lane, full, b0);
   // convective-adjustment finite differences: evaluated once, shared by the T and the S row
   MixFD fd;
   if (active && S.vmix_on && !sbit(c.sig, SIG_NOTOCEAN))
     thcm_mix_fd(S, a.T, c, f.t(0, 0, -1), f.s(0, 0, -1), f.t(0, 0, 0), f.s(0, 0, 0), f.t(0, 0, 1), f.s(0, 0, 1), fd);
-  b[4] = do_jac_row<TT>(a, c, f, active, row0, rp, scr, lane, &fd);
-  b[5] = do_jac_row<SS>(a, c, f, active, row0, rp, scr, lane, &fd);
+  b[4] = do_jac_row<TT>(a, c, f, active, row0, rp, scr, lane, full, b0, &fd);
+  b[5] = do_jac_row<SS>(a, c, f, active, row0, rp, scr, lane, full, b0, &fd);
 
   // diag(B): the active cells of a line are consecutive rows -> one contiguous, coalesced run
   if (active) {

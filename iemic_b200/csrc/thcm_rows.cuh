@@ -82,8 +82,9 @@ struct Tables {
   const double *dfzT;                    // dfzT(k)
   const double *dzdfzT;                  // dz*dfzT(k)
   const double *dzdfzW;                  // dz*dfzW(k), k=0..l
+  const double *r_dfzT, *r_dzdfzT, *r_dzdfzW; // correctly rounded reciprocals of the three divisors above (see thcm_div)
 };
-static const int NJTAB = 29, NKTAB = 12; // number of per-j / per-k tables above
+static const int NJTAB = 29, NKTAB = 15; // number of per-j / per-k tables above
 
 // ---------------------------------------------------------------------------------------------
 // Row patterns: entries sorted by (dk, dj, di, var) == ascending column index away from the periodic
@@ -176,6 +177,16 @@ struct Cell { int i, j, k; uint64_t sig; };
 //   double F::u(di,dj,dk), v, w, t, s  -> the ghosted/land-zeroed fields that usol produces
 //                                          (usrc.F90:997-1104) at cell (i+di, j+dj, k+dk).
 
+// x / d with the divisor's reciprocal rd = RN(1/d) tabulated on the host: q = RN(x*rd), r = x - q*d (exact, one FMA),
+// q' = RN(q + r*rd).  With a correctly rounded reciprocal this Markstein sequence returns the correctly rounded
+// quotient -- the same bits as the Fortran's division -- in 3 instructions instead of the ~25 of a generic fp64
+// divide (no overflow/underflow here: the operands are O(1e-6..1e6)).  Exact zeros stay exact zeros.
+THCM_HD double thcm_div(double x, double d, double rd) {
+  const double q = x * rd;
+  const double r = fma(-q, d, x);
+  return fma(r, rd, q);
+}
+
 // ---- vertical (convective-adjustment) mixing, the only non-zero branch with the stpnt defaults ----
 // mix_imp.f:231-562 with piso=pgm=eps=0: mix = (Fimp(k)-Fimp(k-1))/(dz*dfzT(k)),
 // Fimp(k) = -tprstb(-drhodzt(k),sp1)*kvc*dCdzt(k)   (mix_imp.f:486-492, :837-856)
@@ -188,22 +199,29 @@ THCM_HD double thcm_tprstb(const Scalars& S, double grad) {
   if (!(c > 0.0)) return 0.0;   // max(tanh(c),0) == 0 for c <= 0
   return tanh(c);
 }
-// Implicit flux through one cell face between cell a (below) and cell b (above); flag = isoc(a)*isoc(b).
+// Implicit flux through one cell face between cell a (below) and cell b (above); flag = isoc(a)*isoc(b); ra, rb are
+// thcm_rho of the two cells (passed in so that callers can reuse them).  Shortcuts that do not change any value:
+// a closed face (flag = 0) and a stably stratified one (tprstb = 0) carry a zero flux whatever dT/dz, dS/dz are, so
+// their two extra divisions are skipped (the sign of a zero flux cannot reach the result: thcm_mix_combine adds +0.0).
 struct Face { double ft, fs; };
-THCM_HD_NI Face thcm_face(const Scalars& S, double flag, double dzw, double ta, double sa, double tb, double sb) {
-  double dt = flag * (tb - ta) / dzw, ds = flag * (sb - sa) / dzw;
-  double dr = flag * (thcm_rho(S, tb, sb) - thcm_rho(S, ta, sa)) / dzw;
+struct Div { double d, rd; }; // a divisor and its reciprocal
+THCM_HD Face thcm_face(const Scalars& S, double flag, Div dzw, double ta, double sa, double ra, double tb, double sb, double rb) {
+  Face f; f.ft = 0.0; f.fs = 0.0;
+  if (flag == 0.0) return f;
+  double dr = thcm_div(flag * (rb - ra), dzw.d, dzw.rd);
   double tp = thcm_tprstb(S, -dr);
-  Face f; f.ft = -tp * S.kvc * dt; f.fs = -tp * S.kvc * ds;
+  if (tp == 0.0) return f;
+  double dt = thcm_div(flag * (tb - ta), dzw.d, dzw.rd), ds = thcm_div(flag * (sb - sa), dzw.d, dzw.rd);
+  f.ft = -tp * S.kvc * dt; f.fs = -tp * S.kvc * ds;
   return f;
 }
-THCM_HD void thcm_mix_combine(const Scalars& S, double dzt, const Face& u, const Face& d, double& mt, double& ms) {
+THCM_HD void thcm_mix_combine(const Scalars& S, Div dzt, const Face& u, const Face& d, double& mt, double& ms) {
   if (S.rho_mixing) {
-    mt = ((u.ft - d.ft) - (u.fs - d.fs) * S.lambda) / (2.0 * dzt) + (0.0 + 0.0 + 0.0);
-    ms = ((u.fs - d.fs) - (u.ft - d.ft) / S.lambda) / (2.0 * dzt) + (0.0 + 0.0 + 0.0);
+    mt = ((u.ft - d.ft) - (u.fs - d.fs) * S.lambda) / (2.0 * dzt.d) + (0.0 + 0.0 + 0.0);
+    ms = ((u.fs - d.fs) - (u.ft - d.ft) / S.lambda) / (2.0 * dzt.d) + (0.0 + 0.0 + 0.0);
   } else {
-    mt = (u.ft - d.ft) / dzt + 0.0;
-    ms = (u.fs - d.fs) / dzt + 0.0;
+    mt = thcm_div(u.ft - d.ft, dzt.d, dzt.rd) + 0.0;
+    ms = thcm_div(u.fs - d.fs, dzt.d, dzt.rd) + 0.0;
   }
 }
 // t0,s0: cell k-1; t1,s1: cell k; t2,s2: cell k+1.  Returns mix for the T row in mt and S row in ms.
@@ -212,36 +230,53 @@ THCM_HD void thcm_mix(const Scalars& S, const Tables& T, const Cell& c, double t
   const double up = sbit(c.sig, SIG_FACE_UP) ? 1.0 : 0.0, dn = sbit(c.sig, SIG_FACE_DN) ? 1.0 : 0.0;
   Face fu, fd; fu.ft = 0.0; fu.fs = 0.0; fd.ft = 0.0; fd.fs = 0.0;
   if (S.kvc != 0.0) {
-    fu = thcm_face(S, up, T.dzdfzW[c.k], t1, s1, t2, s2);
-    if (c.k > 1) fd = thcm_face(S, dn, T.dzdfzW[c.k - 1], t0, s0, t1, s1);
+    const double r1 = thcm_rho(S, t1, s1);
+    fu = thcm_face(S, up, Div{T.dzdfzW[c.k], T.r_dzdfzW[c.k]}, t1, s1, r1, t2, s2, thcm_rho(S, t2, s2));
+    if (c.k > 1) fd = thcm_face(S, dn, Div{T.dzdfzW[c.k - 1], T.r_dzdfzW[c.k - 1]}, t0, s0, thcm_rho(S, t0, s0), t1, s1, r1);
   }
-  thcm_mix_combine(S, T.dzdfzT[c.k], fu, fd, mt, ms);
+  thcm_mix_combine(S, Div{T.dzdfzT[c.k], T.r_dzdfzT[c.k]}, fu, fd, mt, ms);
 }
 // vmix_jac (mix_imp.f:729-815): forward differences of mix with eps = 1e-8 with respect to t0,s0,t1,s1,t2,s2 (p = 0..5).
 // A perturbation of the cell below only changes the lower face and one of the cell above only the upper face, so the
-// unchanged face of the base evaluation is reused: 10 face evaluations instead of 14 full ones, same arithmetic.
+// unchanged face (and the unchanged densities) of the base evaluation are reused: 10 face evaluations and 9 densities
+// instead of 14 full evaluations, same arithmetic.
 struct MixFD { double bt, bs, mt[6], ms[6]; };
 THCM_HD void thcm_mix_fd(const Scalars& S, const Tables& T, const Cell& c, double t0, double s0, double t1, double s1,
                          double t2, double s2, MixFD& o) {
   const double eps = 1.0e-08;
   const double up = sbit(c.sig, SIG_FACE_UP) ? 1.0 : 0.0, dn = sbit(c.sig, SIG_FACE_DN) ? 1.0 : 0.0;
-  const double dzu = T.dzdfzW[c.k], dzd = T.dzdfzW[c.k > 1 ? c.k - 1 : 0], dzt = T.dzdfzT[c.k];
+  const int kd = c.k > 1 ? c.k - 1 : 0;
+  const Div dzu{T.dzdfzW[c.k], T.r_dzdfzW[c.k]}, dzd{T.dzdfzW[kd], T.r_dzdfzW[kd]}, dzt{T.dzdfzT[c.k], T.r_dzdfzT[c.k]};
   const bool on = S.kvc != 0.0, lower = on && c.k > 1;
   Face zero; zero.ft = 0.0; zero.fs = 0.0;
-  const Face u0 = on ? thcm_face(S, up, dzu, t1, s1, t2, s2) : zero;
-  const Face d0 = lower ? thcm_face(S, dn, dzd, t0, s0, t1, s1) : zero;
+  const double r0 = thcm_rho(S, t0, s0), r1 = thcm_rho(S, t1, s1), r2 = thcm_rho(S, t2, s2);
+  const Face u0 = on ? thcm_face(S, up, dzu, t1, s1, r1, t2, s2, r2) : zero;
+  const Face d0 = lower ? thcm_face(S, dn, dzd, t0, s0, r0, t1, s1, r1) : zero;
   thcm_mix_combine(S, dzt, u0, d0, o.bt, o.bs);
-#pragma unroll 1
-  for (int p = 0; p < 6; p++) {
-    const double a0 = (p == 0) ? t0 + eps : t0, b0 = (p == 1) ? s0 + eps : s0;
-    const double a1 = (p == 2) ? t1 + eps : t1, b1 = (p == 3) ? s1 + eps : s1;
-    const double a2 = (p == 4) ? t2 + eps : t2, b2 = (p == 5) ? s2 + eps : s2;
-    const Face u = (on && p >= 2) ? thcm_face(S, up, dzu, a1, b1, a2, b2) : u0;
-    const Face d = (lower && p <= 3) ? thcm_face(S, dn, dzd, a0, b0, a1, b1) : d0;
-    double mt, ms;
-    thcm_mix_combine(S, dzt, u, d, mt, ms);
-    o.mt[p] = mt; o.ms[p] = ms;
+  Face u, d;
+  // cell below: lower face only
+  d = lower ? thcm_face(S, dn, dzd, t0 + eps, s0, thcm_rho(S, t0 + eps, s0), t1, s1, r1) : zero;
+  thcm_mix_combine(S, dzt, u0, d, o.mt[0], o.ms[0]);
+  d = lower ? thcm_face(S, dn, dzd, t0, s0 + eps, thcm_rho(S, t0, s0 + eps), t1, s1, r1) : zero;
+  thcm_mix_combine(S, dzt, u0, d, o.mt[1], o.ms[1]);
+  // the cell itself: both faces
+  {
+    const double rp = thcm_rho(S, t1 + eps, s1);
+    u = on ? thcm_face(S, up, dzu, t1 + eps, s1, rp, t2, s2, r2) : zero;
+    d = lower ? thcm_face(S, dn, dzd, t0, s0, r0, t1 + eps, s1, rp) : zero;
+    thcm_mix_combine(S, dzt, u, d, o.mt[2], o.ms[2]);
   }
+  {
+    const double rp = thcm_rho(S, t1, s1 + eps);
+    u = on ? thcm_face(S, up, dzu, t1, s1 + eps, rp, t2, s2, r2) : zero;
+    d = lower ? thcm_face(S, dn, dzd, t0, s0, r0, t1, s1 + eps, rp) : zero;
+    thcm_mix_combine(S, dzt, u, d, o.mt[3], o.ms[3]);
+  }
+  // cell above: upper face only
+  u = on ? thcm_face(S, up, dzu, t1, s1, r1, t2 + eps, s2, thcm_rho(S, t2 + eps, s2)) : zero;
+  thcm_mix_combine(S, dzt, u, d0, o.mt[4], o.ms[4]);
+  u = on ? thcm_face(S, up, dzu, t1, s1, r1, t2, s2 + eps, thcm_rho(S, t2, s2 + eps)) : zero;
+  thcm_mix_combine(S, dzt, u, d0, o.mt[5], o.ms[5]);
 }
 
 // ---- Jacobian rows: An = Al + nlin_jac (usrc.F90:873-995) + vmix_jac (mix_imp.f:729-815) ----
@@ -348,12 +383,13 @@ template <int X, class F> struct TracerJac {
     r.template at<2, UU>() = uw; r.template at<4, UU>() = ue; r.template at<1, UU>() = uw; r.template at<5, UU>() = ue;
     double vs = -cy * (c0 + c_(f, 0, -1, 0)) * T.cyv[j - 1], vn = cy * (c_(f, 0, 1, 0) + c0) * T.cyv[j];
     r.template at<4, VV>() = vs; r.template at<1, VV>() = vs; r.template at<5, VV>() = vn; r.template at<2, VV>() = vn;
-    r.template at<14, WW>() = -td * (c0 + c_(f, 0, 0, -1)) / dT;
-    r.template at<5, WW>() = (k <= S.l - 1) ? td * (c_(f, 0, 0, 1) + c0) / dT : 0.0;
+    const double rdT = T.r_dfzT[k];
+    r.template at<14, WW>() = thcm_div(-td * (c0 + c_(f, 0, 0, -1)), dT, rdT);
+    r.template at<5, WW>() = (k <= S.l - 1) ? thcm_div(td * (c_(f, 0, 0, 1) + c0), dT, rdT) : 0.0;
     // X-X: Utrx + Vtry + Wtrz (tnlin 3,5,7)
     double x2 = -(f.u(-1, 0, 0) + f.u(-1, -1, 0)) * cx, x8 = (f.u(0, 0, 0) + f.u(0, -1, 0)) * cx;
     double y4 = -(f.v(0, -1, 0) + f.v(-1, -1, 0)) * cy * T.cyv[j - 1], y6 = (f.v(0, 0, 0) + f.v(-1, 0, 0)) * cy * T.cyv[j];
-    double z14 = -f.w(0, 0, -1) * td / dT, z23 = f.w(0, 0, 0) * td / dT;
+    double z14 = thcm_div(-f.w(0, 0, -1) * td, dT, rdT), z23 = thcm_div(f.w(0, 0, 0) * td, dT, rdT);
     double surf = (k == S.l) ? (X == TT ? S.tt_surf : S.ss_surf) : 0.0;
     r.template at<2, X>() = T.tt_we[j] + x2;
     r.template at<8, X>() = T.tt_we[j] + x8;
@@ -365,7 +401,7 @@ template <int X, class F> struct TracerJac {
     r.template at<14, Y>() = 0.0; r.template at<5, Y>() = 0.0; r.template at<23, Y>() = 0.0;
     // vmix_jac: forward differences, eps = 1e-8 (mix_imp.f:745-769), only OCEAN rows carry a pattern (:891)
     if (S.vmix_on && !sbit(c.sig, SIG_NOTOCEAN)) {
-      const double eps = 1.0e-08;
+      const double eps = 1.0e-08, reps = 1.0 / 1.0e-08;
       MixFD local;
       if (!fd) {
         thcm_mix_fd(S, T, c, f.t(0, 0, -1), f.s(0, 0, -1), f.t(0, 0, 0), f.s(0, 0, 0), f.t(0, 0, 1), f.s(0, 0, 1), local);
@@ -374,14 +410,14 @@ template <int X, class F> struct TracerJac {
       const double base = (X == TT) ? fd->bt : fd->bs;
       const double* mp = (X == TT) ? fd->mt : fd->ms;
       if (sbit(c.sig, SIG_FACE_DN)) { // neighbour k-1 is OCEAN (pattern of vmix_el_1, mix_imp.f:895-907)
-        r.template at<14, TT>() = r.template at<14, TT>() + (mp[0] - base) / eps;
-        r.template at<14, SS>() = r.template at<14, SS>() + (mp[1] - base) / eps;
+        r.template at<14, TT>() = r.template at<14, TT>() + thcm_div(mp[0] - base, eps, reps);
+        r.template at<14, SS>() = r.template at<14, SS>() + thcm_div(mp[1] - base, eps, reps);
       }
-      r.template at<5, TT>() = r.template at<5, TT>() + (mp[2] - base) / eps;
-      r.template at<5, SS>() = r.template at<5, SS>() + (mp[3] - base) / eps;
+      r.template at<5, TT>() = r.template at<5, TT>() + thcm_div(mp[2] - base, eps, reps);
+      r.template at<5, SS>() = r.template at<5, SS>() + thcm_div(mp[3] - base, eps, reps);
       if (sbit(c.sig, SIG_FACE_UP)) {
-        r.template at<23, TT>() = r.template at<23, TT>() + (mp[4] - base) / eps;
-        r.template at<23, SS>() = r.template at<23, SS>() + (mp[5] - base) / eps;
+        r.template at<23, TT>() = r.template at<23, TT>() + thcm_div(mp[4] - base, eps, reps);
+        r.template at<23, SS>() = r.template at<23, SS>() + thcm_div(mp[5] - base, eps, reps);
       }
     }
   }
@@ -463,7 +499,8 @@ template <int X, class F> struct TracerRhs {
     const double cx = T.cdxt[j], cy = T.cdyt[j], td = S.tdzi2, dT = T.dfzT[k];
     double x2 = -(f.u(-1, 0, 0) + f.u(-1, -1, 0)) * cx, x8 = (f.u(0, 0, 0) + f.u(0, -1, 0)) * cx;
     double y4 = -(f.v(0, -1, 0) + f.v(-1, -1, 0)) * cy * T.cyv[j - 1], y6 = (f.v(0, 0, 0) + f.v(-1, 0, 0)) * cy * T.cyv[j];
-    double z14 = -f.w(0, 0, -1) * td / dT, z23 = f.w(0, 0, 0) * td / dT;
+    const double rdT = T.r_dfzT[k];
+    double z14 = thcm_div(-f.w(0, 0, -1) * td, dT, rdT), z23 = thcm_div(f.w(0, 0, 0) * td, dT, rdT);
     double surf = (k == S.l) ? (X == TT ? S.tt_surf : S.ss_surf) : 0.0;
     r.clear();
     r.template at<2, X>() = T.tt_we[j] + x2;

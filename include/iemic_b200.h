@@ -101,6 +101,10 @@ int thcm_b200_intcond_host(thcm_b200_t* h, double* coeff, int* rowintcon);
 /* host-buffer entry points: what the reference's Ocean::computeRHS / computeJacobian do on Epetra vectors */
 int thcm_b200_rhs_host(thcm_b200_t* h, const double* x, double* F);
 int thcm_b200_jacobian_host(thcm_b200_t* h, const double* x, double* val /* may be NULL */, double* diagB /* may be NULL */);
+/* One Newton-step assembly on ONE state, as Continuation::newtonCorrector does through computeRHS + computeJacobian on
+ * the model's internal state_ (src/continuation/Continuation.H:654,714): x is uploaded once, F (may be NULL) is
+ * downloaded while the Jacobian kernel runs, the Jacobian stays on the device for thcm_b200_spmv / gmres_b200_solve. */
+int thcm_b200_assemble_host(thcm_b200_t* h, const double* x, double* F, int jacobian);
 
 /* ---- sparse matrix-vector product y = J x on the handle's CSR ---- */
 int thcm_b200_spmv(thcm_b200_t* h, double* d_x /* halo part is overwritten when nranks>1 */, double* d_y);

@@ -223,3 +223,15 @@ def test_full_size_properties():
     rc, hist, it = G.solve(y1, torch.zeros_like(dx), m=10, maxit=9, tol=0.0, ortho=ib.CGS2, check_every=0)
     hh = hist[:10]
     assert it == 10 and np.all(np.diff(hh) <= 1e-12) and hh[-1] < 1.0
+
+
+def test_assemble_host_equals_separate_calls():
+    cfg, mask, O, G = cases.make_pair("global4")
+    x = cases.state(cfg, mask, seed=10)
+    F1 = G.computeRHS_host(x)
+    v1, b1 = G.computeJacobian_host(x)
+    F2 = np.empty(G.nrows)
+    G.set_values_host(np.zeros(G.nnz))
+    G.assemble_host(x, F2, jacobian=True)
+    v2, b2 = G.values_host()
+    assert np.array_equal(F1, F2) and np.array_equal(v1, v2) and np.array_equal(b1, b2)
