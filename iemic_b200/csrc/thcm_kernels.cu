@@ -3,7 +3,7 @@
 // Replaces the Fortran pipeline An=Al; nlin_*; vmix_*; boundaries; assemble; matAvec of the reference
 // (src/ocean/usrc.F90:432-586) by two kernels that never materialise the stencil tensor:
 //
-//   jac_kernel : one thread block per 32x2x4 tile of cells.  The ghosted fields u,v,w,T,S that usol produces
+//   jac_kernel : one thread block per 32x4x2 tile of cells.  The ghosted fields u,v,w,T,S that usol produces
 //                (usrc.F90:997-1104) are staged once per tile in shared memory (radius-1 halo); each warp then owns a
 //                line of 32 cells in i and walks the six rows U,V,W,P,T,S.  A row's <=24 entries are built in
 //                registers (thcm_rows.cuh), compacted into a per-warp shared-memory scratch and copied to the static
@@ -22,7 +22,13 @@
 namespace thcm {
 
 namespace {
-constexpr int TI = 32, TJ = 2, TK = 4;
+#ifndef JAC_TK
+#define JAC_TK 2
+#endif
+#ifndef JAC_TJ
+#define JAC_TJ 4
+#endif
+constexpr int TI = 32, TJ = JAC_TJ, TK = JAC_TK;
 constexpr int SX = TI + 2, SY = TJ + 2, SZ = TK + 2;
 constexpr int TCELLS = SX * SY * SZ; // 816 staged cells per tile
 constexpr int NWARP = TJ * TK;       // one warp per line of the tile
@@ -106,9 +112,25 @@ __device__ __forceinline__ void warp_copy_out_full(double* __restrict__ val, con
   }
 }
 
+// Same idea with run-time strides, for lines whose cells all have the SAME (clipped) row lengths: domain edges in j and
+// k, partially filled last tile in i.  `cs` = values per cell, `off`/`len` = this row's offset and length inside a cell.
+__device__ __forceinline__ void warp_copy_out_uniform(double* __restrict__ val, const double* scr, int lane, int nact, int cs, int off, int len) {
+  if (lane < len) {
+    const double* src = scr + lane;
+    double* dst = val + off + lane;
+#pragma unroll 4
+    for (int cell = 0; cell < nact; cell++) {
+      __stcs(dst, src[0]);
+      dst += cs; src += STRIDE;
+    }
+  }
+}
+enum { COPY_GENERAL = 0, COPY_UNIFORM = 1, COPY_FULL = 2 };
+struct CopyPlan { int mode, b0, nact, cs; };
+
 template <int A>
 __device__ __forceinline__ double do_jac_row(const AsmArgs& a, const Cell& c, const TileFields& f, bool active, int row0,
-                                             const int (&rp)[7], double* scr, int lane, bool full, int b0, const MixFD* fd = nullptr) {
+                                             const int (&rp)[7], double* scr, int lane, const CopyPlan& cp, const MixFD* fd = nullptr) {
   double b = 0.0;
   int len = 0;
   if (active) {
@@ -116,12 +138,17 @@ __device__ __forceinline__ double do_jac_row(const AsmArgs& a, const Cell& c, co
     len = (row0 + A - 1 == a.sp.rowintcon) ? 0 : rp[A] - rp[A - 1];
   }
   __syncwarp();
-  if (full) warp_copy_out_full<RowDef<A>::NE, row_offset<A>()>(a.val + (size_t)b0, scr, lane);
-  else warp_copy_out<RowDef<A>::NE>(a.val, scr, rp[A - 1], len, lane);
+  if (cp.mode == COPY_FULL) warp_copy_out_full<RowDef<A>::NE, row_offset<A>()>(a.val + (size_t)cp.b0, scr, lane);
+  else if (cp.mode == COPY_UNIFORM) {
+    const int off = __shfl_sync(FULL, rp[A - 1] - rp[0], 0), ln = __shfl_sync(FULL, rp[A] - rp[A - 1], 0);
+    warp_copy_out_uniform(a.val + (size_t)cp.b0, scr, lane, cp.nact, cp.cs, off, ln);
+  } else warp_copy_out<RowDef<A>::NE>(a.val, scr, rp[A - 1], len, lane);
   __syncwarp();
   return b;
 }
 
+// Fill the shared-memory tile.  (Issuing all of a thread's loads before consuming them -- stage_plan/stage_apply --
+// was measured: it costs registers in the row code that follows and did not pay.)
 template <bool RHS>
 __device__ __forceinline__ void stage_tile(const AsmArgs& a, double* sm, int gi0, int gj0, int gk0) {
   const Scalars& S = a.S;
@@ -143,38 +170,54 @@ __global__ void __launch_bounds__(NTHREADS, JAC_MINB) jac_kernel(const __grid_co
   const Scalars& S = a.S;
   const int bx = blockIdx.x % a.ntx, by = (blockIdx.x / a.ntx) % a.nty, bz = blockIdx.x / (a.ntx * a.nty);
   const int gi0 = S.io0 + bx * TI, gj0 = S.jo0 + by * TJ, gk0 = 1 + bz * TK;
-  stage_tile<false>(a, sm, gi0, gj0, gk0);
-  __syncthreads();
-
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int lj = warp % TJ, lk = warp / TJ;
   const int i = gi0 + lane, j = gj0 + lj, k = gk0 + lk;
-  if (j >= S.jo0 + S.mloc || k > S.l) return; // warp-uniform
-  const bool active = i < S.io0 + S.nloc;
+  const bool line = j < S.jo0 + S.mloc && k <= S.l; // warp-uniform
+  const bool active = line && i < S.io0 + S.nloc;
+  // this thread's own cell: signature and row offsets are requested before the tile is staged so that their latency
+  // hides behind the staging loads
   const size_t cidx = active ? cell_index(S, i, j, k) : 0;
-  Cell c; c.i = i; c.j = j; c.k = k; c.sig = active ? a.sig[cidx] : 0ull;
-  TileFields f; f.pu = sm; f.pv = sm + TCELLS; f.pw = sm + 2 * TCELLS; f.pt = sm + 3 * TCELLS; f.ps = sm + 4 * TCELLS;
-  f.base = (lane + 1) + (lj + 1) * SX + (lk + 1) * SX * SY;
+  Cell c; c.i = i; c.j = j; c.k = k; c.sig = active ? __ldg(a.sig + cidx) : 0ull;
   const int row0 = (int)(6 * cidx);
   int rp[7];
 #pragma unroll
   for (int q = 0; q < 7; q++) rp[q] = active ? __ldg(a.rowptr + row0 + q) : 0;
+
+  stage_tile<false>(a, sm, gi0, gj0, gk0);
+  __syncthreads();
+  if (!line) return;
+  TileFields f; f.pu = sm; f.pv = sm + TCELLS; f.pw = sm + 2 * TCELLS; f.pt = sm + 3 * TCELLS; f.ps = sm + 4 * TCELLS;
+  f.base = (lane + 1) + (lj + 1) * SX + (lk + 1) * SX * SY;
   double* scr = sm + 5 * TCELLS + warp * 32 * STRIDE;
 
-  const int b0 = __shfl_sync(FULL, rp[0], 0);
-  const bool full = __all_sync(FULL, active && rp[0] == b0 + lane * CELL_NNZ && rp[6] - rp[0] == CELL_NNZ &&
-                                         !(a.sp.rowintcon >= row0 && a.sp.rowintcon < row0 + 6));
+  // how this warp's rows go out: all 32 cells complete (compile-time strides), all active cells alike (run-time strides),
+  // or anything else (non-periodic i edge, dense integral row): per-element shuffles
+  CopyPlan cp;
+  cp.b0 = __shfl_sync(FULL, rp[0], 0);
+  cp.cs = __shfl_sync(FULL, rp[6] - rp[0], 0);
+  cp.nact = __popc(__ballot_sync(FULL, active));
+  {
+    bool same = rp[0] == cp.b0 + lane * cp.cs && !(a.sp.rowintcon >= row0 && a.sp.rowintcon < row0 + 6);
+#pragma unroll
+    for (int q = 1; q <= 6; q++) { // the shuffle must be executed by every lane: no short-circuit in front of it
+      const int ref = __shfl_sync(FULL, rp[q] - rp[0], 0);
+      same = (rp[q] - rp[0] == ref) && same;
+    }
+    const bool uniform = __all_sync(FULL, !active || same);
+    cp.mode = !uniform ? COPY_GENERAL : ((cp.nact == 32 && cp.cs == CELL_NNZ) ? COPY_FULL : COPY_UNIFORM);
+  }
   double b[6];
-  b[0] = do_jac_row<UU>(a, c, f, active, row0, rp, scr, lane, full, b0);
-  b[1] = do_jac_row<VV>(a, c, f, active, row0, rp, scr, lane, full, b0);
-  b[2] = do_jac_row<WW>(a, c, f, active, row0, rp, scr, lane, full, b0);
-  b[3] = do_jac_row<PP>(a, c, f, active, row0, rp, scr, lane, full, b0);
+  b[0] = do_jac_row<UU>(a, c, f, active, row0, rp, scr, lane, cp);
+  b[1] = do_jac_row<VV>(a, c, f, active, row0, rp, scr, lane, cp);
+  b[2] = do_jac_row<WW>(a, c, f, active, row0, rp, scr, lane, cp);
+  b[3] = do_jac_row<PP>(a, c, f, active, row0, rp, scr, lane, cp);
   // convective-adjustment finite differences: evaluated once, shared by the T and the S row
   MixFD fd;
   if (active && S.vmix_on && !sbit(c.sig, SIG_NOTOCEAN))
     thcm_mix_fd(S, a.T, c, f.t(0, 0, -1), f.s(0, 0, -1), f.t(0, 0, 0), f.s(0, 0, 0), f.t(0, 0, 1), f.s(0, 0, 1), fd);
-  b[4] = do_jac_row<TT>(a, c, f, active, row0, rp, scr, lane, full, b0, &fd);
-  b[5] = do_jac_row<SS>(a, c, f, active, row0, rp, scr, lane, full, b0, &fd);
+  b[4] = do_jac_row<TT>(a, c, f, active, row0, rp, scr, lane, cp, &fd);
+  b[5] = do_jac_row<SS>(a, c, f, active, row0, rp, scr, lane, cp, &fd);
 
   // diag(B): the active cells of a line are consecutive rows -> one contiguous, coalesced run
   if (active) {

@@ -197,6 +197,7 @@ THCM_HD double thcm_tprstb(const Scalars& S, double grad) {
   double q = -grad * S.fac;
   double c = q * q * q;
   if (!(c > 0.0)) return 0.0;   // max(tanh(c),0) == 0 for c <= 0
+  if (c >= 22.0) return 1.0;    // tanh rounds to exactly 1.0 in double precision beyond ~19.1
   return tanh(c);
 }
 // Implicit flux through one cell face between cell a (below) and cell b (above); flag = isoc(a)*isoc(b); ra, rb are

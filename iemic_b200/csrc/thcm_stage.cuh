@@ -48,59 +48,68 @@ struct LdVec { // three 16-byte read-only loads per cell (the cell stride is 48 
 };
 #endif
 
-// `raw` receives the unmodified state of the cell the ghost rule reads from (the cell itself when it is inside the
-// domain, the periodic image for an x-ghost): what matAvec multiplies the assembled row with (matetc.F90:147-166).
-template <class Ld>
-THCM_HD Staged stage_cell_t(const Ld& ld, const uint64_t* __restrict__ sig, const Scalars& S, int fi, int fj, int fk, X6& raw) {
+// The ghost rule is split in two so that a kernel can issue the loads of several cells before consuming any of them:
+// stage_plan() says which stored cell a (possibly ghost) position reads and by which rule, stage_apply() turns the loaded
+// cell and its signature into the staged values.
+enum { ST_ZERO = 0, ST_IN = 1, ST_GK = 2, ST_GJ = 3, ST_GI_W = 4, ST_GI_E = 5, ST_GI_WALL = 6 };
+struct StagePlan { size_t c; int rule; bool edge, top; };
+THCM_HD StagePlan stage_plan(const Scalars& S, int fi, int fj, int fk) {
   const int n = S.n, m = S.m, l = S.l;
-  Staged o; o.u = 0.0; o.v = 0.0; o.w = 0.0; o.t = 0.0; o.s = 0.0;
-  raw.u = 0.0; raw.v = 0.0; raw.w = 0.0; raw.p = 0.0; raw.t = 0.0; raw.s = 0.0;
+  StagePlan p; p.c = 0; p.rule = ST_ZERO; p.edge = false; p.top = false;
   const bool gi = fi < 1 || fi > n, gj = fj < 1 || fj > m, gk = fk < 1 || fk > l;
   const int ng = (gi ? 1 : 0) + (gj ? 1 : 0) + (gk ? 1 : 0);
-  if (ng > 1) return o;
-  if (ng == 0) {
-    const size_t c = cell_index(S, fi, fj, fk);
-    const X6 xc = ld(c);
-    raw = xc;
-    const bool live = sbit(sig[c], SIG_LIVE);
-    o.u = live ? xc.u : 0.0; o.v = live ? xc.v : 0.0;
-    o.w = (fk == l) ? 0.0 : xc.w;
-    o.t = xc.t; o.s = xc.s;
-    return o;
-  }
+  if (ng > 1) return p;
+  if (ng == 0) { p.rule = ST_IN; p.c = cell_index(S, fi, fj, fk); p.top = (fk == l); return p; }
   if (gk) { // usrc.F90:1066-1081: copies of the first / last layer taken before the land zeroing
-    const int sk = (fk < 1) ? 1 : l;
-    const X6 xc = ld(cell_index(S, fi, fj, sk));
-    const bool edge = (fj == m) || (!S.periodic && fi == n);
-    o.u = edge ? 0.0 : xc.u; o.v = edge ? 0.0 : xc.v;
-    o.w = 0.0;
-    o.t = xc.t; o.s = xc.s;
-    return o;
+    p.rule = ST_GK; p.c = cell_index(S, fi, fj, (fk < 1) ? 1 : l);
+    p.edge = (fj == m) || (!S.periodic && fi == n);
+    return p;
   }
-  if (gj) { // usrc.F90:1053-1064
-    const int sj = (fj < 1) ? 1 : m;
-    const X6 xc = ld(cell_index(S, fi, sj, fk));
-    o.t = xc.t; o.s = xc.s;
-    return o;
-  }
+  if (gj) { p.rule = ST_GJ; p.c = cell_index(S, fi, (fj < 1) ? 1 : m, fk); return p; } // usrc.F90:1053-1064
   // gi, usrc.F90:1029-1051
-  if (S.periodic) {
-    const int si = (fi < 1) ? n : 1;
-    const size_t c = cell_index(S, si, fj, fk);
-    const X6 xc = ld(c);
-    raw = xc;
-    if (fi < 1) {
-      const bool live = sbit(sig[c], SIG_LIVEWRAP);
+  if (S.periodic) { p.rule = (fi < 1) ? ST_GI_W : ST_GI_E; p.c = cell_index(S, (fi < 1) ? n : 1, fj, fk); }
+  else { p.rule = ST_GI_WALL; p.c = cell_index(S, (fi < 1) ? 1 : n, fj, fk); }
+  return p;
+}
+// `raw` receives the unmodified state of the cell the ghost rule reads from (the cell itself when it is inside the
+// domain, the periodic image for an x-ghost): what matAvec multiplies the assembled row with (matetc.F90:147-166).
+THCM_HD Staged stage_apply(const StagePlan& p, const X6& xc, uint64_t sg, X6& raw) {
+  Staged o; o.u = 0.0; o.v = 0.0; o.w = 0.0; o.t = 0.0; o.s = 0.0;
+  raw.u = 0.0; raw.v = 0.0; raw.w = 0.0; raw.p = 0.0; raw.t = 0.0; raw.s = 0.0;
+  switch (p.rule) {
+    case ST_IN: {
+      raw = xc;
+      const bool live = sbit(sg, SIG_LIVE);
       o.u = live ? xc.u : 0.0; o.v = live ? xc.v : 0.0;
-    }
-    o.w = xc.w;
-    o.t = xc.t; o.s = xc.s;
-  } else {
-    const int si = (fi < 1) ? 1 : n;
-    const X6 xc = ld(cell_index(S, si, fj, fk));
-    o.t = xc.t; o.s = xc.s;
+      o.w = p.top ? 0.0 : xc.w;
+      o.t = xc.t; o.s = xc.s;
+    } break;
+    case ST_GK:
+      o.u = p.edge ? 0.0 : xc.u; o.v = p.edge ? 0.0 : xc.v;
+      o.t = xc.t; o.s = xc.s;
+      break;
+    case ST_GJ: case ST_GI_WALL:
+      o.t = xc.t; o.s = xc.s;
+      break;
+    case ST_GI_W: {
+      raw = xc;
+      const bool live = sbit(sg, SIG_LIVEWRAP);
+      o.u = live ? xc.u : 0.0; o.v = live ? xc.v : 0.0;
+      o.w = xc.w; o.t = xc.t; o.s = xc.s;
+    } break;
+    case ST_GI_E:
+      raw = xc;
+      o.w = xc.w; o.t = xc.t; o.s = xc.s;
+      break;
+    default: break;
   }
   return o;
+}
+template <class Ld>
+THCM_HD Staged stage_cell_t(const Ld& ld, const uint64_t* __restrict__ sig, const Scalars& S, int fi, int fj, int fk, X6& raw) {
+  const StagePlan p = stage_plan(S, fi, fj, fk);
+  if (p.rule == ST_ZERO) { X6 z; z.u = 0.0; z.v = 0.0; z.w = 0.0; z.p = 0.0; z.t = 0.0; z.s = 0.0; return stage_apply(p, z, 0ull, raw); }
+  return stage_apply(p, ld(p.c), sig[p.c], raw);
 }
 
 THCM_HD Staged stage_cell(const double* __restrict__ x, const uint64_t* __restrict__ sig, const Scalars& S, int fi, int fj, int fk) {

@@ -47,3 +47,16 @@ if len(sys.argv) > 5:
             op = t[1] if t[0].startswith("@") else t[0]
             ops[op] += int(r[ie])
     print(want, [(k, round(100 * v / tot, 2)) for k, v in ops.most_common(20)])
+if len(sys.argv) > 6:
+    col = sys.argv[6]
+    ci = hdr.index(col)
+    st = collections.Counter()
+    for r in data:
+        try:
+            st[off2line.get(int(r[0], 16) - base) or ("?", 0)] += int(r[ci])
+        except ValueError:
+            pass
+    tt = sum(st.values()) or 1
+    print(col, "total", tt, "of", ts)
+    for k, v in st.most_common(14):
+        print("   %-24s %5d  %5.1f%%" % (k[0], k[1], 100 * v / tt))
