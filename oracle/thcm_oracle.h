@@ -7,9 +7,15 @@
  * exactly like the reference does.
  *
  * PARITY STATUS: the reference itself cannot be built in this image (no Fortran compiler,
- * no MPI, no Trilinos), and its tests hold no stored RHS/Jacobian vectors, so the oracle is
- * pinned by the reference's own invariants I1-I6, not by golden vectors:
- * "parity unpinned" beyond those invariants.
+ * no MPI, no Trilinos) and its tests hold no stored RHS/Jacobian vectors.  The oracle is pinned
+ * (a) by the KNOWN ANSWER of the reference's own integration test src/tests/intt_2dmoc.C:96-97,
+ * 127-128 -- psi_max = 14.7 +- 0.1 Sv, psi_min = 0 +- 1e-4 and the mirror symmetry of the two
+ * branches after the chain of continuations on the 3x6x6 2-D MOC case (tests/test_known_answer_2dmoc.py
+ * gets 14.704 Sv), which exercises lin, nlin_rhs, nlin_jac, boundaries, forcing, the integral
+ * condition and Newton-consistency of the Jacobian together; and (b) by the invariants I1-I5 of
+ * SURVEY.md section 8c (tests/test_oracle_invariants.py, tests/test_dist_cpu.py).  Not pinned by
+ * any reference number: the convective-adjustment branch (P_VC = 0 in that test; covered only by
+ * the analytic-vs-finite-difference check I4) and land-mask configurations beyond I1-I3.
  *
  * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs
  * may call anything declared here.
