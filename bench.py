@@ -248,9 +248,7 @@ def main():
         return float(ms.item())
 
     def step_dev():
-        G.halo_exchange(dx)
-        G.computeJacobian(dx)
-        G.computeRHS(dx, dF)
+        G.assemble(dx, dF, jacobian=True)
 
     def step_e2e():
         G.assemble_host(x_pin_np, F_pin_np, jacobian=True)

@@ -328,20 +328,23 @@ int thcm_b200_halo_exchange(thcm_b200_t* h, double* d_x) {
   return 0;
 }
 
-int thcm_b200_rhs(thcm_b200_t* h, const double* d_x, double* d_F) {
-  CHECK_H(h);
-  if (int rc = refresh_device(h)) return rc;
-  Host* H = h->host;
+} // extern "C" (re-opened below)
+
+namespace {
+int rhs_part(thcm_b200* h, const double* d_x, double* d_F, int part) {
   AsmArgs a = asm_args(h, d_x);
-  a.F = d_F;
+  a.F = d_F; a.part = part;
   {
     Timed t(h, 0);
     launch_rhs(a, h->stream);
     h->launches++;
   }
-  if (int rc = check_launch(h, "rhs_kernel")) return rc;
+  return check_launch(h, "rhs_kernel");
+}
+int rhs_epilogue(thcm_b200* h, const double* d_x, double* d_F) { // THCM.C:1006-1033
+  Host* H = h->host;
   const bool intc = H->cfg.sres == 0 && H->rowintcon >= 0;
-  if (intc) { // THCM.C:1006-1018
+  if (intc) {
     launch_intcond_dot(h->d_coefS, d_x, h->nrows() / 6, h->d_small + 1029, h->stream);
     h->launches++;
     if (int rc = allreduce(h, h->d_small + 1029, 1)) return rc;
@@ -353,17 +356,49 @@ int thcm_b200_rhs(thcm_b200_t* h, const double* d_x, double* d_F) {
   }
   return check_launch(h, "rhs epilogue");
 }
-
-int thcm_b200_jacobian(thcm_b200_t* h, const double* d_x) {
-  CHECK_H(h);
-  if (int rc = refresh_device(h)) return rc;
+int jac_part(thcm_b200* h, const double* d_x, int part) {
   AsmArgs a = asm_args(h, d_x);
+  a.part = part;
   {
     Timed t(h, 1);
     launch_jac(a, h->stream);
     h->launches++;
   }
   return check_launch(h, "jac_kernel");
+}
+} // namespace
+
+extern "C" {
+int thcm_b200_rhs(thcm_b200_t* h, const double* d_x, double* d_F) {
+  CHECK_H(h);
+  if (int rc = refresh_device(h)) return rc;
+  if (int rc = rhs_part(h, d_x, d_F, 0)) return rc;
+  return rhs_epilogue(h, d_x, d_F);
+}
+
+int thcm_b200_jacobian(thcm_b200_t* h, const double* d_x) {
+  CHECK_H(h);
+  if (int rc = refresh_device(h)) return rc;
+  return jac_part(h, d_x, 0);
+}
+
+// Residual and/or Jacobian on one state with the halo exchange hidden behind the tiles that do not need it.
+int thcm_b200_assemble(thcm_b200_t* h, double* d_x, double* d_F, int jacobian) {
+  CHECK_H(h);
+  if (int rc = refresh_device(h)) return rc;
+  if (!h->dist) {
+    if (d_F) { if (int rc = rhs_part(h, d_x, d_F, 0)) return rc; if (int rc = rhs_epilogue(h, d_x, d_F)) return rc; }
+    if (jacobian) if (int rc = jac_part(h, d_x, 0)) return rc;
+    return 0;
+  }
+  if (dist_halo_begin(h->dist, d_x, h->stream) != 0) return fail(IEMIC_B200_ENCCL, dist_last_error());
+  h->launches += dist_halo_launches(h->dist);
+  if (jacobian) if (int rc = jac_part(h, d_x, 1)) return rc;
+  if (d_F) if (int rc = rhs_part(h, d_x, d_F, 1)) return rc;
+  if (dist_halo_end(h->dist, h->stream) != 0) return fail(IEMIC_B200_ENCCL, dist_last_error());
+  if (jacobian) if (int rc = jac_part(h, d_x, 2)) return rc;
+  if (d_F) { if (int rc = rhs_part(h, d_x, d_F, 2)) return rc; if (int rc = rhs_epilogue(h, d_x, d_F)) return rc; }
+  return 0;
 }
 
 int thcm_b200_csr(thcm_b200_t* h, const int** rp, const int** col, double** val, const double** diagB) {
@@ -442,7 +477,12 @@ int thcm_b200_assemble_host(thcm_b200_t* h, const double* x, double* F, int jaco
     CU(cudaEventCreateWithFlags(&h->ev_copy, cudaEventDisableTiming));
   }
   CU(cudaMemcpyAsync(h->d_xs, x, nb, cudaMemcpyHostToDevice, h->stream));
-  if (int rc = thcm_b200_halo_exchange(h, h->d_xs)) return rc;
+  if (h->dist) { // several GPUs: halo exchange hidden behind the interior tiles
+    if (int rc = thcm_b200_assemble(h, h->d_xs, F ? h->d_ys : nullptr, jacobian)) return rc;
+    if (F) CU(cudaMemcpyAsync(F, h->d_ys, nb, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    return 0;
+  }
   if (F) {
     if (int rc = thcm_b200_rhs(h, h->d_xs, h->d_ys)) return rc;
     CU(cudaEventRecord(h->ev_rhs, h->stream));

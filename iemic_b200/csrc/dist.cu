@@ -78,6 +78,7 @@ struct Dist {
   double *d_sbuf = nullptr, *d_rbuf = nullptr;
   // cells exchanged with myself (periodic images when a rank is its own neighbour)
   size_t nself = 0; int *d_self_src = nullptr, *d_self_dst = nullptr;
+  cudaStream_t cs = nullptr; cudaEvent_t ev_pack = nullptr, ev_done = nullptr; // overlap path
 };
 
 Dist* dist_create(const Host& H, int rank, int nranks, const void* nccl_id) {
@@ -109,6 +110,9 @@ Dist* dist_create(const Host& H, int rank, int nranks, const void* nccl_id) {
   bool ok = up(&d->d_send, send) && up(&d->d_recv, recv) && up(&d->d_self_src, self_src) && up(&d->d_self_dst, self_dst);
   ok = ok && cudaMalloc((void**)&d->d_sbuf, (6 * std::max<size_t>(d->nsend, d->nself) + 8) * sizeof(double)) == cudaSuccess;
   ok = ok && cudaMalloc((void**)&d->d_rbuf, (6 * d->nrecv + 8) * sizeof(double)) == cudaSuccess;
+  ok = ok && cudaStreamCreateWithFlags(&d->cs, cudaStreamNonBlocking) == cudaSuccess;
+  ok = ok && cudaEventCreateWithFlags(&d->ev_pack, cudaEventDisableTiming) == cudaSuccess;
+  ok = ok && cudaEventCreateWithFlags(&d->ev_done, cudaEventDisableTiming) == cudaSuccess;
   if (!ok) { g_derr = "cudaMalloc failed in dist_create"; dist_destroy(d); return nullptr; }
   return d;
 }
@@ -118,6 +122,9 @@ void dist_destroy(Dist* d) {
   if (d->comm && N.CommDestroy) N.CommDestroy(d->comm);
   void* ptrs[] = {d->d_send, d->d_recv, d->d_sbuf, d->d_rbuf, d->d_self_src, d->d_self_dst};
   for (void* p : ptrs) if (p) cudaFree(p);
+  if (d->cs) cudaStreamDestroy(d->cs);
+  if (d->ev_pack) cudaEventDestroy(d->ev_pack);
+  if (d->ev_done) cudaEventDestroy(d->ev_done);
   delete d;
 }
 
@@ -133,12 +140,8 @@ int dist_allreduce_sum(Dist* d, double* buf, int count, cudaStream_t st) {
   return nccl_ok(N.AllReduce(buf, buf, (size_t)count, NCCL_FLOAT64, NCCL_SUM, d->comm, st), "ncclAllReduce") ? 0 : -1;
 }
 
-int dist_halo_exchange(Dist* d, double* x, cudaStream_t st) {
-  if (d->nself) { // my own periodic images
-    halo_pack_kernel<<<(int)((6 * d->nself + 255) / 256), 256, 0, st>>>(x, d->d_self_src, (int)d->nself, d->d_sbuf);
-    halo_unpack_kernel<<<(int)((6 * d->nself + 255) / 256), 256, 0, st>>>(x, d->d_self_dst, (int)d->nself, d->d_sbuf);
-  }
-  if (d->nsend) halo_pack_kernel<<<(int)((6 * d->nsend + 255) / 256), 256, 0, st>>>(x, d->d_send, (int)d->nsend, d->d_sbuf);
+namespace {
+int halo_transfers(Dist* d, double* x, cudaStream_t st) { // NCCL group + unpack, all on `st`
   if (!nccl_ok(N.GroupStart(), "ncclGroupStart")) return -1;
   for (const auto& p : d->peers) {
     if (p.ns && !nccl_ok(N.Send(d->d_sbuf + 6 * p.soff, 6 * p.ns, NCCL_FLOAT64, p.rank, d->comm, st), "ncclSend")) return -1;
@@ -146,8 +149,37 @@ int dist_halo_exchange(Dist* d, double* x, cudaStream_t st) {
   }
   if (!nccl_ok(N.GroupEnd(), "ncclGroupEnd")) return -1;
   if (d->nrecv) halo_unpack_kernel<<<(int)((6 * d->nrecv + 255) / 256), 256, 0, st>>>(x, d->d_recv, (int)d->nrecv, d->d_rbuf);
+  return 0;
+}
+int halo_pack(Dist* d, double* x, cudaStream_t st) {
+  if (d->nself) { // my own periodic images
+    halo_pack_kernel<<<(int)((6 * d->nself + 255) / 256), 256, 0, st>>>(x, d->d_self_src, (int)d->nself, d->d_sbuf);
+    halo_unpack_kernel<<<(int)((6 * d->nself + 255) / 256), 256, 0, st>>>(x, d->d_self_dst, (int)d->nself, d->d_sbuf);
+  }
+  if (d->nsend) halo_pack_kernel<<<(int)((6 * d->nsend + 255) / 256), 256, 0, st>>>(x, d->d_send, (int)d->nsend, d->d_sbuf);
+  return 0;
+}
+int halo_check(const char* what) {
   cudaError_t e = cudaGetLastError();
-  if (e != cudaSuccess) { g_derr = std::string("halo exchange: ") + cudaGetErrorString(e); return -1; }
+  if (e != cudaSuccess) { g_derr = std::string(what) + ": " + cudaGetErrorString(e); return -1; }
+  return 0;
+}
+} // namespace
+
+int dist_halo_exchange(Dist* d, double* x, cudaStream_t st) {
+  halo_pack(d, x, st);
+  if (halo_transfers(d, x, st)) return -1;
+  return halo_check("halo exchange");
+}
+int dist_halo_begin(Dist* d, double* x, cudaStream_t st) {
+  halo_pack(d, x, st);
+  if (cudaEventRecord(d->ev_pack, st) != cudaSuccess || cudaStreamWaitEvent(d->cs, d->ev_pack, 0) != cudaSuccess) return halo_check("halo begin");
+  if (halo_transfers(d, x, d->cs)) return -1;
+  if (cudaEventRecord(d->ev_done, d->cs) != cudaSuccess) return halo_check("halo begin");
+  return halo_check("halo begin");
+}
+int dist_halo_end(Dist* d, cudaStream_t st) {
+  if (cudaStreamWaitEvent(st, d->ev_done, 0) != cudaSuccess) return halo_check("halo end");
   return 0;
 }
 int dist_halo_launches(Dist* d) { return (d->nsend ? 1 : 0) + (d->nrecv ? 1 : 0) + 1 + (d->nself ? 2 : 0); }

@@ -13,5 +13,9 @@ int dist_unique_id(void* id128);
 int dist_allreduce_sum(Dist*, double* d_buf, int count, cudaStream_t st);
 int dist_halo_exchange(Dist*, double* d_x, cudaStream_t st);
 int dist_halo_launches(Dist*);
+// split form for overlap: begin() packs on `st` and runs the transfers on the communicator's own stream; end() makes `st`
+// wait for the unpacked halo.  Work enqueued on `st` in between must not touch the halo part of d_x.
+int dist_halo_begin(Dist*, double* d_x, cudaStream_t st);
+int dist_halo_end(Dist*, cudaStream_t st);
 const char* dist_last_error();
 } // namespace thcm

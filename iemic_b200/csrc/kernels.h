@@ -19,6 +19,7 @@ struct AsmArgs {
   double* F;              // residual (rhs only)
   SpecialRows sp;
   int ntx, nty, ntz;
+  int part;               // 0 every tile, 1 only tiles that read no halo cell, 2 only tiles on the block's rim
 };
 void launch_jac(const AsmArgs& a, cudaStream_t st);
 void launch_rhs(const AsmArgs& a, cudaStream_t st);

@@ -169,6 +169,10 @@ __global__ void __launch_bounds__(NTHREADS, JAC_MINB) jac_kernel(const __grid_co
   extern __shared__ double sm[];
   const Scalars& S = a.S;
   const int bx = blockIdx.x % a.ntx, by = (blockIdx.x / a.ntx) % a.nty, bz = blockIdx.x / (a.ntx * a.nty);
+  if (a.part) { // overlap with the halo exchange: rim tiles wait for it, the others do not (block-uniform exit)
+    const bool rim = bx == 0 || bx == a.ntx - 1 || by == 0 || by == a.nty - 1;
+    if (rim != (a.part == 2)) return;
+  }
   const int gi0 = S.io0 + bx * TI, gj0 = S.jo0 + by * TJ, gk0 = 1 + bz * TK;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int lj = warp % TJ, lk = warp / TJ;
@@ -238,6 +242,10 @@ __global__ void __launch_bounds__(NTHREADS, 2) rhs_kernel(const __grid_constant_
   extern __shared__ double sm[];
   const Scalars& S = a.S;
   const int bx = blockIdx.x % a.ntx, by = (blockIdx.x / a.ntx) % a.nty, bz = blockIdx.x / (a.ntx * a.nty);
+  if (a.part) { // overlap with the halo exchange: rim tiles wait for it, the others do not (block-uniform exit)
+    const bool rim = bx == 0 || bx == a.ntx - 1 || by == 0 || by == a.nty - 1;
+    if (rim != (a.part == 2)) return;
+  }
   const int gi0 = S.io0 + bx * TI, gj0 = S.jo0 + by * TJ, gk0 = 1 + bz * TK;
   stage_tile<true>(a, sm, gi0, gj0, gk0);
   __syncthreads();

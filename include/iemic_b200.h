@@ -92,6 +92,10 @@ int thcm_b200_global_ids(thcm_b200_t* h, int64_t* gid /* nvec_local */);
 int thcm_b200_rhs(thcm_b200_t* h, const double* d_x, double* d_F);   /* device pointers; d_x has nvec_local entries */
 int thcm_b200_jacobian(thcm_b200_t* h, const double* d_x);            /* fills the handle's CSR values and diag(B) */
 int thcm_b200_halo_exchange(thcm_b200_t* h, double* d_x);             /* fills the halo part of a stored vector (no-op on 1 GPU) */
+/* residual (d_F may be NULL) and/or Jacobian on one state; on several GPUs the halo exchange of d_x runs concurrently with
+ * the tiles that read no halo cell (NCCL on a second stream), the rim tiles follow.  Replaces the sequence
+ * Solve2Assembly + rhs_/matrix_ of THCM::evaluate (THCM.C:972-1058). */
+int thcm_b200_assemble(thcm_b200_t* h, double* d_x, double* d_F, int jacobian);
 int thcm_b200_csr(thcm_b200_t* h, const int** d_rowptr, const int** d_col, double** d_val, const double** d_diagB);
 int thcm_b200_graph_host(thcm_b200_t* h, int* rowptr, int* col);      /* host copies of the static graph */
 int thcm_b200_values_host(thcm_b200_t* h, double* val, double* diagB);

@@ -65,6 +65,19 @@ def main():
         d = abs(Jo - Jg)
         scale = abs(Jo).max()
         assert d.max() <= 1e-6 * scale, (name, d.max())
+        # overlapped assembly (halo exchange behind the interior tiles) must reproduce the sequential path bit for bit
+        dxs = torch.full((G.nvec,), 7.0, dtype=torch.float64, device="cuda")   # stale halo on purpose
+        dxs[:G.nrows] = torch.from_numpy(xg[own]).cuda()
+        dFs = torch.zeros(G.nvec, dtype=torch.float64, device="cuda")
+        G.set_values_host(np.zeros(G.nnz))
+        G.assemble(dxs, dFs, jacobian=True)
+        G.sync()
+        assert np.array_equal(dFs.cpu().numpy()[:G.nrows], Fg), "overlapped rhs"
+        assert np.array_equal(G.values_host()[0], vg), "overlapped jacobian"
+        Fa = np.empty(G.nrows)
+        G.set_values_host(np.zeros(G.nnz))
+        G.assemble_host(xg[own], Fa, jacobian=True)
+        assert np.array_equal(Fa, Fg) and np.array_equal(G.values_host()[0], vg), "assemble_host"
         # halo exchange on a device vector + SpMV
         v = np.random.default_rng(5).uniform(-1, 1, O.ndim)
         dv = torch.zeros(G.nvec, dtype=torch.float64, device="cuda")

@@ -235,3 +235,12 @@ def test_assemble_host_equals_separate_calls():
     G.assemble_host(x, F2, jacobian=True)
     v2, b2 = G.values_host()
     assert np.array_equal(F1, F2) and np.array_equal(v1, v2) and np.array_equal(b1, b2)
+    # device-pointer variant (thcm_b200_assemble)
+    dx = torch.zeros(G.nvec, dtype=torch.float64, device="cuda")
+    dx[:G.nrows] = torch.from_numpy(x).cuda()
+    dF = torch.zeros(G.nvec, dtype=torch.float64, device="cuda")
+    G.set_values_host(np.zeros(G.nnz))
+    G.assemble(dx, dF, jacobian=True)
+    G.sync()
+    v3, b3 = G.values_host()
+    assert np.array_equal(F1, dF.cpu().numpy()[:G.nrows]) and np.array_equal(v1, v3) and np.array_equal(b1, b3)
