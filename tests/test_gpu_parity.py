@@ -236,6 +236,7 @@ def test_assemble_host_equals_separate_calls():
     v2, b2 = G.values_host()
     assert np.array_equal(F1, F2) and np.array_equal(v1, v2) and np.array_equal(b1, b2)
     # device-pointer variant (thcm_b200_assemble)
+    import torch
     dx = torch.zeros(G.nvec, dtype=torch.float64, device="cuda")
     dx[:G.nrows] = torch.from_numpy(x).cuda()
     dF = torch.zeros(G.nvec, dtype=torch.float64, device="cuda")
