@@ -25,7 +25,7 @@ PAR = dict(AL_T=1, RAYL=2, EK_V=3, EK_H=4, ROSB=5, MIXP=6, RESC=7, SPL1=8, HMTP=
            PE_V=12, P_VC=13, LAMB=14, SALT=15, WIND=16, TEMP=17, BIOT=18, COMB=19, ARCL=20, NLES=21,
            IFRICB=22, CONT=23, ENER=24, ALPC=25, CMPR=26, FPER=27, SPER=28, MKAP=29, SPL2=30)
 
-MGS, CGS2 = 0, 1
+MGS, CGS2, CGS2F = 0, 1, 2
 PREC_NONE, PREC_BLOCKJACOBI = 0, 1
 
 

@@ -70,11 +70,11 @@ struct thcm_b200 {
 
 namespace {
 struct Timed { // RAII bracket: records a pair of events around a kernel group when timing is on
-  thcm_b200* h; int which; TimedEv ev{}; bool on;
-  Timed(thcm_b200* h_, int w) : h(h_), which(w), on(h_->timing) {
-    if (on) { ev.which = w; cudaEventCreate(&ev.a); cudaEventCreate(&ev.b); cudaEventRecord(ev.a, h->stream); }
+  thcm_b200* h; int which; TimedEv ev{}; bool on; cudaStream_t st;
+  Timed(thcm_b200* h_, int w, cudaStream_t st_ = nullptr) : h(h_), which(w), on(h_->timing), st(st_ ? st_ : h_->stream) {
+    if (on) { ev.which = w; cudaEventCreate(&ev.a); cudaEventCreate(&ev.b); cudaEventRecord(ev.a, st); }
   }
-  ~Timed() { if (on) { cudaEventRecord(ev.b, h->stream); h->evs.push_back(ev); } }
+  ~Timed() { if (on) { cudaEventRecord(ev.b, st); h->evs.push_back(ev); } }
 };
 int flush_timing(thcm_b200* h) {
   if (h->evs.empty()) return 0;
@@ -331,12 +331,13 @@ int thcm_b200_halo_exchange(thcm_b200_t* h, double* d_x) {
 } // extern "C" (re-opened below)
 
 namespace {
-int rhs_part(thcm_b200* h, const double* d_x, double* d_F, int part) {
+int rhs_part(thcm_b200* h, const double* d_x, double* d_F, int part, cudaStream_t st = nullptr) {
   AsmArgs a = asm_args(h, d_x);
   a.F = d_F; a.part = part;
+  if (!st) st = h->stream;
   {
-    Timed t(h, 0);
-    launch_rhs(a, h->stream);
+    Timed t(h, 0, st);
+    launch_rhs(a, st);
     h->launches++;
   }
   return check_launch(h, "rhs_kernel");
@@ -391,13 +392,29 @@ int thcm_b200_assemble(thcm_b200_t* h, double* d_x, double* d_F, int jacobian) {
     if (jacobian) if (int rc = jac_part(h, d_x, 0)) return rc;
     return 0;
   }
+  // stream plan: [pack] -> (side stream: NCCL transfers, unpack) || jac interior tiles
+  //              then jac rim tiles || residual kernel on a second stream (it fills the Jacobian kernel's partial waves)
+  if (!h->copy_stream) {
+    CU(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+    CU(cudaEventCreateWithFlags(&h->ev_rhs, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&h->ev_copy, cudaEventDisableTiming));
+  }
   if (dist_halo_begin(h->dist, d_x, h->stream) != 0) return fail(IEMIC_B200_ENCCL, dist_last_error());
   h->launches += dist_halo_launches(h->dist);
   if (jacobian) if (int rc = jac_part(h, d_x, 1)) return rc;
-  if (d_F) if (int rc = rhs_part(h, d_x, d_F, 1)) return rc;
   if (dist_halo_end(h->dist, h->stream) != 0) return fail(IEMIC_B200_ENCCL, dist_last_error());
-  if (jacobian) if (int rc = jac_part(h, d_x, 2)) return rc;
-  if (d_F) { if (int rc = rhs_part(h, d_x, d_F, 2)) return rc; if (int rc = rhs_epilogue(h, d_x, d_F)) return rc; }
+  if (d_F && jacobian) {
+    CU(cudaEventRecord(h->ev_rhs, h->stream));
+    CU(cudaStreamWaitEvent(h->copy_stream, h->ev_rhs, 0));
+    if (int rc = rhs_part(h, d_x, d_F, 0, h->copy_stream)) return rc;
+    CU(cudaEventRecord(h->ev_copy, h->copy_stream));
+    if (int rc = jac_part(h, d_x, 2)) return rc;
+    CU(cudaStreamWaitEvent(h->stream, h->ev_copy, 0));
+  } else {
+    if (jacobian) if (int rc = jac_part(h, d_x, 2)) return rc;
+    if (d_F) if (int rc = rhs_part(h, d_x, d_F, 0)) return rc;
+  }
+  if (d_F) if (int rc = rhs_epilogue(h, d_x, d_F)) return rc;
   return 0;
 }
 
@@ -546,6 +563,7 @@ int gmres_b200_solve(thcm_b200_t* h, const double* d_b, double* d_x, int m, int 
                      const double* d_blockinv, int check_every, double* hist_out, int* iters_out) {
   CHECK_H(h);
   if (m < 1 || m > 500) return fail(IEMIC_B200_EINVAL, "GMRES restart length must be in 1..500");
+  if (ortho != GMRES_B200_MGS && ortho != GMRES_B200_CGS2 && ortho != GMRES_B200_CGS2F) return fail(IEMIC_B200_EINVAL, "unknown orthogonalisation");
   if (prec == GMRES_B200_PREC_BLOCKJACOBI && !d_blockinv) return fail(IEMIC_B200_EINVAL, "block Jacobi needs d_blockinv");
   if (prec != GMRES_B200_PREC_NONE && prec != GMRES_B200_PREC_BLOCKJACOBI) return fail(IEMIC_B200_EINVAL, "unknown preconditioner");
   if (int rc = refresh_device(h)) return rc;
@@ -588,14 +606,24 @@ int gmres_b200_solve(thcm_b200_t* h, const double* d_b, double* d_x, int m, int 
     bool conv = false;
     for (i = 0; i < m && iter <= maxit; i++, iter++) {
       double* vi = g.V + (size_t)i * ld;
+      const bool fused = ortho == GMRES_B200_CGS2F;
+      double* w = fused ? g.V + (size_t)(i + 1) * ld : g.w; // fused mode builds v_{i+1} in place
       if (flex) {
         double* zi = g.Z + (size_t)i * ld;
         launch_block_jacobi(d_blockinv, vi, zi, n / 6, st); L();
-        if (int rc = spmv_impl(h, zi, g.w)) return rc;
-      } else if (int rc = spmv_impl(h, vi, g.w)) return rc;
+        if (int rc = spmv_impl(h, zi, w)) return rc;
+      } else if (int rc = spmv_impl(h, vi, w)) return rc;
       {
         Timed t(h, 3);
-        if (ortho == GMRES_B200_CGS2) {
+        if (fused) {
+          // two reductions per step: the second one also carries <w,w>, the norm of the twice-projected vector follows
+          // from Pythagoras, and the normalisation rides on the second update.
+          launch_multi_dot(g.V, ld, i + 1, w, n, h1, h->rb, st); L();
+          if (int rc = allreduce(h, h1, i + 1)) return rc;
+          launch_multi_axpy(g.V, ld, i + 1, h1, w, n, nullptr, h->rb, st); L();
+          launch_multi_dot(g.V, ld, i + 2, w, n, h2, h->rb, st); L();
+          if (int rc = allreduce(h, h2, i + 2)) return rc;
+        } else if (ortho == GMRES_B200_CGS2) {
           launch_multi_dot(g.V, ld, i + 1, g.w, n, h1, h->rb, st); L();
           if (int rc = allreduce(h, h1, i + 1)) return rc;
           launch_multi_axpy(g.V, ld, i + 1, h1, g.w, n, nullptr, h->rb, st); L();
@@ -612,10 +640,11 @@ int gmres_b200_solve(thcm_b200_t* h, const double* d_b, double* d_x, int m, int 
           if (int rc = allreduce(h, nrm2, 1)) return rc;
         }
         GivensArgs ga;
-        ga.H = g.H; ga.ldh = m + 1; ga.cs = g.cs; ga.sn = g.sn; ga.s = g.s; ga.h1 = h1; ga.h2 = (ortho == GMRES_B200_CGS2) ? h2 : nullptr;
-        ga.nrm2 = nrm2; ga.sq = 1; ga.bnorm = bnorm; ga.hist = g.hist; ga.hnext = hnext; ga.j = i;
+        ga.H = g.H; ga.ldh = m + 1; ga.cs = g.cs; ga.sn = g.sn; ga.s = g.s; ga.h1 = h1; ga.h2 = (ortho != GMRES_B200_MGS) ? h2 : nullptr;
+        ga.nrm2 = nrm2; ga.sq = 1; ga.pyth = fused ? 1 : 0; ga.bnorm = bnorm; ga.hist = g.hist; ga.hnext = hnext; ga.j = i;
         launch_givens(ga, st); L();
-        launch_scale_copy(g.w, g.V + (size_t)(i + 1) * ld, n, hnext, 1, 0, st); L();
+        if (fused) { launch_multi_axpy(g.V, ld, i + 1, h2, w, n, nullptr, h->rb, st, hnext); L(); }
+        else { launch_scale_copy(g.w, g.V + (size_t)(i + 1) * ld, n, hnext, 1, 0, st); L(); }
       }
       space = i; done_in_cycle = i + 1;
       if (check_every > 0 && ((i + 1) % check_every == 0)) {

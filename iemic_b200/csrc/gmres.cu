@@ -96,10 +96,11 @@ __global__ void __launch_bounds__(RT) multi_dot_kernel(const double* __restrict_
 
 __global__ void __launch_bounds__(RT) multi_axpy_kernel(const double* __restrict__ V, long long ldv, int nv, const double* __restrict__ h,
                                                         double* __restrict__ w, long long n, double* nrm2_out, double* partial,
-                                                        unsigned int* ticket) {
+                                                        unsigned int* ticket, const double* inv_scale) {
   __shared__ double hs[MAXV];
   for (int k = threadIdx.x; k < nv; k += RT) hs[k] = h[k];
   __syncthreads();
+  const double sc = inv_scale ? 1.0 / *inv_scale : 1.0; // fused normalisation v_{j+1} = w / H(j+1,j)
   const long long n2 = n >> 1;
   double2* w2 = reinterpret_cast<double2*>(w);
   double acc[1] = {0.0};
@@ -114,6 +115,7 @@ __global__ void __launch_bounds__(RT) multi_axpy_kernel(const double* __restrict
       for (int k = 0; k < KT; k++)
         if (k0 + k < nv) { wv.x = fma(-hs[k0 + k], v[k].x, wv.x); wv.y = fma(-hs[k0 + k], v[k].y, wv.y); }
     }
+    if (inv_scale) { wv.x = sc * wv.x; wv.y = sc * wv.y; }
     w2[i] = wv;
     acc[0] = fma(wv.y, wv.y, fma(wv.x, wv.x, acc[0]));
   }
@@ -227,7 +229,12 @@ __global__ void givens_kernel(const GivensArgs g) {
   const int j = g.j;
   double* Hc = g.H + (size_t)j * g.ldh;
   for (int k = 0; k <= j; k++) Hc[k] = g.h1[k] + (g.h2 ? g.h2[k] : 0.0);
-  double nrm = g.sq ? sqrt(*g.nrm2) : *g.nrm2;
+  double nrm;
+  if (g.pyth) { // ||w - V h2||^2 = ||w||^2 - |h2|^2 for orthonormal V: h2[j+1] carries <w,w> from the same reduction
+    double hh = 0.0;
+    for (int k = 0; k <= j; k++) hh = fma(g.h2[k], g.h2[k], hh);
+    nrm = sqrt(fmax(g.h2[j + 1] - hh, 0.0));
+  } else nrm = g.sq ? sqrt(*g.nrm2) : *g.nrm2;
   Hc[j + 1] = nrm;
   *g.hnext = nrm;
   for (int k = 0; k < j; k++) app_rot(Hc[k], Hc[k + 1], g.cs[k], g.sn[k]);
@@ -276,8 +283,9 @@ int red_blocks() {
 void launch_multi_dot(const double* V, long long ldv, int nv, const double* w, long long n, double* out, RedBuf rb, cudaStream_t st) {
   multi_dot_kernel<<<grid_for(n), RT, 0, st>>>(V, ldv, nv, w, n, out, rb.partial, rb.ticket);
 }
-void launch_multi_axpy(const double* V, long long ldv, int nv, const double* h, double* w, long long n, double* nrm2_out, RedBuf rb, cudaStream_t st) {
-  multi_axpy_kernel<<<grid_for(n), RT, 0, st>>>(V, ldv, nv, h, w, n, nrm2_out, rb.partial, rb.ticket);
+void launch_multi_axpy(const double* V, long long ldv, int nv, const double* h, double* w, long long n, double* nrm2_out, RedBuf rb, cudaStream_t st,
+                       const double* inv_scale) {
+  multi_axpy_kernel<<<grid_for(n), RT, 0, st>>>(V, ldv, nv, h, w, n, nrm2_out, rb.partial, rb.ticket, inv_scale);
 }
 void launch_axpy_dot(const double* hprev, const double* vprev, const double* vnext, double* w, long long n, double* out, RedBuf rb, cudaStream_t st) {
   axpy_dot_kernel<<<grid_for(n), RT, 0, st>>>(hprev, vprev, vnext, w, n, out, rb.partial, rb.ticket);

@@ -48,7 +48,7 @@ int red_blocks();
 void launch_multi_dot(const double* V, long long ldv, int nv, const double* w, long long n, double* out, RedBuf rb, cudaStream_t st);
 // w -= sum_k h[k] V_k ; optionally hacc[k] += h[k] ; optionally nrm2_out = ||w_new||^2
 void launch_multi_axpy(const double* V, long long ldv, int nv, const double* h, double* w, long long n,
-                       double* nrm2_out, RedBuf rb, cudaStream_t st);
+                       double* nrm2_out, RedBuf rb, cudaStream_t st, const double* inv_scale = nullptr /* w /= *inv_scale afterwards */);
 // MGS fused step: if (hprev) w -= hprev[0]*vprev ; out = <w, vnext> (vnext may be null: then out = <w,w>)
 void launch_axpy_dot(const double* hprev, const double* vprev, const double* vnext, double* w, long long n, double* out, RedBuf rb, cudaStream_t st);
 void launch_dot(const double* a, const double* b, long long n, double* out, RedBuf rb, cudaStream_t st);
@@ -71,6 +71,7 @@ struct GivensArgs {
   const double* h1; const double* h2; // h2 may be null
   const double* nrm2;          // squared norm of w (or norm if !sq)
   int sq;
+  int pyth;                    // norm from h2: sqrt(h2[j+1] - sum_k h2[k]^2), h2[j+1] = <w,w> before the second projection
   const double* bnorm;         // device scalar: ||b||
   double* hist;
   double* hnext;               // receives H[j+1][j] (the norm) for the normalisation kernel

@@ -57,7 +57,7 @@ typedef struct {
 } thcm_b200_config;
 
 enum { IEMIC_B200_OK = 0, IEMIC_B200_EINVAL = -1, IEMIC_B200_ECUDA = -2, IEMIC_B200_ENOTSUP = -3, IEMIC_B200_ENCCL = -4 };
-enum { GMRES_B200_MGS = 0, GMRES_B200_CGS2 = 1 };
+enum { GMRES_B200_MGS = 0, GMRES_B200_CGS2 = 1, GMRES_B200_CGS2F = 2 };
 enum { GMRES_B200_PREC_NONE = 0, GMRES_B200_PREC_BLOCKJACOBI = 1 };
 
 const char* iemic_b200_last_error(void);
@@ -123,7 +123,9 @@ int vec_b200_putscalar(thcm_b200_t* h, double a, double* d_this);
 
 /* ---- GMRES(m) on the handle's Jacobian (GMRESSolver.H:81-255) ----
  * ortho: GMRES_B200_MGS reproduces the reference's modified Gram-Schmidt loop (:177-181); GMRES_B200_CGS2 is the
- * fused two-pass classical Gram-Schmidt.  prec: right (flexible) preconditioner; BLOCKJACOBI takes nrows_local/6
+ * fused two-pass classical Gram-Schmidt (three reductions per step: h1, h2, norm); GMRES_B200_CGS2F is the same
+ * projection with two reductions per step (the second also returns <w,w>, the new norm follows from Pythagoras and
+ * the normalisation is fused into the second update: 6 kernels and 2 allreduces per Arnoldi step).  prec: right (flexible) preconditioner; BLOCKJACOBI takes nrows_local/6
  * inverted 6x6 blocks, row-major, in d_blockinv.  hist[it] receives resid_ after inner iteration it
  * (length >= maxit+1).  check_every: 1 tests convergence every iteration like the reference; 0 never leaves the
  * device until the cycle ends (fixed iteration count).  Return value: 0 converged, 1 not converged (like solve()). */

@@ -98,7 +98,7 @@ def main():
         m = 12
         rc_o, xo, ho, it_o = ol.gmres(rpo, colo, vo, b_full, np.zeros(O.ndim), m, m - 1, 0.0)
         db = torch.from_numpy(b_full[own]).cuda()
-        for ortho, tol in ((ib.MGS, 1e-9), (ib.CGS2, 1e-8)):
+        for ortho, tol in ((ib.MGS, 1e-9), (ib.CGS2, 1e-8), (ib.CGS2F, 1e-8)):
             dxs = torch.zeros(G.nvec, dtype=torch.float64, device="cuda")
             rc, hist, it = G.solve(db, dxs, m=m, maxit=m - 1, tol=0.0, ortho=ortho, check_every=0)
             assert it == it_o

@@ -94,7 +94,7 @@ def _blockinv(rp, col, val, nrows):
 
 
 @pytest.mark.parametrize("name", ["natl8_sres1", "rand_periodic", "global_half"])
-@pytest.mark.parametrize("ortho", ["mgs", "cgs2"])
+@pytest.mark.parametrize("ortho", ["mgs", "cgs2", "cgs2f"])
 @pytest.mark.parametrize("prec", [0, 1])
 def test_gmres_history(name, ortho, prec):
     import oracle_lib as ol
@@ -107,7 +107,7 @@ def test_gmres_history(name, ortho, prec):
     m = 20
     binv = _blockinv(rp, col, vg, G.nrows) if prec else None
     rc_o, xo, ho, it_o = ol.gmres(rp, col, vg, b, np.zeros(G.nrows), m, m - 1, 0.0, blockinv=binv)
-    rc_g, xg, hg, it_g = G.solve_host(b, m=m, maxit=m - 1, tol=0.0, ortho=ib.MGS if ortho == "mgs" else ib.CGS2,
+    rc_g, xg, hg, it_g = G.solve_host(b, m=m, maxit=m - 1, tol=0.0, ortho={"mgs": ib.MGS, "cgs2": ib.CGS2, "cgs2f": ib.CGS2F}[ortho],
                                       prec=prec, blockinv=binv, check_every=0)
     assert it_o == it_g
     ho, hg = ho[:m + 1], hg[:m + 1]
