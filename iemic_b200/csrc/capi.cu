@@ -3,6 +3,7 @@
 // per-parameter-change setup delegated to thcm::Host (thcm_host.cpp).
 #include <cuda_runtime.h>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <cmath>
 #include <string>
@@ -194,8 +195,11 @@ void gmres_free(GmresWs& g) {
   g.m = 0;
 }
 // allreduce helper: no-op on one GPU
-int allreduce(thcm_b200* h, double* d, int count) {
-  if (!h->dist) return 0;
+// Reductions across ranks: with the peer-memory path the reducing kernel finishes the sum itself (argument block from
+// red()); otherwise ncclAllReduce follows the kernel.
+PeerRed red(thcm_b200* h) { return dist_next_red(h->dist); }
+int allreduce(thcm_b200* h, double* d, int count, const PeerRed& pr = PeerRed{}) {
+  if (!h->dist || pr.nranks) return 0;
   h->launches++;
   return dist_allreduce_sum(h->dist, d, count, h->stream) == 0 ? 0 : fail(IEMIC_B200_ENCCL, dist_last_error());
 }
@@ -383,6 +387,11 @@ int thcm_b200_jacobian(thcm_b200_t* h, const double* d_x) {
   return jac_part(h, d_x, 0);
 }
 
+int thcm_b200_exchange_mode(thcm_b200_t* h) {
+  if (!h) return -1;
+  return !h->dist ? 0 : (dist_p2p(h->dist) ? 2 : 1);
+}
+
 // Residual and/or Jacobian on one state with the halo exchange hidden behind the tiles that do not need it.
 int thcm_b200_assemble(thcm_b200_t* h, double* d_x, double* d_F, int jacobian) {
   CHECK_H(h);
@@ -392,26 +401,32 @@ int thcm_b200_assemble(thcm_b200_t* h, double* d_x, double* d_F, int jacobian) {
     if (jacobian) if (int rc = jac_part(h, d_x, 0)) return rc;
     return 0;
   }
-  // stream plan: [pack] -> (side stream: NCCL transfers, unpack) || jac interior tiles
-  //              then jac rim tiles || residual kernel on a second stream (it fills the Jacobian kernel's partial waves)
-  if (!h->copy_stream) {
+  // Plans (IEMIC_ASM_PLAN, default 0):
+  //   0  halo exchange, Jacobian, residual, one after the other on the handle's stream
+  //   1  halo exchange, then the residual kernel on a second stream beside the Jacobian kernel (fills its partial waves)
+  //   2  halo exchange started, Jacobian tiles that read no halo cell, exchange finished, rim tiles beside the residual
+  const int plan_env = getenv("IEMIC_ASM_PLAN") ? atoi(getenv("IEMIC_ASM_PLAN")) : 0;
+  const int plan = (d_F && jacobian) ? plan_env : (plan_env == 2 && jacobian ? 2 : 0);
+  if (plan != 0 && !h->copy_stream) {
     CU(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
     CU(cudaEventCreateWithFlags(&h->ev_rhs, cudaEventDisableTiming));
     CU(cudaEventCreateWithFlags(&h->ev_copy, cudaEventDisableTiming));
   }
-  if (dist_halo_begin(h->dist, d_x, h->stream) != 0) return fail(IEMIC_B200_ENCCL, dist_last_error());
   h->launches += dist_halo_launches(h->dist);
-  if (jacobian) if (int rc = jac_part(h, d_x, 1)) return rc;
-  if (dist_halo_end(h->dist, h->stream) != 0) return fail(IEMIC_B200_ENCCL, dist_last_error());
-  if (d_F && jacobian) {
+  if (plan == 2) {
+    if (dist_halo_begin(h->dist, d_x, h->stream) != 0) return fail(IEMIC_B200_ENCCL, dist_last_error());
+    if (int rc = jac_part(h, d_x, 1)) return rc;
+    if (dist_halo_end(h->dist, h->stream) != 0) return fail(IEMIC_B200_ENCCL, dist_last_error());
+  } else if (dist_halo_exchange(h->dist, d_x, h->stream) != 0) return fail(IEMIC_B200_ENCCL, dist_last_error());
+  if (plan != 0 && d_F) {
     CU(cudaEventRecord(h->ev_rhs, h->stream));
     CU(cudaStreamWaitEvent(h->copy_stream, h->ev_rhs, 0));
     if (int rc = rhs_part(h, d_x, d_F, 0, h->copy_stream)) return rc;
     CU(cudaEventRecord(h->ev_copy, h->copy_stream));
-    if (int rc = jac_part(h, d_x, 2)) return rc;
+    if (int rc = jac_part(h, d_x, plan == 2 ? 2 : 0)) return rc;
     CU(cudaStreamWaitEvent(h->stream, h->ev_copy, 0));
   } else {
-    if (jacobian) if (int rc = jac_part(h, d_x, 2)) return rc;
+    if (jacobian) if (int rc = jac_part(h, d_x, plan == 2 ? 2 : 0)) return rc;
     if (d_F) if (int rc = rhs_part(h, d_x, d_F, 0)) return rc;
   }
   if (d_F) if (int rc = rhs_epilogue(h, d_x, d_F)) return rc;
@@ -532,9 +547,10 @@ int thcm_b200_spmv_host(thcm_b200_t* h, const double* x, double* y) {
 // ---- vectors ----
 int vec_b200_dot(thcm_b200_t* h, const double* a, const double* b, double* result) {
   CHECK_H(h);
-  launch_dot(a, b, h->nrows(), h->d_small + 1028, h->rb, h->stream);
+  const PeerRed pr = red(h);
+  launch_dot(a, b, h->nrows(), h->d_small + 1028, h->rb, h->stream, pr);
   h->launches++;
-  if (int rc = allreduce(h, h->d_small + 1028, 1)) return rc;
+  if (int rc = allreduce(h, h->d_small + 1028, 1, pr)) return rc;
   CU(cudaMemcpyAsync(result, h->d_small + 1028, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
   CU(cudaStreamSynchronize(h->stream));
   return 0;
@@ -577,8 +593,8 @@ int gmres_b200_solve(thcm_b200_t* h, const double* d_b, double* d_x, int m, int 
   auto L = [&](int k = 1) { h->launches += k; };
 
   // normb
-  launch_dot(d_b, d_b, n, nrm2, h->rb, st); L();
-  if (int rc = allreduce(h, nrm2, 1)) return rc;
+  { const PeerRed pr = red(h); launch_dot(d_b, d_b, n, nrm2, h->rb, st, pr); L();
+  if (int rc = allreduce(h, nrm2, 1, pr)) return rc; }
   launch_sqrt_store(nrm2, bnorm, st); L();
   double normb = 0.0;
   CU(cudaMemcpyAsync(&normb, bnorm, sizeof(double), cudaMemcpyDeviceToHost, st));
@@ -588,8 +604,8 @@ int gmres_b200_solve(thcm_b200_t* h, const double* d_b, double* d_x, int m, int 
   CU(cudaMemcpyAsync(g.tmp, d_x, n * sizeof(double), cudaMemcpyDeviceToDevice, st));
   if (int rc = spmv_impl(h, g.tmp, g.r)) return rc;
   launch_residual(d_b, g.r, n, st); L();
-  launch_dot(g.r, g.r, n, nrm2, h->rb, st); L();
-  if (int rc = allreduce(h, nrm2, 1)) return rc;
+  { const PeerRed pr = red(h); launch_dot(g.r, g.r, n, nrm2, h->rb, st, pr); L();
+  if (int rc = allreduce(h, nrm2, 1, pr)) return rc; }
   double r2 = 0.0;
   CU(cudaMemcpyAsync(&r2, nrm2, sizeof(double), cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
@@ -618,26 +634,26 @@ int gmres_b200_solve(thcm_b200_t* h, const double* d_b, double* d_x, int m, int 
         if (fused) {
           // two reductions per step: the second one also carries <w,w>, the norm of the twice-projected vector follows
           // from Pythagoras, and the normalisation rides on the second update.
-          launch_multi_dot(g.V, ld, i + 1, w, n, h1, h->rb, st); L();
-          if (int rc = allreduce(h, h1, i + 1)) return rc;
+          { const PeerRed pr = red(h); launch_multi_dot(g.V, ld, i + 1, w, n, h1, h->rb, st, pr); L();
+          if (int rc = allreduce(h, h1, i + 1, pr)) return rc; }
           launch_multi_axpy(g.V, ld, i + 1, h1, w, n, nullptr, h->rb, st); L();
-          launch_multi_dot(g.V, ld, i + 2, w, n, h2, h->rb, st); L();
-          if (int rc = allreduce(h, h2, i + 2)) return rc;
+          { const PeerRed pr = red(h); launch_multi_dot(g.V, ld, i + 2, w, n, h2, h->rb, st, pr); L();
+          if (int rc = allreduce(h, h2, i + 2, pr)) return rc; }
         } else if (ortho == GMRES_B200_CGS2) {
-          launch_multi_dot(g.V, ld, i + 1, g.w, n, h1, h->rb, st); L();
-          if (int rc = allreduce(h, h1, i + 1)) return rc;
+          { const PeerRed pr = red(h); launch_multi_dot(g.V, ld, i + 1, g.w, n, h1, h->rb, st, pr); L();
+          if (int rc = allreduce(h, h1, i + 1, pr)) return rc; }
           launch_multi_axpy(g.V, ld, i + 1, h1, g.w, n, nullptr, h->rb, st); L();
-          launch_multi_dot(g.V, ld, i + 1, g.w, n, h2, h->rb, st); L();
-          if (int rc = allreduce(h, h2, i + 1)) return rc;
-          launch_multi_axpy(g.V, ld, i + 1, h2, g.w, n, nrm2, h->rb, st); L();
-          if (int rc = allreduce(h, nrm2, 1)) return rc;
+          { const PeerRed pr = red(h); launch_multi_dot(g.V, ld, i + 1, g.w, n, h2, h->rb, st, pr); L();
+          if (int rc = allreduce(h, h2, i + 1, pr)) return rc; }
+          { const PeerRed pr = red(h); launch_multi_axpy(g.V, ld, i + 1, h2, g.w, n, nrm2, h->rb, st, nullptr, pr); L();
+          if (int rc = allreduce(h, nrm2, 1, pr)) return rc; }
         } else { // MGS, dependent chain exactly as GMRESSolver.H:177-181
           for (int k = 0; k <= i; k++) {
-            launch_axpy_dot(k ? h1 + k - 1 : nullptr, k ? g.V + (size_t)(k - 1) * ld : nullptr, g.V + (size_t)k * ld, g.w, n, h1 + k, h->rb, st); L();
-            if (int rc = allreduce(h, h1 + k, 1)) return rc;
+            { const PeerRed pr = red(h); launch_axpy_dot(k ? h1 + k - 1 : nullptr, k ? g.V + (size_t)(k - 1) * ld : nullptr, g.V + (size_t)k * ld, g.w, n, h1 + k, h->rb, st, pr); L();
+            if (int rc = allreduce(h, h1 + k, 1, pr)) return rc; }
           }
-          launch_axpy_dot(h1 + i, g.V + (size_t)i * ld, nullptr, g.w, n, nrm2, h->rb, st); L();
-          if (int rc = allreduce(h, nrm2, 1)) return rc;
+          { const PeerRed pr = red(h); launch_axpy_dot(h1 + i, g.V + (size_t)i * ld, nullptr, g.w, n, nrm2, h->rb, st, pr); L();
+          if (int rc = allreduce(h, nrm2, 1, pr)) return rc; }
         }
         GivensArgs ga;
         ga.H = g.H; ga.ldh = m + 1; ga.cs = g.cs; ga.sn = g.sn; ga.s = g.s; ga.h1 = h1; ga.h2 = (ortho != GMRES_B200_MGS) ? h2 : nullptr;
@@ -667,8 +683,8 @@ int gmres_b200_solve(thcm_b200_t* h, const double* d_b, double* d_x, int m, int 
     CU(cudaMemcpyAsync(g.tmp, d_x, n * sizeof(double), cudaMemcpyDeviceToDevice, st));
     if (int rc = spmv_impl(h, g.tmp, g.r)) return rc;
     launch_residual(d_b, g.r, n, st); L();
-    launch_dot(g.r, g.r, n, nrm2, h->rb, st); L();
-    if (int rc = allreduce(h, nrm2, 1)) return rc;
+    { const PeerRed pr = red(h); launch_dot(g.r, g.r, n, nrm2, h->rb, st, pr); L();
+    if (int rc = allreduce(h, nrm2, 1, pr)) return rc; }
     if (conv) { ret = 0; break; }
   }
   CU(cudaMemcpyAsync(&r2, nrm2, sizeof(double), cudaMemcpyDeviceToHost, st));

@@ -4,6 +4,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include "thcm_host.h"
+#include "peer.cuh"
 
 namespace thcm {
 struct Dist;
@@ -17,5 +18,10 @@ int dist_halo_launches(Dist*);
 // wait for the unpacked halo.  Work enqueued on `st` in between must not touch the halo part of d_x.
 int dist_halo_begin(Dist*, double* d_x, cudaStream_t st);
 int dist_halo_end(Dist*, cudaStream_t st);
+// peer-memory path (peer.cuh): true when every rank mapped every other rank's box; dist_next_red() then hands out the
+// argument block that makes a reducing kernel finish the sum across ranks itself (nranks == 0: not available, use
+// dist_allreduce_sum after the kernel).  Every rank must request them in the same order.
+bool dist_p2p(const Dist*);
+PeerRed dist_next_red(Dist*);
 const char* dist_last_error();
 } // namespace thcm

@@ -71,7 +71,7 @@ __device__ __forceinline__ void final_sum(const double* partial, int stride, int
 }
 
 __global__ void __launch_bounds__(RT) multi_dot_kernel(const double* __restrict__ V, long long ldv, int nv, const double* __restrict__ w,
-                                                       long long n, double* out, double* partial, unsigned int* ticket) {
+                                                       long long n, double* out, double* partial, unsigned int* ticket, const PeerRed pr) {
   const long long n2 = n >> 1; // double2 elements (n is even: 6 unknowns per cell)
   const double2* w2 = reinterpret_cast<const double2*>(w);
   for (int k0 = 0; k0 < nv; k0 += KT) {
@@ -91,12 +91,15 @@ __global__ void __launch_bounds__(RT) multi_dot_kernel(const double* __restrict_
     }
     block_publish<KT>(acc, nk, partial, MAXV, k0);
   }
-  if (last_block(ticket)) final_sum(partial, MAXV, nv, out);
+  if (last_block(ticket)) {
+    final_sum(partial, MAXV, nv, out);
+    if (pr.nranks) peer_allreduce_block(pr, out, nv);
+  }
 }
 
 __global__ void __launch_bounds__(RT) multi_axpy_kernel(const double* __restrict__ V, long long ldv, int nv, const double* __restrict__ h,
                                                         double* __restrict__ w, long long n, double* nrm2_out, double* partial,
-                                                        unsigned int* ticket, const double* inv_scale) {
+                                                        unsigned int* ticket, const double* inv_scale, const PeerRed pr) {
   __shared__ double hs[MAXV];
   for (int k = threadIdx.x; k < nv; k += RT) hs[k] = h[k];
   __syncthreads();
@@ -121,13 +124,16 @@ __global__ void __launch_bounds__(RT) multi_axpy_kernel(const double* __restrict
   }
   if (nrm2_out) {
     block_publish<1>(acc, 1, partial, MAXV, 0);
-    if (last_block(ticket)) final_sum(partial, MAXV, 1, nrm2_out);
+    if (last_block(ticket)) {
+      final_sum(partial, MAXV, 1, nrm2_out);
+      if (pr.nranks) peer_allreduce_block(pr, nrm2_out, 1);
+    }
   }
 }
 
 __global__ void __launch_bounds__(RT) axpy_dot_kernel(const double* __restrict__ hprev, const double* __restrict__ vprev,
                                                       const double* __restrict__ vnext, double* __restrict__ w, long long n, double* out,
-                                                      double* partial, unsigned int* ticket) {
+                                                      double* partial, unsigned int* ticket, const PeerRed pr) {
   const long long n2 = n >> 1;
   double2* w2 = reinterpret_cast<double2*>(w);
   const double hp = hprev ? *hprev : 0.0;
@@ -143,11 +149,14 @@ __global__ void __launch_bounds__(RT) axpy_dot_kernel(const double* __restrict__
     acc[0] = fma(wv.y, vn.y, fma(wv.x, vn.x, acc[0]));
   }
   block_publish<1>(acc, 1, partial, MAXV, 0);
-  if (last_block(ticket)) final_sum(partial, MAXV, 1, out);
+  if (last_block(ticket)) {
+    final_sum(partial, MAXV, 1, out);
+    if (pr.nranks) peer_allreduce_block(pr, out, 1);
+  }
 }
 
 __global__ void __launch_bounds__(RT) dot_kernel(const double* __restrict__ a, const double* __restrict__ b, long long n, double* out,
-                                                 double* partial, unsigned int* ticket) {
+                                                 double* partial, unsigned int* ticket, const PeerRed pr) {
   const long long n2 = n >> 1;
   double acc[1] = {0.0};
   for (long long i = (long long)blockIdx.x * RT + threadIdx.x; i < n2; i += (long long)gridDim.x * RT) {
@@ -155,7 +164,10 @@ __global__ void __launch_bounds__(RT) dot_kernel(const double* __restrict__ a, c
     acc[0] = fma(x.y, y.y, fma(x.x, y.x, acc[0]));
   }
   block_publish<1>(acc, 1, partial, MAXV, 0);
-  if (last_block(ticket)) final_sum(partial, MAXV, 1, out);
+  if (last_block(ticket)) {
+    final_sum(partial, MAXV, 1, out);
+    if (pr.nranks) peer_allreduce_block(pr, out, 1);
+  }
 }
 
 __global__ void __launch_bounds__(RT) scale_copy_kernel(const double* __restrict__ x, double* __restrict__ y, long long n, const double* s, int inv, int sq) {
@@ -280,18 +292,18 @@ int red_blocks() {
   return g_red_blocks;
 }
 
-void launch_multi_dot(const double* V, long long ldv, int nv, const double* w, long long n, double* out, RedBuf rb, cudaStream_t st) {
-  multi_dot_kernel<<<grid_for(n), RT, 0, st>>>(V, ldv, nv, w, n, out, rb.partial, rb.ticket);
+void launch_multi_dot(const double* V, long long ldv, int nv, const double* w, long long n, double* out, RedBuf rb, cudaStream_t st, const PeerRed& pr) {
+  multi_dot_kernel<<<grid_for(n), RT, 0, st>>>(V, ldv, nv, w, n, out, rb.partial, rb.ticket, pr);
 }
 void launch_multi_axpy(const double* V, long long ldv, int nv, const double* h, double* w, long long n, double* nrm2_out, RedBuf rb, cudaStream_t st,
-                       const double* inv_scale) {
-  multi_axpy_kernel<<<grid_for(n), RT, 0, st>>>(V, ldv, nv, h, w, n, nrm2_out, rb.partial, rb.ticket, inv_scale);
+                       const double* inv_scale, const PeerRed& pr) {
+  multi_axpy_kernel<<<grid_for(n), RT, 0, st>>>(V, ldv, nv, h, w, n, nrm2_out, rb.partial, rb.ticket, inv_scale, pr);
 }
-void launch_axpy_dot(const double* hprev, const double* vprev, const double* vnext, double* w, long long n, double* out, RedBuf rb, cudaStream_t st) {
-  axpy_dot_kernel<<<grid_for(n), RT, 0, st>>>(hprev, vprev, vnext, w, n, out, rb.partial, rb.ticket);
+void launch_axpy_dot(const double* hprev, const double* vprev, const double* vnext, double* w, long long n, double* out, RedBuf rb, cudaStream_t st, const PeerRed& pr) {
+  axpy_dot_kernel<<<grid_for(n), RT, 0, st>>>(hprev, vprev, vnext, w, n, out, rb.partial, rb.ticket, pr);
 }
-void launch_dot(const double* a, const double* b, long long n, double* out, RedBuf rb, cudaStream_t st) {
-  dot_kernel<<<grid_for(n), RT, 0, st>>>(a, b, n, out, rb.partial, rb.ticket);
+void launch_dot(const double* a, const double* b, long long n, double* out, RedBuf rb, cudaStream_t st, const PeerRed& pr) {
+  dot_kernel<<<grid_for(n), RT, 0, st>>>(a, b, n, out, rb.partial, rb.ticket, pr);
 }
 void launch_scale_copy(const double* x, double* y, long long n, const double* s, int inv, int sq, cudaStream_t st) {
   scale_copy_kernel<<<grid_for(n), RT, 0, st>>>(x, y, n, s, inv, sq);

@@ -4,6 +4,7 @@
 #include <stdint.h>
 #include "thcm_rows.cuh"
 #include "thcm_cell.cuh"
+#include "peer.cuh"
 
 namespace thcm {
 
@@ -44,14 +45,19 @@ int spmv_rows_cap();
 // ---- vector / GMRES kernels (gmres.cu) ----
 struct RedBuf { double* partial; unsigned int* ticket; int nblk_max; }; // workspace for block-partial reductions
 int red_blocks();
-// out[k] = <V_k, w>, k = 0..nv-1 (V_k = V + k*ldv), deterministic two-stage reduction finished by the last block
-void launch_multi_dot(const double* V, long long ldv, int nv, const double* w, long long n, double* out, RedBuf rb, cudaStream_t st);
+// out[k] = <V_k, w>, k = 0..nv-1 (V_k = V + k*ldv), deterministic two-stage reduction finished by the last block.
+// With pr.nranks > 0 the finishing block also sums over the ranks through peer memory (peer.cuh); this holds for every
+// reducing kernel below.
+void launch_multi_dot(const double* V, long long ldv, int nv, const double* w, long long n, double* out, RedBuf rb, cudaStream_t st,
+                      const PeerRed& pr = PeerRed{});
 // w -= sum_k h[k] V_k ; optionally hacc[k] += h[k] ; optionally nrm2_out = ||w_new||^2
 void launch_multi_axpy(const double* V, long long ldv, int nv, const double* h, double* w, long long n,
-                       double* nrm2_out, RedBuf rb, cudaStream_t st, const double* inv_scale = nullptr /* w /= *inv_scale afterwards */);
+                       double* nrm2_out, RedBuf rb, cudaStream_t st, const double* inv_scale = nullptr /* w /= *inv_scale afterwards */,
+                       const PeerRed& pr = PeerRed{});
 // MGS fused step: if (hprev) w -= hprev[0]*vprev ; out = <w, vnext> (vnext may be null: then out = <w,w>)
-void launch_axpy_dot(const double* hprev, const double* vprev, const double* vnext, double* w, long long n, double* out, RedBuf rb, cudaStream_t st);
-void launch_dot(const double* a, const double* b, long long n, double* out, RedBuf rb, cudaStream_t st);
+void launch_axpy_dot(const double* hprev, const double* vprev, const double* vnext, double* w, long long n, double* out, RedBuf rb, cudaStream_t st,
+                     const PeerRed& pr = PeerRed{});
+void launch_dot(const double* a, const double* b, long long n, double* out, RedBuf rb, cudaStream_t st, const PeerRed& pr = PeerRed{});
 // y = alpha * x with alpha = (inv ? 1/s[0] : s[0]) read on the device ; s may be sqrt'ed first (sq: s[0] holds a squared norm)
 void launch_scale_copy(const double* x, double* y, long long n, const double* s, int inv, int sq, cudaStream_t st);
 void launch_update(double a, const double* A, double b, double* y, long long n, cudaStream_t st); // y = a*A + b*y

@@ -91,7 +91,11 @@ int thcm_b200_global_ids(thcm_b200_t* h, int64_t* gid /* nvec_local */);
 /* ---- assembly ---- */
 int thcm_b200_rhs(thcm_b200_t* h, const double* d_x, double* d_F);   /* device pointers; d_x has nvec_local entries */
 int thcm_b200_jacobian(thcm_b200_t* h, const double* d_x);            /* fills the handle's CSR values and diag(B) */
-int thcm_b200_halo_exchange(thcm_b200_t* h, double* d_x);             /* fills the halo part of a stored vector (no-op on 1 GPU) */
+int thcm_b200_halo_exchange(thcm_b200_t* h, double* d_x);
+/* how the exchange steps travel: 0 one GPU (nothing to exchange), 1 NCCL send/recv + allreduce, 2 peer memory over
+ * NVLink (CUDA IPC; halo push/pull kernels, reductions finished inside the reducing kernels).  Mode 2 is chosen when
+ * every rank can map every other rank's buffers; IEMIC_P2P=0 in the environment forces mode 1. */
+int thcm_b200_exchange_mode(thcm_b200_t* h);             /* fills the halo part of a stored vector (no-op on 1 GPU) */
 /* residual (d_F may be NULL) and/or Jacobian on one state; on several GPUs the halo exchange of d_x runs concurrently with
  * the tiles that read no halo cell (NCCL on a second stream), the rim tiles follow.  Replaces the sequence
  * Solve2Assembly + rhs_/matrix_ of THCM::evaluate (THCM.C:972-1058). */

@@ -38,6 +38,8 @@ def main():
             nccl_id = idbuf.cpu().numpy().copy()
         first = False
         G = ib.Ocean(cfg, mask, rank=rank, nranks=world, nccl_id=nccl_id)
+        mode = G.exchange_mode()
+        assert mode == (1 if os.environ.get("IEMIC_P2P") == "0" else mode)
         O = ol.Oracle(cfg, mask)
         for k, v in pars.items():
             G.setPar(k, v)
@@ -104,7 +106,7 @@ def main():
             assert it == it_o
             assert np.all(np.abs(hist[:m] - ho[:m]) <= tol * np.abs(ho[:m]) + 1e-13), (name, hist[:m], ho[:m])
         G.close()
-    print("rank %d ok" % rank, flush=True)
+    print("rank %d ok (exchange mode %d)" % (rank, mode), flush=True)
     dist.destroy_process_group()
 
 

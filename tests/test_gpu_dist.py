@@ -13,14 +13,19 @@ def _ngpu():
     return torch.cuda.device_count()
 
 
+@pytest.mark.parametrize("p2p", ["peer", "nccl"])
 @pytest.mark.parametrize("nproc", [2, 4, 8])
-def test_multi_gpu_parity(nproc):
+def test_multi_gpu_parity(nproc, p2p):
+    """Both exchange paths: peer memory over NVLink (the default when CUDA IPC is available) and NCCL."""
     if _ngpu() < nproc:
         pytest.skip("needs %d GPUs" % nproc)
     here = os.path.dirname(os.path.abspath(__file__))
+    env = dict(os.environ, IEMIC_P2P="1" if p2p == "peer" else "0", IEMIC_DEBUG="1")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(nproc), "--master-addr", "127.0.0.1",
-           "--master-port", str(29600 + nproc), os.path.join(here, "dist_gpu_worker.py")]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
+           "--master-port", str(29600 + nproc + (10 if p2p == "nccl" else 0)), os.path.join(here, "dist_gpu_worker.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     for k in range(nproc):
         assert "rank %d ok" % k in r.stdout
+    if p2p == "nccl":
+        assert "peer-memory exchange on" not in r.stderr

@@ -55,13 +55,16 @@ def main():
     def seq():
         G.halo_exchange(dx); G.computeJacobian(dx); G.computeRHS(dx, dF)
 
-    out = {"n_gpus": world}
+    out = {"n_gpus": world, "exchange_mode": G.exchange_mode()}
     out["halo_ms"] = timed(lambda: G.halo_exchange(dx), 200)
     out["allreduce31_ms"] = timed(lambda: dist.all_reduce(small), 200)
     out["jac_only_ms"] = timed(lambda: G.computeJacobian(dx), 50)
     out["rhs_only_ms"] = timed(lambda: G.computeRHS(dx, dF), 50)
     out["assemble_seq_ms"] = timed(seq, 50)
-    out["assemble_overlap_ms"] = timed(lambda: G.assemble(dx, dF, jacobian=True), 50)
+    for plan in (0, 1, 2):
+        os.environ["IEMIC_ASM_PLAN"] = str(plan)
+        out["assemble_plan%d_ms" % plan] = timed(lambda: G.assemble(dx, dF, jacobian=True), 50)
+    os.environ.pop("IEMIC_ASM_PLAN")
     ones = torch.ones(G.nvec, dtype=torch.float64, device="cuda")
     out["spmv_ms"] = timed(lambda: G.applyMatrix(ones, y), 100)
     b = y.clone()
