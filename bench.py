@@ -319,7 +319,8 @@ def main():
         "data": "synthetic",
         "config": {"workload": "synthetic global 1-degree ocean %s (BASELINE config 4): Jacobian+RHS assembly per step" % args.grid,
                    "grid": args.grid, "unknowns": nrows_g, "nnz": nnz_g, "mask": args.mask, "decomposition": "%dx%d lon x lat" % G.block()[4:6],
-                   "l2": "inputs larger than L2 (CSR %.2f GB), no flush" % (12 * nnz_g / 1e9), "gmres_m": args.gmres_m},
+                   "l2": "inputs larger than L2 (CSR %.2f GB), no flush" % (12 * nnz_g / 1e9), "gmres_m": args.gmres_m,
+                       "exchange": {0: "none (one GPU)", 1: "NCCL send/recv + allreduce", 2: "peer memory over NVLink (CUDA IPC), NCCL bootstrap only"}[G.exchange_mode()]},
         "roofline": {"bound": "hbm", "kernel": "jac_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": None, "peak_kind": peak_kind, "algorithmic_bytes_per_launch": jac_b // world, "kernel_ms": jac_ms,
                      "rhs_kernel_ms": rhs_ms, "rhs_frac": rhs_b / world / (rhs_ms * 1e-3) / 1e9 / peak,
