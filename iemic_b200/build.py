@@ -25,7 +25,7 @@ UNITS = [
     # host-side table construction: host compiler must not contract a*b+c either
     ("thcm_host.cpp", ["-Xcompiler", "-ffp-contract=off"]),
 ]
-HEADERS = ["thcm_rows.cuh", "thcm_stage.cuh", "thcm_cell.cuh", "thcm_host.h", "kernels.h", "dist.h",
+HEADERS = ["thcm_rows.cuh", "thcm_stage.cuh", "thcm_cell.cuh", "thcm_host.h", "kernels.h", "dist.h", "peer.cuh",
            os.path.join("..", "..", "include", "iemic_b200.h")]
 
 

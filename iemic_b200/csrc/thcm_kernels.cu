@@ -165,6 +165,39 @@ __device__ __forceinline__ void stage_tile(const AsmArgs& a, double* sm, int gi0
   }
 }
 
+// Tiles whose cells (halo layer included) are all owned, interior cells of the global grid -- most tiles -- need none
+// of the ghost rules: branch-free addressing, and all of a thread's loads are in flight together.
+__device__ __forceinline__ bool tile_is_plain(const Scalars& S, int gi0, int gj0, int gk0) {
+  return gi0 - 1 >= S.io0 && gi0 + TI <= S.io0 + S.nloc - 1 && gj0 - 1 >= S.jo0 && gj0 + TJ <= S.jo0 + S.mloc - 1 && gk0 >= 2 && gk0 + TK <= S.l;
+}
+template <bool RHS>
+__device__ __forceinline__ void stage_tile_plain(const AsmArgs& a, double* sm, int gi0, int gj0, int gk0) {
+  const Scalars& S = a.S;
+  constexpr int NIT = (TCELLS + NTHREADS - 1) / NTHREADS;
+  const size_t base = ((size_t)(gk0 - 2) * S.mloc + (gj0 - 1 - S.jo0)) * S.nloc + (gi0 - 1 - S.io0); // tile cell (0,0,0)
+  double2 q[NIT][3];
+  uint64_t sg[NIT];
+#pragma unroll
+  for (int it = 0; it < NIT; it++) {
+    const int t = min((int)threadIdx.x + it * NTHREADS, TCELLS - 1);
+    const int ti = t % SX, tj = (t / SX) % SY, tk = t / (SX * SY);
+    const size_t c = base + ((size_t)tk * S.mloc + tj) * S.nloc + ti;
+    const double2* p = reinterpret_cast<const double2*>(a.x + 6 * c);
+    q[it][0] = __ldg(p); q[it][1] = __ldg(p + 1); q[it][2] = __ldg(p + 2);
+    sg[it] = __ldg(a.sig + c);
+  }
+#pragma unroll
+  for (int it = 0; it < NIT; it++) {
+    const int t = threadIdx.x + it * NTHREADS;
+    if (t < TCELLS) {
+      const bool live = sbit(sg[it], SIG_LIVE), top = gk0 + t / (SX * SY) - 1 == S.l;
+      sm[t] = live ? q[it][0].x : 0.0; sm[TCELLS + t] = live ? q[it][0].y : 0.0; sm[2 * TCELLS + t] = top ? 0.0 : q[it][1].x;
+      sm[3 * TCELLS + t] = q[it][2].x; sm[4 * TCELLS + t] = q[it][2].y;
+      if (RHS) { sm[5 * TCELLS + t] = q[it][0].x; sm[6 * TCELLS + t] = q[it][0].y; sm[7 * TCELLS + t] = q[it][1].x; sm[8 * TCELLS + t] = q[it][1].y; }
+    }
+  }
+}
+
 __global__ void __launch_bounds__(NTHREADS, JAC_MINB) jac_kernel(const __grid_constant__ AsmArgs a) {
   extern __shared__ double sm[];
   const Scalars& S = a.S;
@@ -188,7 +221,8 @@ __global__ void __launch_bounds__(NTHREADS, JAC_MINB) jac_kernel(const __grid_co
 #pragma unroll
   for (int q = 0; q < 7; q++) rp[q] = active ? __ldg(a.rowptr + row0 + q) : 0;
 
-  stage_tile<false>(a, sm, gi0, gj0, gk0);
+  if (tile_is_plain(S, gi0, gj0, gk0)) stage_tile_plain<false>(a, sm, gi0, gj0, gk0);
+  else stage_tile<false>(a, sm, gi0, gj0, gk0);
   __syncthreads();
   if (!line) return;
   TileFields f; f.pu = sm; f.pv = sm + TCELLS; f.pw = sm + 2 * TCELLS; f.pt = sm + 3 * TCELLS; f.ps = sm + 4 * TCELLS;
@@ -247,7 +281,8 @@ __global__ void __launch_bounds__(NTHREADS, 2) rhs_kernel(const __grid_constant_
     if (rim != (a.part == 2)) return;
   }
   const int gi0 = S.io0 + bx * TI, gj0 = S.jo0 + by * TJ, gk0 = 1 + bz * TK;
-  stage_tile<true>(a, sm, gi0, gj0, gk0);
+  if (tile_is_plain(S, gi0, gj0, gk0)) stage_tile_plain<true>(a, sm, gi0, gj0, gk0);
+  else stage_tile<true>(a, sm, gi0, gj0, gk0);
   __syncthreads();
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;

@@ -27,7 +27,7 @@ for _ in range(reps):
 G.sync()
 b = y.clone()
 xs = torch.zeros_like(x)
-G.solve(b, xs, m=8, maxit=7, tol=0.0, ortho=ib.CGS2, check_every=0)
+G.solve(b, xs, m=8, maxit=7, tol=0.0, ortho=ib.CGS2F, check_every=0)
 G.solve(b, xs, m=4, maxit=3, tol=0.0, ortho=ib.MGS, check_every=0)
 G.sync()
 print("ok", G.launch_count())
