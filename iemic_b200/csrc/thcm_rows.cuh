@@ -193,12 +193,51 @@ THCM_HD double thcm_div(double x, double d, double rd) {
 THCM_HD double thcm_rho(const Scalars& S, double t, double s) {
   return S.lambda * s - t - S.xes * (2.93 * t + 8.3e-02 * t * t - 6.6e-04 * t * t * t); // alpt1..3, usr.F90:143-145
 }
+#ifdef __CUDACC__
+// tanh(c) for 0 < c < 22 on one straight path: 2c = t ln2 + r with t = rint(2c log2 e),
+// exp(r) = 1 + r + r^2 p(r) (degree-9 fit on |r| <= 0.354, 2.4e-17 relative), 2^t built in the exponent field,
+// tanh = (E-1)/(E+1) with E-1 assembled without cancellation, reciprocal from MUFU.RCP64H plus one cubic Newton step
+// and a final residual correction: relative error of a few 1e-16 over the whole range (tools/tanh_check.cu).  The
+// convective-adjustment terms carry tolerances, not bit parity, already with libm's tanh (the forward-difference
+// Jacobian entries amplify any tanh rounding by 1/eps = 1e8), but they do need RELATIVE accuracy.  Constants sit in the constant
+// bank so that they are instruction operands; about 30 instructions instead of the 60-100 of the generic tanh.
+static __constant__ double THCM_TANH_C[12] = {
+    0.5000000000000001, 0.16666666666666669, 0.041666666666616864, 0.008333333333329503, 0.0013888888920770123,
+    0.00019841269865788537, 2.4801515879478315e-05, 2.7557264294679126e-06, 2.762261407861969e-07, 2.5102327723609146e-08,
+    -0.6931471805598903 /* -ln2, high part (low 11 bits clear) */, -5.497923018708371e-14 /* -ln2, low part */};
+__device__ __forceinline__ double thcm_tanh_pos(double c) {
+  const double* C = THCM_TANH_C;
+  const double x2 = c + c;
+  const float tf = rintf(__double2float_rn(x2) * 1.4426950408889634f);
+  const double td = (double)tf;
+  double r = fma(td, C[10], x2);
+  r = fma(td, C[11], r);
+  double p = C[9];
+  p = fma(p, r, C[8]); p = fma(p, r, C[7]); p = fma(p, r, C[6]); p = fma(p, r, C[5]); p = fma(p, r, C[4]);
+  p = fma(p, r, C[3]); p = fma(p, r, C[2]); p = fma(p, r, C[1]); p = fma(p, r, C[0]);
+  const double em1 = fma(r * r, p, r);                                   // exp(r) - 1, full relative accuracy
+  const double sc = __hiloint2double((__float2int_rn(tf) + 1023) << 20, 0); // 2^t, 0 <= t <= 64
+  const double em = fma(sc, em1, sc - 1.0);                              // exp(2c) - 1 (sc - 1 is exact)
+  const double d = em + 2.0;                                             // exp(2c) + 1
+  double y;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(d));
+  double e = fma(-d, y, 1.0);
+  e = fma(e, e, e);
+  y = fma(y, e, y);
+  const double q = em * y;                                               // tanh = (E - 1)/(E + 1): relative accuracy for small c too
+  return fma(fma(-q, d, em), y, q);
+}
+#endif
 THCM_HD double thcm_tprstb(const Scalars& S, double grad) {
   double q = -grad * S.fac;
   double c = q * q * q;
   if (!(c > 0.0)) return 0.0;   // max(tanh(c),0) == 0 for c <= 0
   if (c >= 22.0) return 1.0;    // tanh rounds to exactly 1.0 in double precision beyond ~19.1
+#ifdef __CUDA_ARCH__
+  return thcm_tanh_pos(c);
+#else
   return tanh(c);
+#endif
 }
 // Implicit flux through one cell face between cell a (below) and cell b (above); flag = isoc(a)*isoc(b); ra, rb are
 // thcm_rho of the two cells (passed in so that callers can reuse them).  Shortcuts that do not change any value:
