@@ -46,15 +46,15 @@ THCM_HD double jac_row(const Scalars& S, const Tables& T, const Cell& c, const F
 template <int A, class F, class X>
 THCM_HD double rhs_row(const Scalars& S, const Tables& T, const Cell& c, const F& f, const X& x, double frc, double mixv) {
   Row<A> r;
+  double Au;
   if (sbit(c.sig, SIG_NOTOCEAN)) {
-    r.clear();
-    r.template at<5, A>() = 1.0;
+    Au = 1.0 * x.raw(0, 0, 0, A) + 0.0; // identity row: what row_dot returns for it, without building the row
   } else {
     RhsRow<A, F>::build(r, S, T, c, f);
     if ((uint32_t)c.sig != 0u) apply_boundaries<A>(r, c.sig);
     filter_row<A>(r);
+    Au = row_dot<A>(r, x);
   }
-  double Au = row_dot<A>(r, x);
   double B = -Au - mixv + frc - 0.0;
   B = B * (sbit(c.sig, SIG_LANDVAL) ? 0.0 : 1.0);
   return B * -1.0;
