@@ -272,7 +272,10 @@ __global__ void __launch_bounds__(NTHREADS, JAC_MINB) jac_kernel(const __grid_co
   }
 }
 
-__global__ void __launch_bounds__(NTHREADS, 2) rhs_kernel(const __grid_constant__ AsmArgs a) {
+#ifndef RHS_MINB
+#define RHS_MINB 2
+#endif
+__global__ void __launch_bounds__(NTHREADS, RHS_MINB) rhs_kernel(const __grid_constant__ AsmArgs a) {
   extern __shared__ double sm[];
   const Scalars& S = a.S;
   const int bx = blockIdx.x % a.ntx, by = (blockIdx.x / a.ntx) % a.nty, bz = blockIdx.x / (a.ntx * a.nty);
