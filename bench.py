@@ -313,6 +313,13 @@ def main():
     jac_ms = t_jac / max(c_jac, 1)
     rhs_ms = t_rhs / max(c_rhs, 1)
     achieved = jac_b / world / (jac_ms * 1e-3) / 1e9  # per GPU (max-rank time approximated by rank 0's kernel time)
+    traffic = None  # DRAM bytes of one jac_kernel launch from the committed ncu capture, when it is this workload
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["jac_kernel"]
+        if tj["grid"] == args.grid and tj["n_gpus"] == world and args.mask == "global":
+            traffic = tj["dram_bytes_per_launch"]
+    except Exception:
+        pass
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
@@ -322,7 +329,7 @@ def main():
                    "l2": "inputs larger than L2 (CSR %.2f GB), no flush" % (12 * nnz_g / 1e9), "gmres_m": args.gmres_m,
                        "exchange": {0: "none (one GPU)", 1: "NCCL send/recv + allreduce", 2: "peer memory over NVLink (CUDA IPC), NCCL bootstrap only"}[G.exchange_mode()]},
         "roofline": {"bound": "hbm", "kernel": "jac_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "peak_kind": peak_kind, "algorithmic_bytes_per_launch": jac_b // world, "kernel_ms": jac_ms,
+                     "traffic": traffic, "peak_kind": peak_kind, "algorithmic_bytes_per_launch": jac_b // world, "kernel_ms": jac_ms,
                      "rhs_kernel_ms": rhs_ms, "rhs_frac": rhs_b / world / (rhs_ms * 1e-3) / 1e9 / peak,
                      "step_frac": (jac_b + rhs_b) / (ms_step * 1e-3) / 1e9 / peak_total},
         "e2e": {"value": 1000.0 / (ms_e2e / args.steps), "unit": UNIT, "h2d_bytes_per_step": 8 * nrows_g,

@@ -7,6 +7,7 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 tag = sys.argv[1]
+cmd = sys.argv[2] if len(sys.argv) > 2 else "tools/profile_step.py"
 out_md = os.path.join(ROOT, "profiles", tag + "_summary.md")
 lines = ["# ncu summary %s" % tag, ""]
 
@@ -22,7 +23,7 @@ if os.path.exists(lcsv):
         v = v / 1e3 if r[ui] == "ns" else (v * 1e3 if r[ui] == "ms" else v)
         agg.setdefault(name, []).append(v)
     tot = sum(sum(v) for v in agg.values())
-    lines += ["## launch list (`ncu --metrics gpu__time_duration.sum --clock-control none`, tools/profile_step.py)", "",
+    lines += ["## launch list (`ncu --metrics gpu__time_duration.sum --clock-control none -c 400`, %s)" % cmd, "",
               "cold-cache, serialised launches: compare shares, not absolutes", "",
               "| kernel | launches | avg us | share |", "|---|---|---|---|"]
     for k, v in agg.items():
