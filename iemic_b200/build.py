@@ -81,7 +81,30 @@ def build(force=False, verbose=False, defines=(), tag=None):
     if rebuilt or not os.path.exists(lib):
         cmd = [_nvcc()] + ARCH + ["-shared", "-o", lib] + objs + ["-cudart", "static", "-ldl"]
         subprocess.run(cmd, check=True)
+    if not tag:
+        build_fortran_abi(lib, force or rebuilt)
     return lib
+
+
+FORTRAN_LIB = os.path.join(LIBDIR, "libthcm_b200_fortran.so")
+
+
+def build_fortran_abi(core_lib, force=False):
+    """Seam S1 (include/thcm_fortran_abi.h): the Fortran symbols THCM.C binds, as a thin host library over the C ABI.
+    A separate .so: names like init_ / rhs_ / matrix_ do not belong in the namespace of every process that loads the
+    core library."""
+    src = os.path.join(CSRC, "fortran_abi.cpp")
+    inc = [os.path.join(HERE, "..", "include", "thcm_fortran_abi.h"), os.path.join(HERE, "..", "include", "iemic_b200.h")]
+    flags = ["-O2", "-std=c++17", "-fPIC", "-fvisibility=hidden", "-shared"]
+    dig = _digest([src] + inc, flags)
+    stamp = os.path.join(HERE, "build", "fortran_abi.sha")
+    if not force and os.path.exists(FORTRAN_LIB) and os.path.exists(stamp) and open(stamp).read() == dig:
+        return FORTRAN_LIB
+    cmd = ["g++"] + flags + ["-o", FORTRAN_LIB, src, "-L" + LIBDIR, "-liemic_b200", "-Wl,-rpath,$ORIGIN", "-ldl"]
+    subprocess.run(cmd, check=True)
+    with open(stamp, "w") as f:
+        f.write(dig)
+    return FORTRAN_LIB
 
 
 if __name__ == "__main__":

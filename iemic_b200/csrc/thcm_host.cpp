@@ -40,7 +40,7 @@ Host::Host(const Config& c, const int* landm_in, int rank_, int nranks_) : cfg(c
   ndim = 6 * ncell;
   decompose();
   if (105ull * (size_t)nloc * mloc * l > 0x7fffffffull) throw std::runtime_error("thcm_b200: sub-domain too large for 32-bit CSR offsets");
-  if (nranks > 1 && cfg.sres == 0) throw std::runtime_error("thcm_b200: the dense salinity-integral row (SRES=0) is only supported on a single GPU");
+  if (nranks > 1 && cfg.sres == 0 && cfg.intcond_i != -2) throw std::runtime_error("thcm_b200: the dense salinity-integral row (SRES=0) is only supported on a single GPU");
   version = 1; mask_version = 0; intCorrection = 0.0;
   make_grid();
   stpnt();
@@ -242,7 +242,7 @@ void Host::set_landmask(const int* landm_in) {
   auto lrow = [&](int gi, int gj, int gk, int X) { return (int)(6 * cell_index(S, gi, gj, gk)) + X - 1; };
   // THCM.C:647-704 integral condition row
   rowintcon = -1; rowintcon_local = -1; owns_rowintcon = false;
-  if (cfg.sres == 0) {
+  if (cfg.sres == 0 && cfg.intcond_i != -2) { // -2: no integral row, the S row stays what the Fortran layer alone makes it
     int Nic = cfg.intcond_i == -1 ? n - 1 : cfg.intcond_i, Mic = cfg.intcond_j == -1 ? m - 1 : cfg.intcond_j;
     if (Nic < 0 || Nic >= n || Mic < 0 || Mic >= m || L(Nic + 1, Mic + 1, l) != OCEAN)
       throw std::runtime_error("thcm_b200: integral row coordinates give a land point"); // THCM.C:678-682

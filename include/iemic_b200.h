@@ -52,7 +52,8 @@ typedef struct {
   int tres, sres, iza, ite, its;
   int coupled_T, coupled_S;
   int int_sign;             /* "Salinity Integral Sign" */
-  int intcond_i, intcond_j; /* "Integral row coordinate i/j", 0-based, -1 = last */
+  int intcond_i, intcond_j; /* "Integral row coordinate i/j", 0-based, -1 = last; intcond_i = -2: no integral row even
+                             * with SRES=0 (the Fortran layer's view, used by the seam-S1 adaptor thcm_fortran_abi.h) */
   int fix_pressure_points;
 } thcm_b200_config;
 

@@ -24,6 +24,19 @@ def test_library_exports_every_declared_symbol():
     assert set(capi.EXPORTED) == set(names)
 
 
+def test_fortran_abi_library_exports_every_declared_symbol():
+    """Seam S1 (include/thcm_fortran_abi.h): the Fortran-named symbols THCM.C binds (src/ocean/THCM.C:47-174)."""
+    import ctypes as C
+    from iemic_b200 import build
+    import fortran_abi
+    build.build()
+    L = C.CDLL(fortran_abi.LIB)
+    names = fortran_abi.declared()
+    assert len(names) >= 15 and "rhs_" in names and "matrix_" in names and "__m_mat_MOD_set_pointers" in names
+    for n in names:
+        assert hasattr(L, n), n
+
+
 def test_no_gpu_fails_loudly():
     """Without a CUDA device creation must fail with an error code and message, never fall back to the CPU."""
     import ctypes as C
