@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <cstdio>
 #include <cstdlib>
+#include <algorithm>
 #include <cstring>
 #include <cmath>
 #include <string>
@@ -50,6 +51,7 @@ struct thcm_b200 {
   Dist* dist = nullptr;          // null on a single GPU
   cudaStream_t stream = 0;
   cudaStream_t copy_stream = nullptr; cudaEvent_t ev_rhs = nullptr, ev_copy = nullptr; // thcm_b200_assemble_host overlap
+  cudaStream_t up_stream = nullptr; std::vector<cudaEvent_t> ev_slab;
   // static / per-parameter device data
   double* d_tab = nullptr; uint64_t* d_sig = nullptr; int* d_rowptr = nullptr; int* d_col = nullptr;
   double* d_val = nullptr; double* d_diagB = nullptr; double* d_frc = nullptr; double* d_coefS = nullptr;
@@ -268,6 +270,8 @@ int thcm_b200_destroy(thcm_b200_t* h) {
   for (void* p : ptrs) if (p) cudaFree(p);
   gmres_free(h->g);
   if (h->copy_stream) { cudaStreamDestroy(h->copy_stream); cudaEventDestroy(h->ev_rhs); cudaEventDestroy(h->ev_copy); }
+  if (h->up_stream) cudaStreamDestroy(h->up_stream);
+  for (cudaEvent_t e : h->ev_slab) cudaEventDestroy(e);
   if (h->dist) dist_destroy(h->dist);
   delete h->host;
   delete h;
@@ -335,9 +339,9 @@ int thcm_b200_halo_exchange(thcm_b200_t* h, double* d_x) {
 } // extern "C" (re-opened below)
 
 namespace {
-int rhs_part(thcm_b200* h, const double* d_x, double* d_F, int part, cudaStream_t st = nullptr) {
+int rhs_part(thcm_b200* h, const double* d_x, double* d_F, int part, cudaStream_t st = nullptr, int kz0 = 0, int nkz = 0) {
   AsmArgs a = asm_args(h, d_x);
-  a.F = d_F; a.part = part;
+  a.F = d_F; a.part = part; a.kz0 = kz0; a.nkz = nkz;
   if (!st) st = h->stream;
   {
     Timed t(h, 0, st);
@@ -361,9 +365,9 @@ int rhs_epilogue(thcm_b200* h, const double* d_x, double* d_F) { // THCM.C:1006-
   }
   return check_launch(h, "rhs epilogue");
 }
-int jac_part(thcm_b200* h, const double* d_x, int part) {
+int jac_part(thcm_b200* h, const double* d_x, int part, int kz0 = 0, int nkz = 0) {
   AsmArgs a = asm_args(h, d_x);
-  a.part = part;
+  a.part = part; a.kz0 = kz0; a.nkz = nkz;
   {
     Timed t(h, 1);
     launch_jac(a, h->stream);
@@ -508,22 +512,52 @@ int thcm_b200_assemble_host(thcm_b200_t* h, const double* x, double* F, int jaco
     CU(cudaEventCreateWithFlags(&h->ev_rhs, cudaEventDisableTiming));
     CU(cudaEventCreateWithFlags(&h->ev_copy, cudaEventDisableTiming));
   }
-  CU(cudaMemcpyAsync(h->d_xs, x, nb, cudaMemcpyHostToDevice, h->stream));
-  if (h->dist) { // several GPUs: halo exchange hidden behind the interior tiles
+  if (h->dist) { // several GPUs: the halo exchange needs the whole state on board
+    CU(cudaMemcpyAsync(h->d_xs, x, nb, cudaMemcpyHostToDevice, h->stream));
     if (int rc = thcm_b200_assemble(h, h->d_xs, F ? h->d_ys : nullptr, jacobian)) return rc;
     if (F) CU(cudaMemcpyAsync(F, h->d_ys, nb, cudaMemcpyDeviceToHost, h->stream));
     CU(cudaStreamSynchronize(h->stream));
     return 0;
   }
-  if (F) {
-    if (int rc = thcm_b200_rhs(h, h->d_xs, h->d_ys)) return rc;
-    CU(cudaEventRecord(h->ev_rhs, h->stream));
-    CU(cudaStreamWaitEvent(h->copy_stream, h->ev_rhs, 0));
-    CU(cudaMemcpyAsync(F, h->d_ys, nb, cudaMemcpyDeviceToHost, h->copy_stream)); // overlaps the Jacobian kernel
-    CU(cudaEventRecord(h->ev_copy, h->copy_stream));
+  // One GPU: the state goes up in slabs of levels, the kernels of a slab start as soon as the slab above it has arrived,
+  // and the residual of a slab goes down while later slabs are still going up (PCIe is full duplex): the call costs about
+  // one upload instead of upload + kernels + download.
+  Host* H = h->host;
+  const int tk = asm_tile_levels(), ntz = (H->l + tk - 1) / tk;
+  const int want = getenv("IEMIC_SLABS") ? std::max(1, atoi(getenv("IEMIC_SLABS"))) : 8;
+  const int nslab = std::min(ntz, want), per = (ntz + nslab - 1) / nslab; // tile layers per slab
+  const size_t lev = (size_t)6 * H->n * H->m;                          // unknowns per level
+  if (!h->up_stream) CU(cudaStreamCreateWithFlags(&h->up_stream, cudaStreamNonBlocking));
+  while ((int)h->ev_slab.size() < 2 * nslab) { cudaEvent_t e; CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); h->ev_slab.push_back(e); }
+  CU(cudaEventRecord(h->ev_rhs, h->stream));             // earlier work on the handle's stream (e.g. a solve reading d_xs)
+  CU(cudaStreamWaitEvent(h->up_stream, h->ev_rhs, 0));
+  CU(cudaStreamWaitEvent(h->copy_stream, h->ev_rhs, 0));
+  auto lev0 = [&](int s) { return std::min(H->l, s * per * tk); };      // first level (0-based) of slab s
+  auto work = [&](int s) -> int {                                       // kernels of slab s; needs the levels of slab s+1 on board
+    const int kz0 = s * per, nkz = std::min(per, ntz - kz0);
+    if (nkz <= 0) return 0;
+    if (jacobian) if (int rc = jac_part(h, h->d_xs, 0, kz0, nkz)) return rc;
+    if (F) {
+      if (int rc = rhs_part(h, h->d_xs, h->d_ys, 0, nullptr, kz0, nkz)) return rc;
+      const bool last = kz0 + nkz >= ntz;
+      if (last) if (int rc = rhs_epilogue(h, h->d_xs, h->d_ys)) return rc; // integral condition / pressure rows live in the top level
+      CU(cudaEventRecord(h->ev_slab[nslab + s], h->stream));
+      CU(cudaStreamWaitEvent(h->copy_stream, h->ev_slab[nslab + s], 0));
+      const size_t a = lev * lev0(s), b = lev * lev0(s + 1);
+      if (b > a) CU(cudaMemcpyAsync(F + a, h->d_ys + a, (b - a) * sizeof(double), cudaMemcpyDeviceToHost, h->copy_stream));
+    }
+    return 0;
+  };
+  for (int s = 0; s < nslab; s++) {
+    const size_t a = lev * lev0(s), b = lev * lev0(s + 1);
+    if (b > a) CU(cudaMemcpyAsync(h->d_xs + a, x + a, (b - a) * sizeof(double), cudaMemcpyHostToDevice, h->up_stream));
+    CU(cudaEventRecord(h->ev_slab[s], h->up_stream));
+    CU(cudaStreamWaitEvent(h->stream, h->ev_slab[s], 0));
+    if (s >= 1) if (int rc = work(s - 1)) return rc;
   }
-  if (jacobian) if (int rc = thcm_b200_jacobian(h, h->d_xs)) return rc;
-  if (F) CU(cudaStreamWaitEvent(h->stream, h->ev_copy, 0));
+  if (int rc = work(nslab - 1)) return rc;
+  CU(cudaEventRecord(h->ev_copy, h->copy_stream));
+  CU(cudaStreamWaitEvent(h->stream, h->ev_copy, 0));
   CU(cudaStreamSynchronize(h->stream));
   return 0;
 }

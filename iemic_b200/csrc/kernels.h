@@ -21,7 +21,9 @@ struct AsmArgs {
   SpecialRows sp;
   int ntx, nty, ntz;
   int part;               // 0 every tile, 1 only tiles that read no halo cell, 2 only tiles on the block's rim
+  int kz0, nkz;           // restrict the launch to nkz tile layers starting at layer kz0 (nkz = 0: all layers)
 };
+int asm_tile_levels();    // model levels per tile layer
 void launch_jac(const AsmArgs& a, cudaStream_t st);
 void launch_rhs(const AsmArgs& a, cudaStream_t st);
 int jac_smem_bytes();

@@ -201,7 +201,7 @@ __device__ __forceinline__ void stage_tile_plain(const AsmArgs& a, double* sm, i
 __global__ void __launch_bounds__(NTHREADS, JAC_MINB) jac_kernel(const __grid_constant__ AsmArgs a) {
   extern __shared__ double sm[];
   const Scalars& S = a.S;
-  const int bx = blockIdx.x % a.ntx, by = (blockIdx.x / a.ntx) % a.nty, bz = blockIdx.x / (a.ntx * a.nty);
+  const int bx = blockIdx.x % a.ntx, by = (blockIdx.x / a.ntx) % a.nty, bz = blockIdx.x / (a.ntx * a.nty) + a.kz0;
   if (a.part) { // overlap with the halo exchange: rim tiles wait for it, the others do not (block-uniform exit)
     const bool rim = bx == 0 || bx == a.ntx - 1 || by == 0 || by == a.nty - 1;
     if (rim != (a.part == 2)) return;
@@ -278,7 +278,7 @@ __global__ void __launch_bounds__(NTHREADS, JAC_MINB) jac_kernel(const __grid_co
 __global__ void __launch_bounds__(NTHREADS, RHS_MINB) rhs_kernel(const __grid_constant__ AsmArgs a) {
   extern __shared__ double sm[];
   const Scalars& S = a.S;
-  const int bx = blockIdx.x % a.ntx, by = (blockIdx.x / a.ntx) % a.nty, bz = blockIdx.x / (a.ntx * a.nty);
+  const int bx = blockIdx.x % a.ntx, by = (blockIdx.x / a.ntx) % a.nty, bz = blockIdx.x / (a.ntx * a.nty) + a.kz0;
   if (a.part) { // overlap with the halo exchange: rim tiles wait for it, the others do not (block-uniform exit)
     const bool rim = bx == 0 || bx == a.ntx - 1 || by == 0 || by == a.nty - 1;
     if (rim != (a.part == 2)) return;
@@ -363,11 +363,13 @@ __global__ void intcond_finish_kernel(const double* dotval, double sign, double 
 int jac_smem_bytes() { return (5 * TCELLS + NWARP * 32 * STRIDE) * (int)sizeof(double); }
 int rhs_smem_bytes() { return (9 * TCELLS + NWARP * 32 * 6) * (int)sizeof(double); }
 
-static int grid_of(const AsmArgs& a) { return a.ntx * a.nty * a.ntz; }
+static int grid_of(const AsmArgs& a) { return a.ntx * a.nty * (a.nkz > 0 ? a.nkz : a.ntz); }
+int asm_tile_levels() { return TK; }
 
 void launch_jac(const AsmArgs& a0, cudaStream_t st) {
   AsmArgs a = a0;
   a.ntx = (a.S.nloc + TI - 1) / TI; a.nty = (a.S.mloc + TJ - 1) / TJ; a.ntz = (a.S.l + TK - 1) / TK;
+  if (a.nkz <= 0) a.kz0 = 0;
   static bool attr = false;
   if (!attr) { cudaFuncSetAttribute(jac_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, jac_smem_bytes()); attr = true; }
   jac_kernel<<<grid_of(a), NTHREADS, jac_smem_bytes(), st>>>(a);
@@ -375,6 +377,7 @@ void launch_jac(const AsmArgs& a0, cudaStream_t st) {
 void launch_rhs(const AsmArgs& a0, cudaStream_t st) {
   AsmArgs a = a0;
   a.ntx = (a.S.nloc + TI - 1) / TI; a.nty = (a.S.mloc + TJ - 1) / TJ; a.ntz = (a.S.l + TK - 1) / TK;
+  if (a.nkz <= 0) a.kz0 = 0;
   static bool attr = false;
   if (!attr) { cudaFuncSetAttribute(rhs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, rhs_smem_bytes()); attr = true; }
   rhs_kernel<<<grid_of(a), NTHREADS, rhs_smem_bytes(), st>>>(a);
