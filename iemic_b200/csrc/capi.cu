@@ -55,7 +55,7 @@ struct thcm_b200 {
   // static / per-parameter device data
   double* d_tab = nullptr; uint64_t* d_sig = nullptr; int* d_rowptr = nullptr; int* d_col = nullptr;
   double* d_val = nullptr; double* d_diagB = nullptr; double* d_frc = nullptr; double* d_coefS = nullptr;
-  int* d_blkrow = nullptr; int nblk = 0;
+  int* d_blkrow = nullptr; int nblk = 0; size_t d_frc_len = 0;
   uint64_t dev_version = 0, dev_mask_version = 0;
   // scratch vectors for the host-buffer entry points
   double *d_xs = nullptr, *d_ys = nullptr;
@@ -145,7 +145,14 @@ int refresh_device(thcm_b200* h) {
   }
   if (h->dev_version != H->version) {
     if (int rc = dev_upload(&h->d_tab, H->tab)) return rc;
-    if (int rc = dev_upload(&h->d_frc, H->frc)) return rc;
+    if (h->d_frc && h->d_frc_len == H->frc.size() && H->frc_dirty_from > 0) { // only the rows a parameter change rewrote
+      const size_t a = std::min(H->frc_dirty_from, H->frc.size());
+      if (a < H->frc.size()) CU(cudaMemcpy(h->d_frc + a, H->frc.data() + a, (H->frc.size() - a) * sizeof(double), cudaMemcpyHostToDevice));
+    } else {
+      if (int rc = dev_upload(&h->d_frc, H->frc)) return rc;
+      h->d_frc_len = H->frc.size();
+    }
+    H->frc_dirty_from = H->frc.size();
     h->dev_version = H->version;
   }
   return 0;

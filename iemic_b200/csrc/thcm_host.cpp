@@ -211,7 +211,7 @@ void Host::set_par(int idx1, double value) {
   if (cfg.vmix != 0 && (par[P_MIXP] * par[P_PE_H] != 0.0 || par[P_MKAP] * par[P_PE_H] != 0.0 || (1.0 - par[P_ALPC]) * par[P_ENER] * par[P_PE_V] != 0.0))
     throw std::runtime_error("thcm_b200: MIXP/MKAP/ALPC settings enable neutral-physics or consistent mixing, which the B200 path does not implement");
   build_tables();
-  build_forcing();
+  build_forcing(true); // forcing.F90 depends on the parameters through the surface terms only (the body term is an exact zero)
   version++;
 }
 
@@ -453,9 +453,17 @@ double wfun(double yy, int v1) {
 } // namespace
 
 // forcing.F90:4-218 (idealized, uncoupled salinity) followed by the Frc zeroing of boundary.F90
-void Host::build_forcing() {
+void Host::build_forcing(bool surface_only) {
   const size_t nrows = 6 * (size_t)S.nown;
-  frc.assign(nrows, 0.0);
+  const size_t top = 6 * (size_t)nloc * mloc * (l - 1); // first row of the surface level (levels are the slowest index)
+  if (surface_only && frc.size() == nrows) {
+    std::fill(frc.begin() + top, frc.end(), 0.0);
+    frc_dirty_from = std::min(frc_dirty_from, top);
+  } else {
+    surface_only = false;
+    frc.assign(nrows, 0.0);
+    frc_dirty_from = 0;
+  }
   const int TRES = cfg.tres, SRES = cfg.sres;
   const double gymin = cfg.ymin, gymax = cfg.ymax;
   const int i1 = io0, i2 = io0 + nloc - 1, j1 = jo0, j2 = jo0 + mloc - 1; // owned block, global Fortran indices
@@ -501,10 +509,11 @@ void Host::build_forcing() {
   for (int j = j1; j <= j2; j++) for (int i = i1; i <= i2; i++)
     frc[row(i, j, l, SS)] = gamma * (1 - par[P_HMTP]) * (emip[(size_t)(i - 1) + (size_t)n * (j - 1)] - salcor) +
                             gamma * par[P_HMTP] * (0.0 - adapted_salcor) + par[P_SPER] * (1 - SRES + SRES * par[P_BIOT]) * (0.0 - spertcor);
+  if (!surface_only)
   for (int k = 1; k <= l - 1; k++) for (int j = j1; j <= j2; j++) for (int i = i1; i <= i2; i++) // internal T/S forcing is zero (THCM.C:540-544)
     frc[row(i, j, k, WW)] = -par[P_COMB] * (1 - lm(i, j, k)) * par[P_RAYL] * (par[P_LAMB] * (0.0 + 0.0) / 2. - (0.0 + 0.0) / 2.);
   // rows whose forcing `boundaries` resets to zero on every call
-  for (size_t c = 0; c < (size_t)S.nown; c++) {
+  for (size_t c = surface_only ? top / 6 : 0; c < (size_t)S.nown; c++) {
     uint64_t g = sig[c];
     if (frc_masked<UU>(g)) frc[6 * c + 0] = 0.0;
     if (frc_masked<VV>(g)) frc[6 * c + 1] = 0.0;

@@ -75,6 +75,7 @@ class Host {
   size_t nvec_local() const { return gid.size(); }
   double intcond_col(int col) const { return intcond[(size_t)col]; } // coefficient of stored column `col`
 
+  size_t frc_dirty_from = 0; // first row of `frc` a device copy made before the last change does not have yet
   Tables tables(const double* base) const; // pointers into a (host or device) copy of `tab`
   inline int lm(int i, int j, int k) const { return landm[(size_t)i + (size_t)(n + 2) * (j + (size_t)(m + 2) * k)]; }
 
@@ -84,7 +85,8 @@ class Host {
   void stpnt();
   void build_signatures();
   void build_tables();
-  void build_forcing();
+  // surface_only: a parameter change touches the top level only (wind stress, surface T/S forcing); the body rows stay zero
+  void build_forcing(bool surface_only = false);
   void build_graph();
   void check_supported() const;
 };

@@ -245,3 +245,29 @@ def test_assemble_host_equals_separate_calls():
     G.sync()
     v3, b3 = G.values_host()
     assert np.array_equal(F1, dF.cpu().numpy()[:G.nrows]) and np.array_equal(v1, v3) and np.array_equal(b1, b3)
+
+
+@pytest.mark.parametrize("name", ["natl8", "rand_periodic", "global4"])
+def test_parameter_change_after_first_evaluation(name):
+    """Continuation changes parameters between evaluations (Continuation.H:405-410): only the surface slice of the forcing
+    and the coefficient tables are rebuilt and re-uploaded, and the results must equal a fresh model's."""
+    cfg, mask, O, G = cases.make_pair(name)
+    x = cases.state(cfg, mask, seed=14)
+    G.computeRHS_host(x)
+    G.computeJacobian_host(x)
+    for k, v in (("COMB", 0.37), ("TEMP", 7.5), ("WIND", 0.6), ("SALT", 0.8), ("RAYL", 0.031)):
+        O.set_par(k, v)
+        G.setPar(k, v)
+        assert G.getPar(k) == v
+    O.rhs(x)
+    assert np.array_equal(O.frc(), G.forcing_host())
+    Fo, Fg = O.rhs(x), G.computeRHS_host(x)
+    ts = _mix_rows(cfg, Fo.size)
+    assert np.array_equal(Fo[~ts], Fg[~ts])
+    assert np.abs(Fo - Fg).max() <= 1e-12 * np.abs(Fo).max()
+    vo, bo = O.jac(x)
+    vg, bg = G.computeJacobian_host(x)
+    rp, col = O.graph()
+    rows = np.repeat(np.arange(rp.size - 1), np.diff(rp))
+    tracer = (rows % 6 >= 4) & (col % 6 >= 4)
+    assert np.array_equal(vo[~tracer], vg[~tracer]) and np.array_equal(bo, bg)
