@@ -56,6 +56,7 @@ struct thcm_b200 {
   double* d_tab = nullptr; uint64_t* d_sig = nullptr; int* d_rowptr = nullptr; int* d_col = nullptr;
   double* d_val = nullptr; double* d_diagB = nullptr; double* d_frc = nullptr; double* d_coefS = nullptr;
   int* d_blkrow = nullptr; int nblk = 0; size_t d_frc_len = 0;
+  int* d_blkp0 = nullptr; unsigned char* d_blkreg = nullptr; SpmvTab spmv_tab; size_t spmv_regular_cells = 0;
   uint64_t dev_version = 0, dev_mask_version = 0;
   // scratch vectors for the host-buffer entry points
   double *d_xs = nullptr, *d_ys = nullptr;
@@ -92,20 +93,61 @@ int flush_timing(thcm_b200* h) {
   return 0;
 }
 
-// Build the row-run plan of the SpMV kernel (spmv.cu): runs of <= rows_cap rows and <= nnz_cap non-zeros.
-std::vector<int> spmv_plan(const std::vector<int>& rowptr) {
-  std::vector<int> blk;
-  const int nrows = (int)rowptr.size() - 1, ncap = spmv_nnz_cap(), rcap = spmv_rows_cap();
+// Build the plan of the SpMV kernel (spmv.cu): blocks of whole regular cells (columns follow from the cell index, checked
+// here against the real column array) and, for everything else, runs of <= rows_cap rows and <= nnz_cap non-zeros.
+struct SpmvHostPlan { std::vector<int> blk_row, blk_p0; std::vector<unsigned char> blk_reg; SpmvTab tab; size_t regular_cells = 0; };
+template <int A> void spmv_tab_rows(SpmvTab& T, int& pos, int nloc, long long nlm) {
+  for (int e = 0; e < RowDef<A>::NE; e++) {
+    const int slot = RowDef<A>::e[e].slot;
+    T.off[pos++] = (int)(6 * (slot_di(slot) + (long long)slot_dj(slot) * nloc + slot_dk(slot) * nlm)) + RowDef<A>::e[e].var - 1;
+  }
+}
+SpmvHostPlan spmv_plan(const Host& H) {
+  SpmvHostPlan P;
+  const std::vector<int>& rowptr = H.rowptr;
+  const std::vector<int>& col = H.col;
+  const int nrows = (int)rowptr.size() - 1, ncap = spmv_nnz_cap(), rcap = spmv_rows_cap(), ncell = nrows / 6;
+  int pos = 0;
+  const long long nlm = (long long)H.nloc * H.mloc;
+  std::memset(&P.tab, 0, sizeof(P.tab));
+  spmv_tab_rows<UU>(P.tab, pos, H.nloc, nlm); spmv_tab_rows<VV>(P.tab, pos, H.nloc, nlm); spmv_tab_rows<WW>(P.tab, pos, H.nloc, nlm);
+  spmv_tab_rows<PP>(P.tab, pos, H.nloc, nlm); spmv_tab_rows<TT>(P.tab, pos, H.nloc, nlm); spmv_tab_rows<SS>(P.tab, pos, H.nloc, nlm);
+  const bool use_regular = !(getenv("IEMIC_SPMV_REGULAR") && getenv("IEMIC_SPMV_REGULAR")[0] == '0') && pos == SPMV_CELL_NNZ;
+  const int lens[6] = {RowDef<UU>::NE, RowDef<VV>::NE, RowDef<WW>::NE, RowDef<PP>::NE, RowDef<TT>::NE, RowDef<SS>::NE};
+  std::vector<unsigned char> regular((size_t)ncell, 0);
+  if (use_regular)
+    for (int c = 0; c < ncell; c++) {
+      bool ok = true;
+      for (int a = 0; a < 6 && ok; a++) ok = rowptr[6 * c + a + 1] - rowptr[6 * c + a] == lens[a];
+      const int p0 = rowptr[6 * c];
+      for (int q = 0; q < SPMV_CELL_NNZ && ok; q++) ok = col[p0 + q] == 6 * c + P.tab.off[q];
+      regular[c] = ok;
+      P.regular_cells += ok;
+    }
+  const int G = spmv_regular_cells();
+  if (G <= 0) std::fill(regular.begin(), regular.end(), 0);
   int r = 0;
-  blk.push_back(0);
+  P.blk_row.push_back(0);
   while (r < nrows) {
-    int r1 = r + 1; // always take one row (a long row becomes a block of its own)
-    if (rowptr[r1] - rowptr[r] <= ncap)
-      while (r1 < nrows && r1 - r < rcap && rowptr[r1 + 1] - rowptr[r] <= ncap) r1++;
-    blk.push_back(r1);
+    int r1;
+    const int c = r / 6;
+    if (r % 6 == 0 && c < ncell && regular[c]) {
+      int g = 1;
+      while (g < G && c + g < ncell && regular[c + g]) g++;
+      r1 = r + 6 * g;
+      P.blk_reg.push_back(1);
+    } else {
+      r1 = r + 1; // always take one row (a long row becomes a block of its own)
+      auto stop = [&](int rr) { return rr % 6 == 0 && rr / 6 < ncell && regular[rr / 6]; }; // regular cells start their own block
+      if (rowptr[r1] - rowptr[r] <= ncap)
+        while (r1 < nrows && !stop(r1) && r1 - r < rcap && rowptr[r1 + 1] - rowptr[r] <= ncap) r1++;
+      P.blk_reg.push_back(0);
+    }
+    P.blk_p0.push_back(rowptr[r]);
+    P.blk_row.push_back(r1);
     r = r1;
   }
-  return blk;
+  return P;
 }
 
 int refresh_device(thcm_b200* h) {
@@ -121,9 +163,13 @@ int refresh_device(thcm_b200* h) {
     if (h->d_diagB) { cudaFree(h->d_diagB); h->d_diagB = nullptr; }
     CU(cudaMalloc((void**)&h->d_diagB, (size_t)h->nrows() * sizeof(double)));
     CU(cudaMemset(h->d_diagB, 0, (size_t)h->nrows() * sizeof(double)));
-    std::vector<int> blk = spmv_plan(H->rowptr);
-    h->nblk = (int)blk.size() - 1;
-    if (int rc = dev_upload(&h->d_blkrow, blk)) return rc;
+    SpmvHostPlan sp = spmv_plan(*H);
+    h->nblk = (int)sp.blk_row.size() - 1;
+    h->spmv_tab = sp.tab; h->spmv_regular_cells = sp.regular_cells;
+    if (getenv("IEMIC_DEBUG")) fprintf(stderr, "[iemic_b200] SpMV plan: %d blocks, %zu of %lld cells regular\n", h->nblk, sp.regular_cells, h->nrows() / 6);
+    if (int rc = dev_upload(&h->d_blkrow, sp.blk_row)) return rc;
+    if (int rc = dev_upload(&h->d_blkp0, sp.blk_p0)) return rc;
+    if (int rc = dev_upload(&h->d_blkreg, sp.blk_reg)) return rc;
     // integral condition: compact per-cell coefficients, and the static dense Jacobian row (THCM.C:2121-2198)
     std::vector<double> coefS((size_t)h->nrows() / 6);
     for (size_t c = 0; c < coefS.size(); c++) coefS[c] = H->intcond[6 * c + 5];
@@ -219,7 +265,7 @@ int spmv_impl(thcm_b200* h, double* d_x, double* d_y) {
   }
   {
     Timed t(h, 2);
-    SpmvPlan p{h->nblk, h->d_blkrow, spmv_nnz_cap()};
+    SpmvPlan p{h->nblk, h->d_blkrow, spmv_nnz_cap(), h->d_blkp0, h->d_blkreg, h->spmv_tab};
     launch_spmv(p, h->d_rowptr, h->d_col, h->d_val, d_x, d_y, h->stream);
     h->launches++;
   }
@@ -272,7 +318,7 @@ int thcm_b200_destroy(thcm_b200_t* h) {
   CHECK_H(h);
   cudaStreamSynchronize(h->stream);
   flush_timing(h);
-  void* ptrs[] = {h->d_tab, h->d_sig, h->d_rowptr, h->d_col, h->d_val, h->d_diagB, h->d_frc, h->d_coefS, h->d_blkrow, h->d_xs, h->d_ys,
+  void* ptrs[] = {h->d_tab, h->d_sig, h->d_rowptr, h->d_col, h->d_val, h->d_diagB, h->d_frc, h->d_coefS, h->d_blkrow, h->d_blkp0, h->d_blkreg, h->d_xs, h->d_ys,
                   h->rb.partial, h->rb.ticket, h->d_small};
   for (void* p : ptrs) if (p) cudaFree(p);
   gmres_free(h->g);

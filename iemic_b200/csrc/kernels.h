@@ -35,14 +35,24 @@ void launch_intcond_dot(const double* coefS, const double* x, long long ncell, d
 void launch_intcond_finish(const double* dotval, double sign, double corr, double* F, int row, int rowPfix1, int rowPfix2, cudaStream_t st);
 
 // ---- CSR SpMV (spmv.cu) ----
+// Most cells of the static THCM graph are "regular": all 27 neighbours stored, so the 104 columns of the cell's six rows
+// are the cell's own first column plus one fixed table of offsets.  Blocks made of such cells compute their column
+// indices instead of loading them (the plan is verified against the real column array on the host); everything else --
+// domain edges, the periodic seam, halo neighbours, the dense integral row -- takes the generic CSR path.
+constexpr int SPMV_CELL_NNZ = 104;
+struct SpmvTab { int off[SPMV_CELL_NNZ]; }; // column of entry q of a regular cell, relative to 6 * cell
 struct SpmvPlan {
   int nblocks;
-  const int* blk_row;   // device, nblocks+1 row boundaries; a block with a single "long" row is reduced block-wide
-  int nnz_cap;          // max non-zeros staged per block
+  const int* blk_row;            // device, nblocks+1 row boundaries; a block with a single "long" row is reduced block-wide
+  int nnz_cap;                   // max non-zeros staged per block
+  const int* blk_p0;             // device, first non-zero of every block (regular blocks skip the rowptr loads); may be null
+  const unsigned char* blk_reg;  // device, 1 = block of whole regular cells; may be null (all generic)
+  SpmvTab tab;                   // column offsets of a regular cell, relative to 6 * cell
 };
 void launch_spmv(const SpmvPlan& p, const int* rowptr, const int* col, const double* val, const double* x, double* y, cudaStream_t st);
 int spmv_nnz_cap();
 int spmv_rows_cap();
+int spmv_regular_cells(); // regular cells per block
 
 // ---- vector / GMRES kernels (gmres.cu) ----
 struct RedBuf { double* partial; unsigned int* ticket; int nblk_max; }; // workspace for block-partial reductions

@@ -19,4 +19,4 @@ for _ in range(50): G.applyMatrix(x, y)
 e1.record(); torch.cuda.synchronize()
 ms = e0.elapsed_time(e1) / 50
 b = 12 * G.nnz + 20 * G.nrows
-print("variant", os.environ.get("IEMIC_SPMV_VARIANT"), "ms %.4f GB/s %.0f" % (ms, b / ms / 1e6), "checksum %.17g" % float(y.sum()))
+print("variant", os.environ.get("IEMIC_SPMV_VARIANT"), "rvar", os.environ.get("IEMIC_SPMV_RVAR"), "regular", os.environ.get("IEMIC_SPMV_REGULAR"), "ms %.4f GB/s %.0f" % (ms, b / ms / 1e6), "checksum %.17g" % float(y.sum()))
