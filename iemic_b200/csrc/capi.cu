@@ -718,13 +718,21 @@ int gmres_b200_solve(thcm_b200_t* h, const double* d_b, double* d_x, int m, int 
       } else if (int rc = spmv_impl(h, vi, w)) return rc;
       {
         Timed t(h, 3);
+        bool givens_done = false;
         if (fused) {
           // two reductions per step: the second one also carries <w,w>, the norm of the twice-projected vector follows
           // from Pythagoras, and the normalisation rides on the second update.
           { const PeerRed pr = red(h); launch_multi_dot(g.V, ld, i + 1, w, n, h1, h->rb, st, pr); L();
           if (int rc = allreduce(h, h1, i + 1, pr)) return rc; }
           launch_multi_axpy(g.V, ld, i + 1, h1, w, n, nullptr, h->rb, st); L();
-          { const PeerRed pr = red(h); launch_multi_dot(g.V, ld, i + 2, w, n, h2, h->rb, st, pr); L();
+          { const PeerRed pr = red(h);
+            // the Arnoldi bookkeeping rides in the finishing block of this reduction unless NCCL still has to sum h2
+            const bool fuse_gv = !h->dist || pr.nranks > 0;
+            GivensArgs gf;
+            gf.H = g.H; gf.ldh = m + 1; gf.cs = g.cs; gf.sn = g.sn; gf.s = g.s; gf.h1 = h1; gf.h2 = h2; gf.nrm2 = nrm2; gf.sq = 1; gf.pyth = 1;
+            gf.bnorm = bnorm; gf.hist = g.hist; gf.hnext = hnext; gf.j = i;
+            launch_multi_dot(g.V, ld, i + 2, w, n, h2, h->rb, st, pr, fuse_gv ? &gf : nullptr); L();
+            givens_done = fuse_gv;
           if (int rc = allreduce(h, h2, i + 2, pr)) return rc; }
         } else if (ortho == GMRES_B200_CGS2) {
           { const PeerRed pr = red(h); launch_multi_dot(g.V, ld, i + 1, g.w, n, h1, h->rb, st, pr); L();
@@ -745,7 +753,7 @@ int gmres_b200_solve(thcm_b200_t* h, const double* d_b, double* d_x, int m, int 
         GivensArgs ga;
         ga.H = g.H; ga.ldh = m + 1; ga.cs = g.cs; ga.sn = g.sn; ga.s = g.s; ga.h1 = h1; ga.h2 = (ortho != GMRES_B200_MGS) ? h2 : nullptr;
         ga.nrm2 = nrm2; ga.sq = 1; ga.pyth = fused ? 1 : 0; ga.bnorm = bnorm; ga.hist = g.hist; ga.hnext = hnext; ga.j = i;
-        launch_givens(ga, st); L();
+        if (!givens_done) { launch_givens(ga, st); L(); }
         if (fused) { launch_multi_axpy(g.V, ld, i + 1, h2, w, n, nullptr, h->rb, st, hnext); L(); }
         else { launch_scale_copy(g.w, g.V + (size_t)(i + 1) * ld, n, hnext, 1, 0, st); L(); }
       }

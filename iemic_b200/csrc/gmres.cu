@@ -70,8 +70,12 @@ __device__ __forceinline__ void final_sum(const double* partial, int stride, int
   }
 }
 
+__device__ void givens_step(const GivensArgs& g);
+// With gv.H set, the finishing block also performs the Arnoldi bookkeeping of this step (fused CGS2: the second
+// multi-dot is the last reduction of the step), which saves the launch of the single-thread givens kernel.
 __global__ void __launch_bounds__(RT) multi_dot_kernel(const double* __restrict__ V, long long ldv, int nv, const double* __restrict__ w,
-                                                       long long n, double* out, double* partial, unsigned int* ticket, const PeerRed pr) {
+                                                       long long n, double* out, double* partial, unsigned int* ticket, const PeerRed pr,
+                                                       const GivensArgs gv) {
   const long long n2 = n >> 1; // double2 elements (n is even: 6 unknowns per cell)
   const double2* w2 = reinterpret_cast<const double2*>(w);
   for (int k0 = 0; k0 < nv; k0 += KT) {
@@ -94,6 +98,10 @@ __global__ void __launch_bounds__(RT) multi_dot_kernel(const double* __restrict_
   if (last_block(ticket)) {
     final_sum(partial, MAXV, nv, out);
     if (pr.nranks) peer_allreduce_block(pr, out, nv);
+    if (gv.H) {
+      __syncthreads(); // out[] complete and visible to thread 0
+      if (threadIdx.x == 0) givens_step(gv);
+    }
   }
 }
 
@@ -236,8 +244,7 @@ __device__ void app_rot(double& dx, double& dy, double cs, double sn) {
   dy = -sn * dx + cs * dy;
   dx = temp;
 }
-__global__ void givens_kernel(const GivensArgs g) {
-  if (threadIdx.x != 0) return;
+__device__ void givens_step(const GivensArgs& g) { // one thread
   const int j = g.j;
   double* Hc = g.H + (size_t)j * g.ldh;
   for (int k = 0; k <= j; k++) Hc[k] = g.h1[k] + (g.h2 ? g.h2[k] : 0.0);
@@ -254,6 +261,9 @@ __global__ void givens_kernel(const GivensArgs g) {
   app_rot(Hc[j], Hc[j + 1], g.cs[j], g.sn[j]);
   app_rot(g.s[j], g.s[j + 1], g.cs[j], g.sn[j]);
   g.hist[j] = fabs(g.s[j + 1]) / *g.bnorm;
+}
+__global__ void givens_kernel(const GivensArgs g) {
+  if (threadIdx.x == 0) givens_step(g);
 }
 __global__ void backsolve_kernel(const double* H, int ldh, const double* s, int k, double* y) {
   if (threadIdx.x != 0) return;
@@ -292,8 +302,11 @@ int red_blocks() {
   return g_red_blocks;
 }
 
-void launch_multi_dot(const double* V, long long ldv, int nv, const double* w, long long n, double* out, RedBuf rb, cudaStream_t st, const PeerRed& pr) {
-  multi_dot_kernel<<<grid_for(n), RT, 0, st>>>(V, ldv, nv, w, n, out, rb.partial, rb.ticket, pr);
+void launch_multi_dot(const double* V, long long ldv, int nv, const double* w, long long n, double* out, RedBuf rb, cudaStream_t st, const PeerRed& pr,
+                      const GivensArgs* gv) {
+  GivensArgs g;
+  if (gv) g = *gv; else g.H = nullptr;
+  multi_dot_kernel<<<grid_for(n), RT, 0, st>>>(V, ldv, nv, w, n, out, rb.partial, rb.ticket, pr, g);
 }
 void launch_multi_axpy(const double* V, long long ldv, int nv, const double* h, double* w, long long n, double* nrm2_out, RedBuf rb, cudaStream_t st,
                        const double* inv_scale, const PeerRed& pr) {

@@ -57,11 +57,25 @@ int spmv_regular_cells(); // regular cells per block
 // ---- vector / GMRES kernels (gmres.cu) ----
 struct RedBuf { double* partial; unsigned int* ticket; int nblk_max; }; // workspace for block-partial reductions
 int red_blocks();
+// Arnoldi bookkeeping on the device (single thread): column j of H from h1 (+h2), norm from nrm2 (squared),
+// Givens rotations (GMRESSolver.H:190-200), residual estimate hist[j] = |s[j+1]| / bnorm.
+struct GivensArgs {
+  double* H; int ldh;          // (m+1) x m, column major
+  double* cs; double* sn; double* s;
+  const double* h1; const double* h2; // h2 may be null
+  const double* nrm2;          // squared norm of w (or norm if !sq)
+  int sq;
+  int pyth;                    // norm from h2: sqrt(h2[j+1] - sum_k h2[k]^2), h2[j+1] = <w,w> before the second projection
+  const double* bnorm;         // device scalar: ||b||
+  double* hist;
+  double* hnext;               // receives H[j+1][j] (the norm) for the normalisation kernel
+  int j;
+};
 // out[k] = <V_k, w>, k = 0..nv-1 (V_k = V + k*ldv), deterministic two-stage reduction finished by the last block.
 // With pr.nranks > 0 the finishing block also sums over the ranks through peer memory (peer.cuh); this holds for every
 // reducing kernel below.
 void launch_multi_dot(const double* V, long long ldv, int nv, const double* w, long long n, double* out, RedBuf rb, cudaStream_t st,
-                      const PeerRed& pr = PeerRed{});
+                      const PeerRed& pr = PeerRed{}, const GivensArgs* fused_givens = nullptr /* run this step's bookkeeping in the finishing block */);
 // w -= sum_k h[k] V_k ; optionally hacc[k] += h[k] ; optionally nrm2_out = ||w_new||^2
 void launch_multi_axpy(const double* V, long long ldv, int nv, const double* h, double* w, long long n,
                        double* nrm2_out, RedBuf rb, cudaStream_t st, const double* inv_scale = nullptr /* w /= *inv_scale afterwards */,
@@ -81,20 +95,6 @@ void launch_block_jacobi(const double* binv, const double* v, double* z, long lo
 // r = b - r  (r holds A x on entry)
 void launch_residual(const double* b, double* r, long long n, cudaStream_t st);
 
-// Arnoldi bookkeeping on the device (single thread): column j of H from h1 (+h2), norm from nrm2 (squared),
-// Givens rotations (GMRESSolver.H:190-200), residual estimate hist[j] = |s[j+1]| / bnorm.
-struct GivensArgs {
-  double* H; int ldh;          // (m+1) x m, column major
-  double* cs; double* sn; double* s;
-  const double* h1; const double* h2; // h2 may be null
-  const double* nrm2;          // squared norm of w (or norm if !sq)
-  int sq;
-  int pyth;                    // norm from h2: sqrt(h2[j+1] - sum_k h2[k]^2), h2[j+1] = <w,w> before the second projection
-  const double* bnorm;         // device scalar: ||b||
-  double* hist;
-  double* hnext;               // receives H[j+1][j] (the norm) for the normalisation kernel
-  int j;
-};
 void launch_givens(const GivensArgs& g, cudaStream_t st);
 // y = H(0:k,0:k)^-1 s(0:k)   (GMRESSolver::backSolve, :258-289)
 void launch_backsolve(const double* H, int ldh, const double* s, int k, double* y, cudaStream_t st);
