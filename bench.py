@@ -298,6 +298,30 @@ def main():
         t_sp, c_sp = G.timing_get(2)
         G.timing(False)
         gm = (ms_g / ksteps, t_orth / max(c_orth, 1), t_sp / max(c_sp, 1))
+        # SURVEY 8d "fixed preconditioner" leg (row N3): point-block Jacobi built on the device from the current Jacobian,
+        # THCM block scaling, and the same GMRES cycle with the preconditioner applied (flexible: a second basis Z)
+        d_binv = torch.empty(G.nrows * 6, dtype=torch.float64, device="cuda")
+        d_rs = torch.empty(G.nrows, dtype=torch.float64, device="cuda")
+        ms_bj = timed(lambda: G.block_jacobi(d_binv), 5, 2) / 5
+        ms_sc = timed(lambda: G.recompute_scaling(d_rs, None), 5, 2) / 5
+        d_ri = torch.empty_like(d_rs)
+        G.reciprocal(d_rs, d_ri)
+
+        def scale_unscale():
+            G.left_scale(d_rs)
+            G.left_scale(d_ri)
+
+        ms_ls = timed(scale_unscale, 3, 1) / 6
+        G.computeJacobian(dx)  # undo the rounding of scale / unscale
+
+        def cycle_prec():
+            xs.zero_()
+            G.solve(b, xs, m=mm, maxit=mm - 1, tol=0.0, ortho=ib.CGS2F, prec=ib.PREC_BLOCKJACOBI, d_blockinv=d_binv, check_every=0)
+
+        ms_gp = timed(cycle_prec, 2, 1) / 2
+        prec_leg = {"block_jacobi_build_ms": ms_bj, "recompute_scaling_ms": ms_sc, "left_scale_ms": ms_ls,
+                    "gmres_block_jacobi_iters_per_s": mm / (ms_gp * 1e-3), "gmres_block_jacobi_ms_per_cycle": ms_gp}
+        del d_binv, d_rs, d_ri
     clocks = sampler.stop() if rank == 0 else None
 
     if rank != 0:
@@ -340,6 +364,7 @@ def main():
         "clocks": clocks,
     }
     if gm:
+        line["preconditioned"] = prec_leg
         ms_cycle, orth_ms, sp_ms = gm
         line["gmres"] = {"iters_per_s": args.gmres_m / (ms_cycle * 1e-3), "ms_per_cycle": ms_cycle, "m": args.gmres_m, "ortho": "CGS2 (two reductions per step, fused normalisation)",
                          "frac": cycle_b / (ms_cycle * 1e-3) / 1e9 / peak_total, "algorithmic_bytes_per_cycle": cycle_b,

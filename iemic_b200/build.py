@@ -20,6 +20,7 @@ UNITS = [
     ("thcm_kernels.cu", ["-fmad=false"]),
     ("spmv.cu", []),
     ("gmres.cu", []),
+    ("scaling.cu", ["-fmad=false"]),
     ("dist.cu", []),
     ("capi.cu", ["-Xcompiler", "-fvisibility=default"]),
     # host-side table construction: host compiler must not contract a*b+c either

@@ -76,6 +76,9 @@ def lib():
             "vec_b200_dot": [vp, vp, vp, dp], "vec_b200_norm2": [vp, vp, dp],
             "vec_b200_update": [vp, C.c_double, vp, C.c_double, vp], "vec_b200_scale": [vp, C.c_double, vp],
             "vec_b200_putscalar": [vp, C.c_double, vp],
+            "vec_b200_multiply": [vp, C.c_double, vp, vp, C.c_double, vp], "vec_b200_reciprocal": [vp, vp, vp],
+            "thcm_b200_average_block": [vp, dp], "thcm_b200_scal": [dp, dp, dp], "thcm_b200_recompute_scaling": [vp, vp, vp, dp, dp],
+            "thcm_b200_left_scale": [vp, vp], "thcm_b200_block_jacobi": [vp, vp, ip],
             "gmres_b200_solve": [vp, vp, vp, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int, vp, C.c_int, dp, ip],
             "gmres_b200_solve_host": [vp, vp, vp, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int, vp, C.c_int, dp, ip],
             "thcm_b200_launch_count": [vp, i64p], "thcm_b200_timing_enable": [vp, C.c_int],
@@ -100,6 +103,8 @@ EXPORTED = ["iemic_b200_last_error", "iemic_b200_version", "iemic_b200_device_co
             "thcm_b200_values_host", "thcm_b200_set_values_host", "thcm_b200_forcing_host", "thcm_b200_intcond_host",
             "thcm_b200_rhs_host", "thcm_b200_jacobian_host", "thcm_b200_assemble_host", "thcm_b200_assemble", "thcm_b200_exchange_mode", "thcm_b200_spmv", "thcm_b200_spmv_host",
             "vec_b200_dot", "vec_b200_norm2", "vec_b200_update", "vec_b200_scale", "vec_b200_putscalar",
+            "vec_b200_multiply", "vec_b200_reciprocal", "thcm_b200_average_block", "thcm_b200_scal", "thcm_b200_recompute_scaling",
+            "thcm_b200_left_scale", "thcm_b200_block_jacobi",
             "gmres_b200_solve", "gmres_b200_solve_host", "thcm_b200_launch_count", "thcm_b200_timing_enable",
             "thcm_b200_timing_reset", "thcm_b200_timing_get", "iemic_b200_malloc", "iemic_b200_free",
             "iemic_b200_memcpy_h2d", "iemic_b200_memcpy_d2h"]
@@ -293,6 +298,34 @@ class Ocean:
 
     def update(self, a, d_A, b, d_this):
         check(lib().vec_b200_update(self.h, float(a), _ptr(d_A), float(b), _ptr(d_this)))
+
+    def multiply(self, a, d_A, d_B, b, d_this):
+        check(lib().vec_b200_multiply(self.h, float(a), _ptr(d_A), _ptr(d_B), float(b), _ptr(d_this)))
+
+    def reciprocal(self, d_A, d_this):
+        check(lib().vec_b200_reciprocal(self.h, _ptr(d_A), _ptr(d_this)))
+
+    # ---- scaling and point-block Jacobi on the current Jacobian (THCM::RecomputeScaling, Ocean::scaleProblem) ----
+    def average_block(self):
+        """m_scaling::average_block: 6x6 array db[ii, jj]"""
+        db = np.zeros(36)
+        check(lib().thcm_b200_average_block(self.h, db.ctypes.data_as(C.POINTER(C.c_double))))
+        return db.reshape(6, 6).T.copy()  # column-major on the C side
+
+    def recompute_scaling(self, d_rowscal=None, d_colscal=None):
+        """THCM::RecomputeScaling; returns the six row and six column factors of ocean cells"""
+        rs, cs = np.zeros(6), np.zeros(6)
+        check(lib().thcm_b200_recompute_scaling(self.h, _ptr(d_rowscal), _ptr(d_colscal), rs.ctypes.data_as(C.POINTER(C.c_double)),
+                                                cs.ctypes.data_as(C.POINTER(C.c_double))))
+        return rs, cs
+
+    def left_scale(self, d_scal):
+        check(lib().thcm_b200_left_scale(self.h, _ptr(d_scal)))
+
+    def block_jacobi(self, d_blockinv):
+        ns = C.c_int(0)
+        check(lib().thcm_b200_block_jacobi(self.h, _ptr(d_blockinv), C.byref(ns)))
+        return ns.value
 
     def set_stream(self, stream_ptr):
         check(lib().thcm_b200_set_stream(self.h, C.c_void_p(int(stream_ptr))))

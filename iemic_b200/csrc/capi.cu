@@ -58,11 +58,13 @@ struct thcm_b200 {
   int* d_blkrow = nullptr; int nblk = 0; size_t d_frc_len = 0;
   int* d_blkp0 = nullptr; unsigned char* d_blkreg = nullptr; SpmvTab spmv_tab; size_t spmv_regular_cells = 0;
   uint64_t dev_version = 0, dev_mask_version = 0;
+  unsigned int* d_dinfo = nullptr; uint64_t dinfo_mask_version = 0; // diagonal-block positions (scaling.cu), built on first use
   // scratch vectors for the host-buffer entry points
   double *d_xs = nullptr, *d_ys = nullptr;
   // reductions and small device scalars
   RedBuf rb{nullptr, nullptr, 0};
-  double* d_small = nullptr; // [0,512) h1, [512,1024) h2, 1024 nrm2, 1025 hnext, 1026 bnorm, 1027 beta, 1028 dot, 1029 intcond
+  double* d_small = nullptr; // [0,512) h1, [512,1024) h2, 1024 nrm2, 1025 hnext, 1026 bnorm, 1027 beta, 1028 dot, 1029 intcond,
+                             // [1030,1067) average block + count, [1070,1088) Fortran-level centre entries of the special rows, 1090 int counter
   GmresWs g;
   long long launches = 0;
   bool timing = false;
@@ -213,6 +215,7 @@ AsmArgs asm_args(thcm_b200* h, const double* d_x) {
   a.x = d_x; a.sig = h->d_sig; a.rowptr = h->d_rowptr; a.frc = h->d_frc; a.val = h->d_val; a.diagB = h->d_diagB;
   a.sp.rowintcon = H->owns_rowintcon ? H->rowintcon_local : -1;
   a.sp.rowPfix1 = H->rowPfix1_local; a.sp.rowPfix2 = H->rowPfix2_local;
+  a.sp.side = (a.sp.rowintcon >= 0 || a.sp.rowPfix1 >= 0 || a.sp.rowPfix2 >= 0) ? h->d_small + 1070 : nullptr;
   return a;
 }
 int check_launch(thcm_b200* h, const char* what) {
@@ -318,7 +321,7 @@ int thcm_b200_destroy(thcm_b200_t* h) {
   CHECK_H(h);
   cudaStreamSynchronize(h->stream);
   flush_timing(h);
-  void* ptrs[] = {h->d_tab, h->d_sig, h->d_rowptr, h->d_col, h->d_val, h->d_diagB, h->d_frc, h->d_coefS, h->d_blkrow, h->d_blkp0, h->d_blkreg, h->d_xs, h->d_ys,
+  void* ptrs[] = {h->d_tab, h->d_sig, h->d_rowptr, h->d_col, h->d_val, h->d_diagB, h->d_frc, h->d_coefS, h->d_blkrow, h->d_blkp0, h->d_blkreg, h->d_xs, h->d_ys, h->d_dinfo,
                   h->rb.partial, h->rb.ticket, h->d_small};
   for (void* p : ptrs) if (p) cudaFree(p);
   gmres_free(h->g);
@@ -629,6 +632,106 @@ int thcm_b200_spmv_host(thcm_b200_t* h, const double* x, double* y) {
   CU(cudaMemcpyAsync(y, h->d_ys, nb, cudaMemcpyDeviceToHost, h->stream));
   CU(cudaStreamSynchronize(h->stream));
   return 0;
+}
+
+// ---- diagonal blocks: THCM scaling (THCM::RecomputeScaling, THCM.C:1694-1750), point-block Jacobi, row scaling ----
+namespace {
+int diag_args(thcm_b200* h, DiagArgs& a, int stored_rows) {
+  if (int rc = refresh_device(h)) return rc;
+  Host* H = h->host;
+  if (!h->d_dinfo || h->dinfo_mask_version != H->mask_version) {
+    std::vector<unsigned> info;
+    try { info = H->diag_info(); } catch (const std::exception& e) { return fail(IEMIC_B200_EINVAL, e.what()); }
+    if (int rc = dev_upload(&h->d_dinfo, info)) return rc;
+    h->dinfo_mask_version = H->mask_version;
+  }
+  a.rowptr = h->d_rowptr; a.dinfo = h->d_dinfo; a.val = h->d_val; a.sig = h->d_sig; a.ncell = h->nrows() / 6;
+  a.sp.rowintcon = H->owns_rowintcon ? H->rowintcon_local : -1;
+  a.sp.rowPfix1 = H->rowPfix1_local; a.sp.rowPfix2 = H->rowPfix2_local;
+  a.sp.side = h->d_small + 1070;
+  a.stored_rows = stored_rows;
+  return 0;
+}
+} // namespace
+
+int thcm_b200_average_block(thcm_b200_t* h, double* db) {
+  CHECK_H(h);
+  if (!db) return fail(IEMIC_B200_EINVAL, "average_block: null output");
+  DiagArgs a;
+  if (int rc = diag_args(h, a, 0)) return rc;
+  double* out = h->d_small + 1030;
+  launch_average_block(a, h->rb.partial, h->rb.ticket + 8, out, h->stream);
+  h->launches++;
+  if (int rc = check_launch(h, "average_block")) return rc;
+  if (int rc = allreduce(h, out, 37)) return rc;
+  double s[37];
+  CU(cudaMemcpyAsync(s, out, sizeof(s), cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  const double nl = s[36];
+  for (int ii = 0; ii < 6; ii++) for (int jj = 0; jj < 6; jj++) db[ii + 6 * jj] = nl > 0.0 ? s[ii * 6 + jj] / nl : s[ii * 6 + jj];
+  return 0;
+}
+
+int thcm_b200_scal(const double* db, double* dr, double* dc) {
+  if (!db || !dr || !dc) return fail(IEMIC_B200_EINVAL, "scal: null argument");
+  return scal(db, dr, dc) ? 0 : fail(IEMIC_B200_EINVAL, "thcm scaling: diagonal block is singular up to working precision");
+}
+
+int thcm_b200_recompute_scaling(thcm_b200_t* h, double* d_rowscal, double* d_colscal, double* rs6, double* cs6) {
+  CHECK_H(h);
+  double db[36], dr[6], dc[6];
+  if (int rc = thcm_b200_average_block(h, db)) return rc;
+  if (!scal(db, dr, dc)) return fail(IEMIC_B200_EINVAL, "thcm scaling: diagonal block is singular up to working precision");
+  ScalTab t;
+  for (int q = 0; q < 6; q++) { t.r[q] = 1.0 / dr[q]; t.c[q] = 1.0 / dc[q]; } // Trilinos' are the inverse of THCM's, THCM.C:1726-1730
+  double mean = 0.5 * (t.r[4] + t.r[5]); t.r[4] = mean; t.r[5] = mean;       // T and S scaled alike, THCM.C:1736-1745
+  mean = 0.5 * (t.c[4] + t.c[5]); t.c[4] = mean; t.c[5] = mean;
+  if (rs6) std::memcpy(rs6, t.r, sizeof(t.r));
+  if (cs6) std::memcpy(cs6, t.c, sizeof(t.c));
+  if (d_rowscal || d_colscal) {
+    launch_scaling_fill(h->d_sig, h->nrows(), t, d_rowscal, d_colscal, h->stream);
+    h->launches++;
+    return check_launch(h, "scaling_fill");
+  }
+  return 0;
+}
+
+int thcm_b200_block_jacobi(thcm_b200_t* h, double* d_blockinv, int* nsingular) {
+  CHECK_H(h);
+  if (!d_blockinv) return fail(IEMIC_B200_EINVAL, "block_jacobi: null output");
+  DiagArgs a;
+  if (int rc = diag_args(h, a, 1)) return rc;
+  int* d_cnt = reinterpret_cast<int*>(h->d_small + 1090);
+  CU(cudaMemsetAsync(d_cnt, 0, sizeof(int), h->stream));
+  launch_block_inverse(a, d_blockinv, d_cnt, h->stream);
+  h->launches++;
+  if (int rc = check_launch(h, "block_inverse")) return rc;
+  if (nsingular) {
+    CU(cudaMemcpyAsync(nsingular, d_cnt, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+  }
+  return 0;
+}
+
+int thcm_b200_left_scale(thcm_b200_t* h, const double* d_scal) {
+  CHECK_H(h);
+  if (int rc = refresh_device(h)) return rc;
+  launch_left_scale(h->d_rowptr, h->d_val, d_scal, h->nrows(), h->stream);
+  h->launches++;
+  return check_launch(h, "left_scale");
+}
+
+int vec_b200_multiply(thcm_b200_t* h, double a, const double* A, const double* B, double b, double* y) {
+  CHECK_H(h);
+  launch_multiply(a, A, B, b, y, h->nrows(), h->stream);
+  h->launches++;
+  return check_launch(h, "multiply");
+}
+int vec_b200_reciprocal(thcm_b200_t* h, const double* A, double* y) {
+  CHECK_H(h);
+  launch_reciprocal(A, y, h->nrows(), h->stream);
+  h->launches++;
+  return check_launch(h, "reciprocal");
 }
 
 // ---- vectors ----

@@ -217,4 +217,27 @@ EXPORT void __m_thcm_utils_MOD_intcond_scaling(double* values, int* indices, int
   *len = v;
 }
 
+
+// m_scaling (src/ocean/scaling.F90), as THCM::RecomputeScaling calls it (THCM.C:1707-1721): average_block on the matrix of the
+// last matrix_ call, then -- after the caller's SumAll / NumProc -- compute() with the globally averaged block.  The
+// block average runs on the device; compute() hands out THCM-convention factors (the caller takes the reciprocals).
+EXPORT void __m_scaling_MOD_average_block(double* db) {
+  need_model("m_scaling::average_block");
+  if (thcm_b200_average_block(M.h, db) != 0) die("m_scaling::average_block");
+}
+EXPORT void __m_scaling_MOD_compute(double* db, double* row_scaling, double* col_scaling) {
+  need_model("m_scaling::compute");
+  double dr[6], dc[6];
+  if (thcm_b200_scal(db, dr, dc) != 0) { // scaling.F90:233-236: message, and the vectors stay as they are
+    std::fprintf(stderr, " thcm scaling: diagonal block is singular up to working precision\n");
+    return;
+  }
+  const int n = M.cfg.n, m = M.cfg.m, l = M.cfg.l;
+  for (int k = 1; k <= l; k++) for (int j = 1; j <= m; j++) for (int i = 1; i <= n; i++) {
+    const bool ocean = M.landm[((size_t)k * (m + 2) + j) * (n + 2) + i] == 0;
+    const size_t r = 6 * (((size_t)(k - 1) * m + (j - 1)) * n + (i - 1));
+    for (int ii = 0; ii < 6; ii++) { row_scaling[r + ii] = ocean ? dr[ii] : 1.0; col_scaling[r + ii] = ocean ? dc[ii] : 1.0; }
+  }
+}
+
 } // extern "C"

@@ -54,6 +54,27 @@ int spmv_nnz_cap();
 int spmv_rows_cap();
 int spmv_regular_cells(); // regular cells per block
 
+// ---- diagonal 6x6 blocks of the Jacobian: THCM scaling, point-block Jacobi, row scaling (scaling.cu) ----
+struct DiagArgs {
+  const int* rowptr;
+  const unsigned int* dinfo;  // per row: bits 0..25 offset of the first centre-cell entry inside the row, bits 26..31 unknowns present
+  const double* val;
+  const uint64_t* sig;
+  long long ncell;            // owned cells
+  SpecialRows sp;             // rows overwritten by the C++ glue and the side buffer holding their Fortran-level centre entries
+  int stored_rows;            // 1: take those rows as stored (the matrix GMRES sees); 0: as the Fortran built them (m_scaling)
+};
+struct ScalTab { double r[6], c[6]; }; // per-unknown factors on ocean cells (land rows: 1)
+int average_block_partials(); // doubles of workspace launch_average_block needs
+// out37[ii*6+jj] = sum over owned OCEAN cells of J(6c+ii,6c+jj), out37[36] = their number (scaling.F90:29-62)
+void launch_average_block(const DiagArgs& a, double* partial, unsigned int* ticket, double* out37, cudaStream_t st);
+void launch_scaling_fill(const uint64_t* sig, long long nrows, const ScalTab& t, double* rowscal, double* colscal, cudaStream_t st);
+// binv[c] = inverse of the diagonal block of cell c, row-major (identity where the block is singular, counted in *nsingular)
+void launch_block_inverse(const DiagArgs& a, double* binv, int* nsingular, cudaStream_t st);
+void launch_left_scale(const int* rowptr, double* val, const double* s, long long nrows, cudaStream_t st); // val(row,:) *= s[row]
+void launch_multiply(double a, const double* A, const double* B, double b, double* y, long long n, cudaStream_t st); // y = a*A.*B + b*y
+void launch_reciprocal(const double* A, double* y, long long n, cudaStream_t st);
+
 // ---- vector / GMRES kernels (gmres.cu) ----
 struct RedBuf { double* partial; unsigned int* ticket; int nblk_max; }; // workspace for block-partial reductions
 int red_blocks();

@@ -6,7 +6,18 @@
 namespace thcm {
 
 // Rows the C++ glue of the reference overwrites after the Fortran call (THCM.C:1006-1033, :1160-1165).
-struct SpecialRows { int rowintcon, rowPfix1, rowPfix2; };
+// `side` (optional, 18 doubles): the centre-slot entries An(5,A,1:6) of those three rows as the Fortran built them,
+// which m_scaling::average_block (scaling.F90:29-62) reads from the Fortran CSR and the overwritten rows no longer hold.
+struct SpecialRows { int rowintcon, rowPfix1, rowPfix2; double* side; };
+template <int A> THCM_HD void save_centre(Row<A>& r, double* dst) {
+  dst[0] = 0.0; dst[1] = 0.0; dst[2] = 0.0; dst[3] = 0.0; dst[4] = 0.0; dst[5] = 0.0;
+  if constexpr (Row<A>::template has<5, UU>()) dst[0] = r.template at<5, UU>();
+  if constexpr (Row<A>::template has<5, VV>()) dst[1] = r.template at<5, VV>();
+  if constexpr (Row<A>::template has<5, WW>()) dst[2] = r.template at<5, WW>();
+  if constexpr (Row<A>::template has<5, PP>()) dst[3] = r.template at<5, PP>();
+  if constexpr (Row<A>::template has<5, TT>()) dst[4] = r.template at<5, TT>();
+  if constexpr (Row<A>::template has<5, SS>()) dst[5] = r.template at<5, SS>();
+}
 
 // Jacobian row A of cell c -> `out` (first stored value of the row in the static CSR), returns diag(B) entry.
 // The integral-condition row is left untouched (its dense values are static, written by jac_intcond_row).
@@ -29,9 +40,13 @@ THCM_HD double jac_row(const Scalars& S, const Tables& T, const Cell& c, const F
     if (A == VV) b = sbit(c.sig, SIG_BV) ? -S.epsr : 0.0;
     if (A == TT || A == SS) b = -1.0;
   }
-  if (row == sp.rowintcon) return 0.0;                    // intcond_S, THCM.C:2137-2139
+  if (row == sp.rowintcon) {                              // intcond_S, THCM.C:2137-2139
+    if constexpr (A == SS) { if (sp.side) save_centre<A>(r, sp.side); } // the integral row replaces an S row
+    return 0.0;
+  }
   if constexpr (A == PP) {
     if (row == sp.rowPfix1 || row == sp.rowPfix2) { // fixPressurePoints, THCM.C:2201-2238
+      if (sp.side) save_centre<A>(r, sp.side + (row == sp.rowPfix1 ? 6 : 12));
       r.clear();
       r.template at<5, PP>() = 1.0;
       b = 0.0;

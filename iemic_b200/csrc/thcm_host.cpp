@@ -566,4 +566,82 @@ void Host::build_graph() {
   rowptr[nrows] = (int)col.size();
 }
 
+// Where the 6x6 diagonal block sits inside every row of the static graph: offset of the first entry whose column belongs
+// to the row's own cell (bits 0..25) and which unknowns are present (bits 26..31).  The centre-slot entries are adjacent
+// in both the static (dk,dj,di,var) order and the sorted order of seam rows.
+std::vector<unsigned> Host::diag_info() const {
+  const size_t nrows = rowptr.size() - 1;
+  std::vector<unsigned> info(nrows, 0u);
+  for (size_t r = 0; r < nrows; r++) {
+    const int cell = (int)(r / 6);
+    int first = -1;
+    unsigned mask = 0;
+    for (int p = rowptr[r]; p < rowptr[r + 1]; p++)
+      if (col[p] / 6 == cell) {
+        if (first < 0) first = p - rowptr[r];
+        mask |= 1u << (col[p] % 6);
+      }
+    if (first < 0) first = 0;
+    if (first >= (1 << 26)) throw std::runtime_error("diag_info: row too long");
+    info[r] = (unsigned)first | (mask << 26);
+  }
+  return info;
+}
+
+// m_scaling::scal (src/ocean/scaling.F90:198-284): invert the averaged 6x6 block and derive the row / column factors
+// "special for the oceanography problem".  db is column-major like the Fortran array, db[ii + 6*jj].  The reference calls
+// LAPACK dgetrf / dgecon / dgetri; here: LU with partial pivoting (the dgetf2 pivot rule), the inverse column by column,
+// and the exact 1/(|A|_inf |A^-1|_inf) where dgecon estimates it (used only for the singularity test :233-236).
+bool scal(const double* db, double* dr, double* dc) {
+  const int N = 6;
+  double A[N][N], LU[N][N], inv[N][N];
+  for (int i = 0; i < N; i++) for (int j = 0; j < N; j++) { A[i][j] = db[i + N * j]; LU[i][j] = A[i][j]; }
+  double anorm = 0.0;
+  for (int i = 0; i < N; i++) { double s = 0.0; for (int j = 0; j < N; j++) s += std::fabs(A[i][j]); anorm = std::max(anorm, s); }
+  int piv[N];
+  for (int k = 0; k < N; k++) {
+    int p = k;
+    for (int i = k + 1; i < N; i++) if (std::fabs(LU[i][k]) > std::fabs(LU[p][k])) p = i;
+    piv[k] = p;
+    if (LU[p][k] == 0.0) return false;
+    if (p != k) for (int j = 0; j < N; j++) std::swap(LU[k][j], LU[p][j]);
+    for (int i = k + 1; i < N; i++) {
+      LU[i][k] /= LU[k][k];
+      for (int j = k + 1; j < N; j++) LU[i][j] -= LU[i][k] * LU[k][j];
+    }
+  }
+  for (int c = 0; c < N; c++) {
+    double b[N];
+    for (int i = 0; i < N; i++) b[i] = (i == c) ? 1.0 : 0.0;
+    for (int k = 0; k < N; k++) std::swap(b[k], b[piv[k]]);
+    for (int i = 1; i < N; i++) for (int j = 0; j < i; j++) b[i] -= LU[i][j] * b[j];
+    for (int i = N - 1; i >= 0; i--) { for (int j = i + 1; j < N; j++) b[i] -= LU[i][j] * b[j]; b[i] /= LU[i][i]; }
+    for (int i = 0; i < N; i++) inv[i][c] = b[i];
+  }
+  double inorm = 0.0;
+  for (int i = 0; i < N; i++) { double s = 0.0; for (int j = 0; j < N; j++) s += std::fabs(inv[i][j]); inorm = std::max(inorm, s); }
+  const double rcond = (anorm > 0.0 && inorm > 0.0) ? (1.0 / anorm) / inorm : 0.0;
+  if (1.0 + rcond == 1.0) return false; // "diagonal block is singular up to working precision"
+  auto mat = [&](int i, int j) -> double& { return inv[i - 1][j - 1]; }; // 1-based like the Fortran
+  double idc, idr;
+  dr[0] = 1.0; dc[0] = 1.0;
+  idc = std::sqrt(mat(1, 1) / mat(2, 2));
+  dr[1] = 1 / idc; dc[1] = dr[1];
+  idr = std::sqrt(std::fabs(mat(1, 1) / mat(4, 4)));
+  dr[3] = 1 / idr; dc[3] = dr[3];
+  if (std::fabs(mat(4, 3)) > std::fabs(mat(3, 3))) idr = mat(1, 1) / (idr * mat(4, 3));
+  else idr = std::sqrt(std::fabs(mat(1, 1) / mat(3, 3)));
+  dr[2] = 2 / idr; dc[2] = dr[2];
+  if (std::fabs(mat(4, 5) * mat(5, 4)) < .01 * std::fabs(mat(4, 4) * mat(5, 5))) { mat(4, 5) = 1; mat(5, 4) = 1; }
+  idc = std::sqrt(std::fabs(mat(1, 1) * mat(4, 5) / (mat(5, 4) * mat(5, 5))));
+  idr = mat(1, 1) / (idc * mat(5, 5));
+  dr[4] = 1 / idr; dc[4] = 1 / idc;
+  if (std::fabs(mat(4, 6) * mat(6, 4)) < .01 * std::fabs(mat(4, 4) * mat(6, 6))) { mat(4, 6) = 1; mat(6, 4) = 1; }
+  idc = std::sqrt(std::fabs(mat(1, 1) * mat(4, 6) / (mat(6, 4) * mat(6, 6))));
+  idr = mat(1, 1) / (idc * mat(6, 6));
+  dr[5] = 1 / idr; dc[5] = 1 / idc;
+  return true;
+}
+
+
 } // namespace thcm

@@ -75,6 +75,8 @@ class Host {
   size_t nvec_local() const { return gid.size(); }
   double intcond_col(int col) const { return intcond[(size_t)col]; } // coefficient of stored column `col`
 
+  std::vector<unsigned> diag_info() const; // per row: where its own cell's 6x6 block entries sit (scaling.cu)
+
   size_t frc_dirty_from = 0; // first row of `frc` a device copy made before the last change does not have yet
   Tables tables(const double* base) const; // pointers into a (host or device) copy of `tab`
   inline int lm(int i, int j, int k) const { return landm[(size_t)i + (size_t)(n + 2) * (j + (size_t)(m + 2) * k)]; }
@@ -90,5 +92,9 @@ class Host {
   void build_graph();
   void check_supported() const;
 };
+
+// m_scaling::scal (scaling.F90:198-284): db[ii+6*jj] averaged diagonal block -> six row and six column factors (THCM
+// convention; Trilinos uses the reciprocals).  false: block singular to working precision (dr, dc untouched).
+bool scal(const double* db, double* dr, double* dc);
 
 } // namespace thcm

@@ -126,6 +126,34 @@ int vec_b200_update(thcm_b200_t* h, double a, const double* d_A, double b, doubl
 int vec_b200_scale(thcm_b200_t* h, double a, double* d_this);
 int vec_b200_putscalar(thcm_b200_t* h, double a, double* d_this);
 
+int vec_b200_multiply(thcm_b200_t* h, double a, const double* d_A, const double* d_B, double b, double* d_this); /* this = a*A.*B + b*this (Epetra Multiply, Ocean.C:1213,1241) */
+int vec_b200_reciprocal(thcm_b200_t* h, const double* d_A, double* d_this);                                      /* this = 1./A (Ocean.C:1195) */
+
+/* ---- diagonal 6x6 blocks of the handle's current Jacobian: scaling and the fixed point-block-Jacobi preconditioner ----
+ * thcm_b200_average_block      m_scaling::average_block (src/ocean/scaling.F90:29-62) followed by the SumAll of
+ *                              THCM::RecomputeScaling (src/ocean/THCM.C:1711-1718): db[ii + 6*jj] (host, column-major like the
+ *                              Fortran array) = mean over all OCEAN cells of J(6c+ii, 6c+jj).  Rows the C++ glue overwrites
+ *                              (integral condition, pressure fix) enter with the values the Fortran built, as in the reference.
+ *                              On several GPUs the mean is the global one (sums and counts are all-reduced): independent of the
+ *                              decomposition and equal to the reference on one rank; the reference's own multi-rank result is
+ *                              the mean of per-rank means over ghosted sub-domains (THCM.C:1713-1718) and depends on the rank count.
+ * thcm_b200_recompute_scaling  THCM::RecomputeScaling (THCM.C:1694-1750): m_scaling::scal + compute (scaling.F90:69-99, 198-284),
+ *                              reciprocals and T/S averaging; fills the device vectors d_rowscal / d_colscal (nrows_local each,
+ *                              either may be NULL; land rows get 1) = THCM::getRowScaling / getColScaling, and optionally the
+ *                              six per-unknown factors on the host (rs6 / cs6).  IEMIC_B200_EINVAL if the block is singular.
+ * thcm_b200_left_scale         Epetra_CrsMatrix::LeftScale on the Jacobian values (Ocean::scaleProblem / unscaleProblem,
+ *                              src/ocean/Ocean.C:1207, 1238): val(row,:) *= d_scal[row].
+ * thcm_b200_block_jacobi       d_blockinv[36*c ..] = inverse (row-major) of the 6x6 diagonal block of owned cell c of the matrix
+ *                              as stored (the operator gmres_b200_solve applies); singular blocks become the identity and are
+ *                              counted in *nsingular (may be NULL: no synchronisation then). */
+int thcm_b200_average_block(thcm_b200_t* h, double* db36);
+/* m_scaling::scal (scaling.F90:198-284) alone, host arithmetic on 36 numbers: db36 column-major -> THCM-convention factors
+ * dr6 / dc6 (Trilinos uses their reciprocals).  IEMIC_B200_EINVAL: block singular to working precision, outputs untouched. */
+int thcm_b200_scal(const double* db36, double* dr6, double* dc6);
+int thcm_b200_recompute_scaling(thcm_b200_t* h, double* d_rowscal, double* d_colscal, double* rs6, double* cs6);
+int thcm_b200_left_scale(thcm_b200_t* h, const double* d_scal);
+int thcm_b200_block_jacobi(thcm_b200_t* h, double* d_blockinv, int* nsingular);
+
 /* ---- GMRES(m) on the handle's Jacobian (GMRESSolver.H:81-255) ----
  * ortho: GMRES_B200_MGS reproduces the reference's modified Gram-Schmidt loop (:177-181); GMRES_B200_CGS2 is the
  * fused two-pass classical Gram-Schmidt (three reductions per step: h1, h2, norm); GMRES_B200_CGS2F is the same

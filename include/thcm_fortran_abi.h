@@ -28,6 +28,8 @@
  *   matrix_                             src/ocean/usrc.F90:432-504       (coA/jcoA/begA by fillcolA's rule, coB)
  *   fillcolb_                           src/ocean/assemble.F90:18-54
  *   __m_thcm_utils_MOD_intcond_scaling  src/ocean/thcm_utils.F90:285-323
+ *   __m_scaling_MOD_average_block       src/ocean/scaling.F90:29-62      (db(6,6) column-major; called at THCM.C:1709)
+ *   __m_scaling_MOD_compute             src/ocean/scaling.F90:69-99      (THCM-convention factors; called at THCM.C:1721)
  */
 #ifndef THCM_FORTRAN_ABI_H
 #define THCM_FORTRAN_ABI_H
@@ -64,6 +66,8 @@ void matrix_(double* un);
 void fillcolb_(void);
 
 void __m_thcm_utils_MOD_intcond_scaling(double* values, int* indices, int* len);
+void __m_scaling_MOD_average_block(double* db);
+void __m_scaling_MOD_compute(double* db, double* row_scaling, double* col_scaling);
 
 #ifdef __cplusplus
 }

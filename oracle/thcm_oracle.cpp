@@ -1648,6 +1648,114 @@ void thcm_oracle_eval_jac(thcm_oracle* t, const double* x, double* val, double* 
   }
 }
 
+// ---- m_scaling (src/ocean/scaling.F90) and THCM::RecomputeScaling (src/ocean/THCM.C:1694-1750), single process ----
+// scaling.F90:29-62: average diagonal block over OCEAN cells, read from the Fortran CSR of the last matrix() call.
+// db is the Fortran array db(nun,nun), column-major: db[(ii-1) + 6*(jj-1)].
+void thcm_oracle_average_block(thcm_oracle* t, double* db) {
+  for (int q = 0; q < NUN * NUN; q++) db[q] = 0.0;
+  int nl = 0;
+  for (int i = 1; i <= t->ndim; i++) {
+    int ix, iy, iz, ii; findex(*t, i, ix, iy, iz, ii);
+    if (t->lm(ix, iy, iz) == OCEAN) {
+      if (ii == PP) nl = nl + 1;
+      for (int j = t->begA[i - 1]; j <= t->begA[i] - 1; j++) {
+        int jx, jy, jz, jj; findex(*t, t->jcoA[j - 1], jx, jy, jz, jj);
+        if (ix == jx && iy == jy && iz == jz) db[(ii - 1) + NUN * (jj - 1)] = db[(ii - 1) + NUN * (jj - 1)] + t->coA[j - 1];
+      }
+    }
+  }
+  if (nl > 0) for (int q = 0; q < NUN * NUN; q++) db[q] = db[q] / nl;
+}
+// scaling.F90:198-284 (the LAPACK variant that is compiled, "#if 0 ... #else").  dgetrf/dgetri are restated as LU with
+// partial pivoting (dgetf2's rule: first row of maximal modulus) and inv(A) from inv(U) and the unit lower factor, the
+// way dgetri forms it; dgecon's estimate only feeds the test 1.0+rcond==1.0 and is replaced by the exact reciprocal
+// condition number in the infinity norm.  tests/test_scaling_cpu.py pins this against LAPACK itself (scipy).
+// Returns 0 if the block is singular to working precision (the Fortran returns with dr, dc unset).
+int thcm_oracle_scal(const double* mat_in, double* dr, double* dc) {
+  const int N = NUN;
+  double a[NUN][NUN]; // a[i][j] = mat(i+1,j+1)
+  for (int i = 0; i < N; i++) for (int j = 0; j < N; j++) a[i][j] = mat_in[i + N * j];
+  double Anorm = 0.0;
+  for (int i = 0; i < N; i++) { double s = 0.0; for (int j = 0; j < N; j++) s += std::fabs(a[i][j]); Anorm = std::max(Anorm, s); }
+  int ipvt[NUN];
+  for (int k = 0; k < N; k++) { // dgetf2
+    int p = k;
+    for (int i = k + 1; i < N; i++) if (std::fabs(a[i][k]) > std::fabs(a[p][k])) p = i;
+    ipvt[k] = p;
+    if (a[p][k] == 0.0) return 0;
+    if (p != k) for (int j = 0; j < N; j++) std::swap(a[k][j], a[p][j]);
+    const double r = 1.0 / a[k][k];
+    for (int i = k + 1; i < N; i++) a[i][k] *= r;
+    for (int j = k + 1; j < N; j++) for (int i = k + 1; i < N; i++) a[i][j] -= a[i][k] * a[k][j];
+  }
+  // dgetri: inv(U) in place (dtrtri, upper, non-unit) ...
+  for (int j = 0; j < N; j++) {
+    a[j][j] = 1.0 / a[j][j];
+    const double ajj = -a[j][j];
+    for (int i = 0; i < j; i++) { // column j above the diagonal := inv(U)(0:j,0:j) * U(0:j,j), then scaled by ajj
+      double s = 0.0;
+      for (int k2 = i; k2 < j; k2++) s += a[i][k2] * a[k2][j];
+      a[i][j] = s;
+    }
+    for (int i = 0; i < j; i++) a[i][j] *= ajj;
+  }
+  // ... then solve inv(A)*L = inv(U) column by column from the right, and undo the row interchanges as column swaps
+  for (int j = N - 2; j >= 0; j--) {
+    double work[NUN];
+    for (int i = j + 1; i < N; i++) { work[i] = a[i][j]; a[i][j] = 0.0; }
+    for (int k2 = j + 1; k2 < N; k2++) for (int i = 0; i < N; i++) a[i][j] -= a[i][k2] * work[k2];
+  }
+  for (int j = N - 2; j >= 0; j--) {
+    const int jp = ipvt[j];
+    if (jp != j) for (int i = 0; i < N; i++) std::swap(a[i][j], a[i][jp]);
+  }
+  double Inorm = 0.0;
+  for (int i = 0; i < N; i++) { double s = 0.0; for (int j = 0; j < N; j++) s += std::fabs(a[i][j]); Inorm = std::max(Inorm, s); }
+  const double rcond = (Anorm > 0.0 && Inorm > 0.0) ? (1.0 / Anorm) / Inorm : 0.0;
+  if (1.0 + rcond == 1.0) return 0;
+#define MAT(i, j) a[(i) - 1][(j) - 1]
+  double idc, idr;
+  dr[0] = 1.0; dc[0] = 1.0;
+  idc = std::sqrt(MAT(1, 1) / MAT(2, 2));
+  dr[1] = 1 / idc; dc[1] = dr[1];
+  idr = std::sqrt(std::fabs(MAT(1, 1) / MAT(4, 4)));
+  dr[3] = 1 / idr; dc[3] = dr[3];
+  if (std::fabs(MAT(4, 3)) > std::fabs(MAT(3, 3))) idr = MAT(1, 1) / (idr * MAT(4, 3));
+  else idr = std::sqrt(std::fabs(MAT(1, 1) / MAT(3, 3)));
+  dr[2] = 2 / idr; dc[2] = dr[2];
+  if (std::fabs(MAT(4, 5) * MAT(5, 4)) < .01 * std::fabs(MAT(4, 4) * MAT(5, 5))) { MAT(4, 5) = 1; MAT(5, 4) = 1; }
+  idc = std::sqrt(std::fabs(MAT(1, 1) * MAT(4, 5) / (MAT(5, 4) * MAT(5, 5))));
+  idr = MAT(1, 1) / (idc * MAT(5, 5));
+  dr[4] = 1 / idr; dc[4] = 1 / idc;
+  if (std::fabs(MAT(4, 6) * MAT(6, 4)) < .01 * std::fabs(MAT(4, 4) * MAT(6, 6))) { MAT(4, 6) = 1; MAT(6, 4) = 1; }
+  idc = std::sqrt(std::fabs(MAT(1, 1) * MAT(4, 6) / (MAT(6, 4) * MAT(6, 6))));
+  idr = MAT(1, 1) / (idc * MAT(6, 6));
+  dr[5] = 1 / idr; dc[5] = 1 / idc;
+#undef MAT
+  return 1;
+}
+// THCM.C:1694-1750 on one process (SumAll / NumProc are identities): average_block, scal + compute (scaling.F90:69-99),
+// reciprocals, then T and S rows share the mean of their two factors.  Returns 0 if the block is singular.
+int thcm_oracle_recompute_scaling(thcm_oracle* t, double* rowScaling, double* colScaling) {
+  double gdb[NUN * NUN], rs[NUN], cs[NUN];
+  thcm_oracle_average_block(t, gdb);
+  if (!thcm_oracle_scal(gdb, rs, cs)) return 0;
+  for (int i = 1; i <= t->ndim; i++) {
+    int ix, iy, iz, ii; findex(*t, i, ix, iy, iz, ii);
+    double r = 1.0, c = 1.0;
+    if (t->lm(ix, iy, iz) == OCEAN) { r = rs[ii - 1]; c = cs[ii - 1]; }
+    rowScaling[i - 1] = 1.0 / r;
+    colScaling[i - 1] = 1.0 / c;
+  }
+  for (int i = TT - 1; i < t->ndim; i += NUN) {
+    double mean = 0.5 * (rowScaling[i] + rowScaling[i + 1]);
+    rowScaling[i] = mean; rowScaling[i + 1] = mean;
+    mean = 0.5 * (colScaling[i] + colScaling[i + 1]);
+    colScaling[i] = mean; colScaling[i + 1] = mean;
+  }
+  return 1;
+}
+
 void thcm_oracle_spmv(int nrows, const int* rowptr, const int* col, const double* val, const double* x, double* y) {
   for (int i = 0; i < nrows; i++) {
     double s = 0.0;

@@ -68,6 +68,12 @@ void thcm_oracle_intcond_coeff(thcm_oracle*, double* c /* ndim */);
 void thcm_oracle_set_intcond_correction(thcm_oracle*, double corr);
 int64_t thcm_oracle_dropped_entries(thcm_oracle*); /* Fortran entries outside the static graph in the last eval_jac */
 
+/* m_scaling::average_block / scal (scaling.F90:29-62, 198-284) on the Fortran CSR of the last fortran_matrix / eval_jac
+ * call, and THCM::RecomputeScaling (THCM.C:1694-1750) on one process.  db, mat: column-major 6x6. */
+void thcm_oracle_average_block(thcm_oracle*, double* db /* 36 */);
+int thcm_oracle_scal(const double* mat /* 36 */, double* dr /* 6 */, double* dc /* 6 */); /* 0: singular block */
+int thcm_oracle_recompute_scaling(thcm_oracle*, double* rowScaling /* ndim */, double* colScaling /* ndim */);
+
 /* matAvec-order CSR SpMV (matetc.F90:147-166), 0-based CSR. */
 void thcm_oracle_spmv(int nrows, const int* rowptr, const int* col, const double* val, const double* x, double* y);
 

@@ -86,6 +86,20 @@ class FortranTHCM:
         getattr(self.L, "__m_thcm_utils_MOD_intcond_scaling")(val.ctypes.data_as(C.POINTER(C.c_double)), ind.ctypes.data_as(C.POINTER(C.c_int)), C.byref(ln))
         return val[:ln.value], ind[:ln.value]
 
+    def recompute_scaling(self):
+        """THCM::RecomputeScaling on one process (THCM.C:1694-1750) through the m_scaling symbols"""
+        dp = lambda a: a.ctypes.data_as(C.POINTER(C.c_double))
+        db = np.zeros(36)
+        getattr(self.L, "__m_scaling_MOD_average_block")(dp(db))
+        rowscal, colscal = np.full(self.nrows, np.nan), np.full(self.nrows, np.nan)
+        getattr(self.L, "__m_scaling_MOD_compute")(dp(db), dp(rowscal), dp(colscal))
+        r, c = 1.0 / rowscal, 1.0 / colscal
+        for v in (r, c):
+            mean = 0.5 * (v[4::6] + v[5::6])
+            v[4::6] = mean
+            v[5::6] = mean
+        return db.reshape(6, 6).T.copy(), r, c
+
     def close(self):
         self.L.finalize_()
         getattr(self.L, "__m_global_MOD_finalize")()

@@ -70,11 +70,48 @@ void hostcheck_frc(void* h, double* frc) { Host* H = (Host*)h; memcpy(frc, H->fr
 void hostcheck_sig(void* h, unsigned long long* sig) { Host* H = (Host*)h; memcpy(sig, H->sig.data(), 8 * H->sig.size()); }
 void hostcheck_intcond(void* h, double* c) { Host* H = (Host*)h; memcpy(c, H->intcond.data(), sizeof(double) * H->nrows_local()); }
 
-void hostcheck_jac(void* h, const double* x, double* val, double* diagB) {
+static void jac_with_side(void* h, const double* x, double* val, double* diagB, double* side);
+void hostcheck_jac(void* h, const double* x, double* val, double* diagB) { jac_with_side(h, x, val, diagB, nullptr); }
+
+// The product's scaling path on the CPU: Jacobian rows with the side buffer of the special rows, the diagonal-block
+// positions of Host::diag_info, the sum over OCEAN cells exactly as average_block_kernel forms it (other order), thcm::scal.
+// db: column-major 6x6 like the C ABI; rs/cs: the Trilinos-convention factors of thcm_b200_recompute_scaling.  Returns 0 if singular.
+int hostcheck_scaling(void* h, const double* x, double* db, double* rs, double* cs) {
+  Host* H = (Host*)h;
+  std::vector<double> val(H->col.size()), diagB(H->nrows_local());
+  double side[18] = {0};
+  jac_with_side(h, x, val.data(), diagB.data(), side);
+  std::vector<unsigned> info = H->diag_info();
+  double sum[36] = {0}; double nl = 0.0;
+  const int sp[3] = {H->owns_rowintcon ? H->rowintcon_local : -1, H->rowPfix1_local, H->rowPfix2_local};
+  for (size_t r = 0; r < H->nrows_local(); r++) {
+    if (sbit(H->sig[r / 6], SIG_NOTOCEAN)) continue;
+    double d[6] = {0, 0, 0, 0, 0, 0};
+    int special = -1;
+    for (int q = 0; q < 3; q++) if ((int)r == sp[q]) special = q;
+    if (special >= 0) for (int b = 0; b < 6; b++) d[b] = side[6 * special + b];
+    else {
+      const double* p = val.data() + H->rowptr[r] + (info[r] & 0x3ffffffu);
+      for (int b = 0; b < 6; b++) if ((info[r] >> (26 + b)) & 1u) d[b] = *p++;
+    }
+    for (int b = 0; b < 6; b++) sum[(r % 6) * 6 + b] += d[b];
+    if (r % 6 == 3) nl += 1.0;
+  }
+  for (int ii = 0; ii < 6; ii++) for (int jj = 0; jj < 6; jj++) db[ii + 6 * jj] = nl > 0 ? sum[ii * 6 + jj] / nl : sum[ii * 6 + jj];
+  double dr[6], dc[6];
+  if (!scal(db, dr, dc)) return 0;
+  for (int q = 0; q < 6; q++) { rs[q] = 1.0 / dr[q]; cs[q] = 1.0 / dc[q]; }
+  double mean = 0.5 * (rs[4] + rs[5]); rs[4] = mean; rs[5] = mean;
+  mean = 0.5 * (cs[4] + cs[5]); cs[4] = mean; cs[5] = mean;
+  return 1;
+}
+int hostcheck_scal(const double* db, double* dr, double* dc) { return scal(db, dr, dc) ? 1 : 0; }
+
+static void jac_with_side(void* h, const double* x, double* val, double* diagB, double* side) {
   Host* H = (Host*)h;
   const Scalars& S = H->S;
   Tables T = H->tables(H->tab.data());
-  SpecialRows sp{H->owns_rowintcon ? H->rowintcon_local : -1, H->rowPfix1_local, H->rowPfix2_local};
+  SpecialRows sp{H->owns_rowintcon ? H->rowintcon_local : -1, H->rowPfix1_local, H->rowPfix2_local, side};
   for (size_t q = 0; q < H->col.size(); q++) val[q] = 0.0;
   for (int k = 1; k <= S.l; k++) for (int j = S.jo0; j < S.jo0 + S.mloc; j++) for (int i = S.io0; i < S.io0 + S.nloc; i++) {
     size_t ci = cell_index(S, i, j, k);

@@ -52,6 +52,8 @@ def lib():
         L.hostcheck_intcond.argtypes = [C.c_void_p, dp]
         L.hostcheck_jac.argtypes = [C.c_void_p, dp, dp, dp]
         L.hostcheck_rhs.argtypes = [C.c_void_p, dp, dp]
+        L.hostcheck_scaling.argtypes = [C.c_void_p, dp, dp, dp, dp]
+        L.hostcheck_scal.argtypes = [dp, dp, dp]
         _LIB = L
     return _LIB
 
@@ -133,6 +135,13 @@ class HostCheck:
         lib().hostcheck_rhs(self.h, _dp(x), _dp(F))
         return F
 
+    def scaling(self, x):
+        """(db[ii, jj], rs6, cs6) of the product's scaling path evaluated on the CPU; None if the block is singular"""
+        x = np.ascontiguousarray(x, np.float64)
+        db, rs, cs = np.zeros(36), np.zeros(6), np.zeros(6)
+        ok = lib().hostcheck_scaling(self.h, _dp(x), _dp(db), _dp(rs), _dp(cs))
+        return (db.reshape(6, 6).T.copy(), rs, cs) if ok else None
+
     def frc(self):
         f = np.zeros(self.ndim)
         lib().hostcheck_frc(self.h, _dp(f))
@@ -140,3 +149,10 @@ class HostCheck:
 
     def rowintcon(self):
         return lib().hostcheck_rowintcon(self.h)
+
+
+def scal(db):
+    """thcm::scal of the product on a 6x6 array db[ii, jj]: (dr, dc) or None if singular"""
+    a = np.ascontiguousarray(np.asarray(db, np.float64).T).ravel()  # column-major
+    dr, dc = np.zeros(6), np.zeros(6)
+    return (dr, dc) if lib().hostcheck_scal(_dp(a), _dp(dr), _dp(dc)) else None

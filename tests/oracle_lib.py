@@ -83,6 +83,9 @@ def lib():
         L.thcm_oracle_set_intcond_correction.argtypes = [C.c_void_p, C.c_double]
         L.thcm_oracle_dropped_entries.argtypes = [C.c_void_p]
         L.thcm_oracle_dropped_entries.restype = C.c_int64
+        L.thcm_oracle_average_block.argtypes = [C.c_void_p, dp]
+        L.thcm_oracle_scal.argtypes = [dp, dp, dp]
+        L.thcm_oracle_recompute_scaling.argtypes = [C.c_void_p, dp, dp]
         L.thcm_oracle_spmv.argtypes = [C.c_int, ip, ip, dp, dp, dp]
         L.thcm_oracle_gmres.argtypes = [C.c_int, ip, ip, dp, dp, dp, C.c_int, C.c_int, C.c_double, C.c_int, dp, dp, ip]
         L.thcm_oracle_gmres.restype = C.c_int
@@ -169,6 +172,17 @@ class Oracle:
         lib().thcm_oracle_frc(self.h, _dp(f))
         return f
 
+    def average_block(self):
+        """m_scaling::average_block on the Fortran CSR of the last jac()/fortran_matrix() call: db[ii, jj]"""
+        db = np.zeros(36)
+        lib().thcm_oracle_average_block(self.h, _dp(db))
+        return db.reshape(6, 6).T.copy()
+
+    def recompute_scaling(self):
+        """THCM::RecomputeScaling: (rowScaling, colScaling) or None if the averaged block is singular"""
+        r, c = np.zeros(self.ndim), np.zeros(self.ndim)
+        return (r, c) if lib().thcm_oracle_recompute_scaling(self.h, _dp(r), _dp(c)) else None
+
     def rowintcon(self):
         return lib().thcm_oracle_rowintcon(self.h)
 
@@ -176,6 +190,13 @@ class Oracle:
         c = np.zeros(self.ndim)
         lib().thcm_oracle_intcond_coeff(self.h, _dp(c))
         return c
+
+
+def scal(db):
+    """m_scaling::scal on a 6x6 array db[ii, jj]: (dr, dc) or None if singular"""
+    a = np.ascontiguousarray(np.asarray(db, np.float64).T).ravel()  # column-major like the Fortran array
+    dr, dc = np.zeros(6), np.zeros(6)
+    return (dr, dc) if lib().thcm_oracle_scal(_dp(a), _dp(dr), _dp(dc)) else None
 
 
 def spmv(rowptr, col, val, x):

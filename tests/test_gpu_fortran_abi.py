@@ -47,6 +47,13 @@ def test_fortran_symbols_match_oracle(name):
         val, ind = T.intcond_scaling()
         c = O.intcond_coeff()
         assert np.array_equal(c[ind - 1], val) and np.count_nonzero(c) == val.size
+        # m_scaling::average_block / compute as THCM::RecomputeScaling drives them (THCM.C:1707-1745)
+        db_o, ref = O.average_block(), O.recompute_scaling()
+        if ref is not None:
+            db_t, r_t, c_t = T.recompute_scaling()
+            assert np.abs(db_o - db_t).max() <= 1e-6 * np.abs(db_o).max()
+            np.testing.assert_allclose(r_t, ref[0], rtol=1e-6)
+            np.testing.assert_allclose(c_t, ref[1], rtol=1e-6)
     finally:
         T.close()
 
