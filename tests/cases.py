@@ -47,6 +47,21 @@ def case(name):
     raise KeyError(name)
 
 
+def reference_state():
+    """The reference's own golden state (tests/golden/ocean_reference.npz, from test/ocean/ocean_reference.h5): the end of
+    the continuation of src/tests/reft_ocean.C on the 16^3 periodic gateway box (test/ocean/reft_ocean_params.xml).
+    Returns (config, mask, {parameter index: value}, state).  "Mixing" = 2 there: convective adjustment switched on as
+    soon as T and S are non-zero (vmix_control, mix_imp.f:131-166), which is Mixing = 1 at this state."""
+    import os
+    from iemic_b200.capi import PAR_NAMES
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ocean_reference.npz"))
+    cfg = grids.default_config(16, 16, 16, xmin=300.0, xmax=340.0, ymin=20.0, ymax=60.0, periodic=True, hdim=4000.0, qz=1.0,
+                               forcing_type=2, tres=1, sres=1, vmix=1)
+    idx = dict(PAR_NAMES, FPER=27)
+    pars = {idx[str(n)]: float(v) for n, v in zip(z["par_names"], z["par_values"])}
+    return cfg, z["mask"].astype(np.int32), pars, z["state"].astype(np.float64)
+
+
 def state(cfg, mask, seed=1, kind="random"):
     return grids.synthetic_state(cfg["n"], cfg["m"], cfg["l"], mask, seed=seed, kind=kind)
 

@@ -1,5 +1,9 @@
 """Generates tests/golden/masks.npz from the reference's land-mask data files (data/mkmask/*).
 
+Also turns the reference's own golden state test/ocean/ocean_reference.h5 (the end state of the continuation of
+src/tests/reft_ocean.C, written by the reference itself) into tests/golden/ocean_reference.npz: state vector,
+continuation parameters and the land mask stored with it (read with the minimal HDF5 reader h5min.py).
+
 Run in the build container (the reference tree is not present on the GPU box):
     python tests/golden/make_fixtures.py
 The masks are input DATA of the reference's own test / run configurations (test/ocean, test/matrix, run/coupled),
@@ -14,7 +18,7 @@ import numpy as np
 REF = "/root/reference/data/mkmask"
 OUT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "masks.npz")
 FILES = {"mask_global_96x38x12": (96, 38, 12), "mask_natl8": (8, 8, 4), "test6x6x4": (6, 6, 4), "test8x8x4": (8, 8, 4),
-         "mask_global_48x19x12": (48, 19, 12), "mask_natl16": (16, 16, 16)}
+         "mask_global_48x19x12": (48, 19, 12), "mask_natl16": (16, 16, 16), "mask_gateway": (16, 16, 16)}
 
 
 def read_mask(path, n, m, l):
@@ -29,7 +33,22 @@ def read_mask(path, n, m, l):
     return a
 
 
+def reference_state():
+    """test/ocean/ocean_reference.h5 -> ocean_reference.npz (State/Values, Parameters/*, MaskGlobal/Global)"""
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from h5min import H5File
+    src = "/root/reference/test/ocean/ocean_reference.h5"
+    t = H5File(src).tree()
+    names = sorted(k for k in t["Parameters"] if k != "Time")
+    out = os.path.join(os.path.dirname(OUT), "ocean_reference.npz")
+    np.savez_compressed(out, state=t["State"]["Values"].ravel(), par_names=np.array(names),
+                        par_values=np.array([float(t["Parameters"][k]) for k in names]),
+                        mask=t["MaskGlobal"]["Global"].reshape(18, 18, 18).astype(np.int8))
+    print("wrote", out, os.path.getsize(out), "bytes")
+
+
 def main():
+    reference_state()
     out = {}
     for name, (n, m, l) in FILES.items():
         path = os.path.join(REF, name)
