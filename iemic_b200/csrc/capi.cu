@@ -827,14 +827,19 @@ int gmres_b200_solve(thcm_b200_t* h, const double* d_b, double* d_x, int m, int 
           // from Pythagoras, and the normalisation rides on the second update.
           { const PeerRed pr = red(h); launch_multi_dot(g.V, ld, i + 1, w, n, h1, h->rb, st, pr); L();
           if (int rc = allreduce(h, h1, i + 1, pr)) return rc; }
-          launch_multi_axpy(g.V, ld, i + 1, h1, w, n, nullptr, h->rb, st); L();
+          // first update and second reduction share one pass over the basis while its tile fits in shared memory
+          static const bool fuse23_on = !(getenv("IEMIC_GMRES_FUSE23") && getenv("IEMIC_GMRES_FUSE23")[0] == '0');
+          const bool fuse23 = fuse23_on && i + 1 <= multi_axpy_dot_max_nv();
+          if (!fuse23) { launch_multi_axpy(g.V, ld, i + 1, h1, w, n, nullptr, h->rb, st); L(); }
           { const PeerRed pr = red(h);
             // the Arnoldi bookkeeping rides in the finishing block of this reduction unless NCCL still has to sum h2
             const bool fuse_gv = !h->dist || pr.nranks > 0;
             GivensArgs gf;
             gf.H = g.H; gf.ldh = m + 1; gf.cs = g.cs; gf.sn = g.sn; gf.s = g.s; gf.h1 = h1; gf.h2 = h2; gf.nrm2 = nrm2; gf.sq = 1; gf.pyth = 1;
             gf.bnorm = bnorm; gf.hist = g.hist; gf.hnext = hnext; gf.j = i;
-            launch_multi_dot(g.V, ld, i + 2, w, n, h2, h->rb, st, pr, fuse_gv ? &gf : nullptr); L();
+            if (fuse23) launch_multi_axpy_dot(g.V, ld, i + 1, h1, w, n, h2, h->rb, st, pr, fuse_gv ? &gf : nullptr);
+            else launch_multi_dot(g.V, ld, i + 2, w, n, h2, h->rb, st, pr, fuse_gv ? &gf : nullptr);
+            L();
             givens_done = fuse_gv;
           if (int rc = allreduce(h, h2, i + 2, pr)) return rc; }
         } else if (ortho == GMRES_B200_CGS2) {

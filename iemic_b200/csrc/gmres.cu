@@ -13,6 +13,8 @@
 // block to arrive (atomic ticket) adds the partials in block order.  All loads are 16-byte vectorised; basis
 // vectors are streamed with evict-first hints, w stays cacheable.
 // HBM traffic per call: multi_dot (nv + ceil(nv/8)) * 8n, multi_axpy (nv + 2) * 8n, axpy_dot 4 * 8n.
+#include <algorithm>
+#include <cstdlib>
 #include "kernels.h"
 
 namespace thcm {
@@ -62,7 +64,7 @@ __device__ __forceinline__ bool last_block(unsigned int* ticket) {
 // out[k] = sum over blocks of partial[b*stride + k], fixed order; one warp per k
 __device__ __forceinline__ void final_sum(const double* partial, int stride, int nv, double* out) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  for (int k = warp; k < nv; k += RT / 32) {
+  for (int k = warp; k < nv; k += (int)(blockDim.x >> 5)) {
     double s = 0.0;
     for (int b = lane; b < (int)gridDim.x; b += 32) s += __ldcg(partial + (size_t)b * stride + k);
     s = warp_sum(s);
@@ -135,6 +137,79 @@ __global__ void __launch_bounds__(RT) multi_axpy_kernel(const double* __restrict
     if (last_block(ticket)) {
       final_sum(partial, MAXV, 1, nrm2_out);
       if (pr.nranks) peer_allreduce_block(pr, nrm2_out, 1);
+    }
+  }
+}
+
+// Fused second and third pass of a CGS2 step: w <- w - sum_k h[k] V_k and, from the SAME pass over the basis,
+// out[k] = <V_k, w_new> (k < nv) and out[nv] = <w_new, w_new>.  A block keeps its 256-row tile of the basis in shared memory
+// ((nv+1) x 256 doubles, row nv = the updated w) between the update and the dots, so the basis is read from HBM once
+// instead of twice: (nv + 2) * 8n bytes for both passes.  Warp q owns the dots k = q, q+8, ...; fixed summation order.
+constexpr int FUSE_MAXNV = 55;                 // largest basis the fused kernel takes ((nv+1) * FT * 8 B of shared memory per buffer)
+// FT = rows per tile = threads per block, NB = shared-memory tiles (2: a warp may load the next tile while others still
+// reduce the current one, one barrier per tile instead of two), MINB = resident blocks per SM the registers are capped for
+// FK = loads in flight per thread in the update phase
+template <int FT, int NB, int MINB, int FK>
+__global__ void __launch_bounds__(FT, MINB) multi_axpy_dot_kernel(const double* __restrict__ V, long long ldv, int nv, const double* __restrict__ h,
+                                                                  double* __restrict__ w, long long n, double* out, double* partial,
+                                                                  unsigned int* ticket, const PeerRed pr, const GivensArgs gv) {
+  constexpr int NW = FT / 32;
+  constexpr int KPW = (FUSE_MAXNV + 1 + NW - 1) / NW;
+  extern __shared__ double tile_all[];
+  __shared__ double hs[FUSE_MAXNV + 1];
+  for (int k = threadIdx.x; k < nv; k += FT) hs[k] = h[k];
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  double acc[KPW];
+#pragma unroll
+  for (int q = 0; q < KPW; q++) acc[q] = 0.0;
+  int buf = 0;
+  for (long long t0 = (long long)blockIdx.x * FT; t0 < n; t0 += (long long)gridDim.x * FT) {
+    double* tile = tile_all + (size_t)buf * (nv + 1) * FT;
+    double* wrow = tile + (size_t)nv * FT;
+    const long long i = t0 + threadIdx.x;
+    const bool in = i < n;
+    double wv = in ? w[i] : 0.0;
+    for (int k0 = 0; k0 < nv; k0 += FK) {
+      double v[FK];
+#pragma unroll
+      for (int k = 0; k < FK; k++) v[k] = (in && k0 + k < nv) ? __ldcs(V + (size_t)(k0 + k) * ldv + i) : 0.0;
+#pragma unroll
+      for (int k = 0; k < FK; k++)
+        if (k0 + k < nv) { tile[(size_t)(k0 + k) * FT + threadIdx.x] = v[k]; wv = fma(-hs[k0 + k], v[k], wv); }
+    }
+    if (in) w[i] = wv;
+    wrow[threadIdx.x] = wv;
+    __syncthreads();
+    double wr[NW];
+#pragma unroll
+    for (int q = 0; q < NW; q++) wr[q] = wrow[lane + 32 * q];
+#pragma unroll
+    for (int q = 0; q < KPW; q++) {
+      const int k = warp + q * NW;
+      if (k <= nv) {
+        const double* row = tile + (size_t)k * FT + lane;
+        double sacc = acc[q];
+#pragma unroll
+        for (int r = 0; r < NW; r++) sacc = fma(row[32 * r], wr[r], sacc);
+        acc[q] = sacc;
+      }
+    }
+    if (NB == 1) __syncthreads(); else buf ^= 1;
+  }
+  // block partials (RT/32 slots are not needed here: one value per dot and block)
+#pragma unroll
+  for (int q = 0; q < KPW; q++) {
+    const int k = warp + q * NW;
+    const double sacc = warp_sum(acc[q]);
+    if (k <= nv && lane == 0) partial[(size_t)blockIdx.x * MAXV + k] = sacc;
+  }
+  if (last_block(ticket)) {
+    final_sum(partial, MAXV, nv + 1, out);
+    if (pr.nranks) peer_allreduce_block(pr, out, nv + 1);
+    if (gv.H) {
+      __syncthreads();
+      if (threadIdx.x == 0) givens_step(gv);
     }
   }
 }
@@ -311,6 +386,33 @@ void launch_multi_dot(const double* V, long long ldv, int nv, const double* w, l
 void launch_multi_axpy(const double* V, long long ldv, int nv, const double* h, double* w, long long n, double* nrm2_out, RedBuf rb, cudaStream_t st,
                        const double* inv_scale, const PeerRed& pr) {
   multi_axpy_kernel<<<grid_for(n), RT, 0, st>>>(V, ldv, nv, h, w, n, nrm2_out, rb.partial, rb.ticket, inv_scale, pr);
+}
+int multi_axpy_dot_max_nv() { return FUSE_MAXNV; }
+template <int FT, int NB, int MINB, int FK = 16>
+static void launch_mad(const double* V, long long ldv, int nv, const double* h, double* w, long long n, double* out, RedBuf rb, cudaStream_t st,
+                       const PeerRed& pr, const GivensArgs& g) {
+  const int smem = NB * (nv + 1) * FT * (int)sizeof(double);
+  static bool attr = false;
+  if (!attr) { cudaFuncSetAttribute(multi_axpy_dot_kernel<FT, NB, MINB, FK>, cudaFuncAttributeMaxDynamicSharedMemorySize, NB * (FUSE_MAXNV + 1) * FT * (int)sizeof(double)); attr = true; }
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  const int per_sm = std::max(1, std::min(MINB, (220 * 1024) / (smem + 1024)));
+  const long long need = (n + FT - 1) / FT, cap = std::min<long long>((long long)sms * per_sm, rb.nblk_max);
+  multi_axpy_dot_kernel<FT, NB, MINB, FK><<<(int)(need < cap ? need : cap), FT, smem, st>>>(V, ldv, nv, h, w, n, out, rb.partial, rb.ticket, pr, g);
+}
+void launch_multi_axpy_dot(const double* V, long long ldv, int nv, const double* h, double* w, long long n, double* out, RedBuf rb, cudaStream_t st,
+                           const PeerRed& pr, const GivensArgs* gv) {
+  GivensArgs g;
+  if (gv) g = *gv; else g.H = nullptr;
+  // measured on B200 at 1 degree, GMRES(30) cycle: tiles of 160 rows, 5 blocks per SM: orthogonalisation 0.807 ms per step
+  // (128 rows x 6 blocks: 0.829; 256 x 3: 0.869; two shared-memory tiles per block: no gain; 32 loads in flight: spills)
+  static const int variant = getenv("IEMIC_GMRES_FUSE_VARIANT") ? atoi(getenv("IEMIC_GMRES_FUSE_VARIANT")) : 0;
+  switch (variant) {
+    case 1: launch_mad<128, 1, 6>(V, ldv, nv, h, w, n, out, rb, st, pr, g); break;
+    case 2: launch_mad<256, 1, 3>(V, ldv, nv, h, w, n, out, rb, st, pr, g); break;
+    default: launch_mad<160, 1, 5>(V, ldv, nv, h, w, n, out, rb, st, pr, g); break;
+  }
 }
 void launch_axpy_dot(const double* hprev, const double* vprev, const double* vnext, double* w, long long n, double* out, RedBuf rb, cudaStream_t st, const PeerRed& pr) {
   axpy_dot_kernel<<<grid_for(n), RT, 0, st>>>(hprev, vprev, vnext, w, n, out, rb.partial, rb.ticket, pr);

@@ -101,6 +101,11 @@ void launch_multi_dot(const double* V, long long ldv, int nv, const double* w, l
 void launch_multi_axpy(const double* V, long long ldv, int nv, const double* h, double* w, long long n,
                        double* nrm2_out, RedBuf rb, cudaStream_t st, const double* inv_scale = nullptr /* w /= *inv_scale afterwards */,
                        const PeerRed& pr = PeerRed{});
+// Fused CGS2 passes 2+3: w -= sum_k h[k] V_k, then out[k] = <V_k, w> (k < nv), out[nv] = <w, w> from the same read of the basis
+// (nv <= multi_axpy_dot_max_nv()); finishing block as in launch_multi_dot.
+int multi_axpy_dot_max_nv();
+void launch_multi_axpy_dot(const double* V, long long ldv, int nv, const double* h, double* w, long long n, double* out, RedBuf rb, cudaStream_t st,
+                           const PeerRed& pr = PeerRed{}, const GivensArgs* fused_givens = nullptr);
 // MGS fused step: if (hprev) w -= hprev[0]*vprev ; out = <w, vnext> (vnext may be null: then out = <w,w>)
 void launch_axpy_dot(const double* hprev, const double* vprev, const double* vnext, double* w, long long n, double* out, RedBuf rb, cudaStream_t st,
                      const PeerRed& pr = PeerRed{});

@@ -25,6 +25,17 @@ for _ in range(reps):
     G.computeRHS(x, F)
     G.applyMatrix(x, y)
 G.sync()
+# row N3: scaling and the point-block-Jacobi builder on the current Jacobian
+binv = torch.empty(G.nrows * 6, dtype=torch.float64, device="cuda")
+rs = torch.empty(G.nrows, dtype=torch.float64, device="cuda")
+ri = torch.empty_like(rs)
+G.block_jacobi(binv)
+G.recompute_scaling(rs, None)
+G.reciprocal(rs, ri)
+G.left_scale(rs)
+G.left_scale(ri)
+G.computeJacobian(x)
+del binv, rs, ri
 b = y.clone()
 xs = torch.zeros_like(x)
 G.solve(b, xs, m=8, maxit=7, tol=0.0, ortho=ib.CGS2F, check_every=0)
