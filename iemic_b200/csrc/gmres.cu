@@ -169,16 +169,28 @@ __global__ void __launch_bounds__(FT, MINB) multi_axpy_dot_kernel(const double* 
     double* wrow = tile + (size_t)nv * FT;
     const long long i = t0 + threadIdx.x;
     const bool in = i < n;
-    double wv = in ? w[i] : 0.0;
-    for (int k0 = 0; k0 < nv; k0 += FK) {
+    const long long ic = in ? i : n - 1;      // rows past the end read a valid address and are weighted with w = 0 below
+    double wv = w[ic];
+    const double* vp = V + ic;
+    double* tp = tile + threadIdx.x;
+    int k0 = 0;
+    for (; k0 + FK <= nv; k0 += FK) {         // full chunks: no predicates, FK loads in flight
       double v[FK];
 #pragma unroll
-      for (int k = 0; k < FK; k++) v[k] = (in && k0 + k < nv) ? __ldcs(V + (size_t)(k0 + k) * ldv + i) : 0.0;
+      for (int k = 0; k < FK; k++) v[k] = __ldcs(vp + (size_t)k * ldv);
 #pragma unroll
-      for (int k = 0; k < FK; k++)
-        if (k0 + k < nv) { tile[(size_t)(k0 + k) * FT + threadIdx.x] = v[k]; wv = fma(-hs[k0 + k], v[k], wv); }
+      for (int k = 0; k < FK; k++) { tp[k * FT] = v[k]; wv = fma(-hs[k0 + k], v[k], wv); }
+      vp += (size_t)FK * ldv; tp += FK * FT;
     }
-    if (in) w[i] = wv;
+    if (k0 < nv) {
+      const int rem = nv - k0;
+      double v[FK - 1];
+#pragma unroll
+      for (int k = 0; k < FK - 1; k++) if (k < rem) v[k] = __ldcs(vp + (size_t)k * ldv);
+#pragma unroll
+      for (int k = 0; k < FK - 1; k++) if (k < rem) { tp[k * FT] = v[k]; wv = fma(-hs[k0 + k], v[k], wv); }
+    }
+    if (in) w[i] = wv; else wv = 0.0;
     wrow[threadIdx.x] = wv;
     __syncthreads();
     double wr[NW];
@@ -187,13 +199,12 @@ __global__ void __launch_bounds__(FT, MINB) multi_axpy_dot_kernel(const double* 
 #pragma unroll
     for (int q = 0; q < KPW; q++) {
       const int k = warp + q * NW;
-      if (k <= nv) {
-        const double* row = tile + (size_t)k * FT + lane;
-        double sacc = acc[q];
+      if (k > nv) break;
+      const double* row = tile + (size_t)k * FT + lane;
+      double sacc = acc[q];
 #pragma unroll
-        for (int r = 0; r < NW; r++) sacc = fma(row[32 * r], wr[r], sacc);
-        acc[q] = sacc;
-      }
+      for (int r = 0; r < NW; r++) sacc = fma(row[32 * r], wr[r], sacc);
+      acc[q] = sacc;
     }
     if (NB == 1) __syncthreads(); else buf ^= 1;
   }
@@ -388,7 +399,7 @@ void launch_multi_axpy(const double* V, long long ldv, int nv, const double* h, 
   multi_axpy_kernel<<<grid_for(n), RT, 0, st>>>(V, ldv, nv, h, w, n, nrm2_out, rb.partial, rb.ticket, inv_scale, pr);
 }
 int multi_axpy_dot_max_nv() { return FUSE_MAXNV; }
-template <int FT, int NB, int MINB, int FK = 16>
+template <int FT, int NB, int MINB, int FK = 8>
 static void launch_mad(const double* V, long long ldv, int nv, const double* h, double* w, long long n, double* out, RedBuf rb, cudaStream_t st,
                        const PeerRed& pr, const GivensArgs& g) {
   const int smem = NB * (nv + 1) * FT * (int)sizeof(double);
@@ -405,13 +416,13 @@ void launch_multi_axpy_dot(const double* V, long long ldv, int nv, const double*
                            const PeerRed& pr, const GivensArgs* gv) {
   GivensArgs g;
   if (gv) g = *gv; else g.H = nullptr;
-  // measured on B200 at 1 degree, GMRES(30) cycle: tiles of 160 rows, 5 blocks per SM: orthogonalisation 0.807 ms per step
-  // (128 rows x 6 blocks: 0.829; 256 x 3: 0.869; two shared-memory tiles per block: no gain; 32 loads in flight: spills)
+  // measured on B200 at 1 degree, GMRES(30) cycle, orthogonalisation per step: tiles of 256 rows x 3 blocks per SM 0.786 ms,
+  // 128 x 6: 0.800, 160 x 5: 0.809, 16 instead of 8 loads in flight: 0.871 (registers), two shared-memory tiles per block: no gain
   static const int variant = getenv("IEMIC_GMRES_FUSE_VARIANT") ? atoi(getenv("IEMIC_GMRES_FUSE_VARIANT")) : 0;
   switch (variant) {
-    case 1: launch_mad<128, 1, 6>(V, ldv, nv, h, w, n, out, rb, st, pr, g); break;
-    case 2: launch_mad<256, 1, 3>(V, ldv, nv, h, w, n, out, rb, st, pr, g); break;
-    default: launch_mad<160, 1, 5>(V, ldv, nv, h, w, n, out, rb, st, pr, g); break;
+    case 1: launch_mad<128, 1, 6, 8>(V, ldv, nv, h, w, n, out, rb, st, pr, g); break;
+    case 2: launch_mad<160, 1, 5, 8>(V, ldv, nv, h, w, n, out, rb, st, pr, g); break;
+    default: launch_mad<256, 1, 3, 8>(V, ldv, nv, h, w, n, out, rb, st, pr, g); break;
   }
 }
 void launch_axpy_dot(const double* hprev, const double* vprev, const double* vnext, double* w, long long n, double* out, RedBuf rb, cudaStream_t st, const PeerRed& pr) {
