@@ -1,0 +1,48 @@
+"""Loading what the reference writes: HDF5 checkpoints of Model::saveStateToFile
+(src/utils/Model.H:149-232: groups "State", "Parameters", and for the ocean "MaskGlobal" etc., written through
+EpetraExt::HDF5) and the plain-text land-mask files of data/mkmask (readmask, src/ocean/topo.F90:41-75).
+
+Read-only: a state computed by a reference run can be loaded into the B200 path (Ocean.setPar / device vectors);
+writing the format back is not implemented."""
+import numpy as np
+
+from .capi import PAR_NAMES
+from .h5min import H5File
+
+# names Model.H stores that THCM::par2int does not know under that spelling
+_ALIASES = {"FPER": 27, "SPER": 28}
+
+
+def load_state(path):
+    """-> dict(state=float64[N], parameters={name: value}, par_index={THCM index: value}, mask=int32[(l+2),(m+2),(n+2)] or None)
+
+    Model::loadStateFromFile (src/utils/Model.H:236-310) reads "State"/"Values" and every entry of "Parameters";
+    Ocean additionally stores the global land mask ("MaskGlobal"/"Global", (n+2)(m+2)(l+2) ints, i fastest)."""
+    t = H5File(path).tree()
+    if "State" not in t or "Values" not in t["State"]:
+        raise ValueError("%s: no State/Values dataset" % path)
+    state = np.ascontiguousarray(t["State"]["Values"], np.float64).ravel()
+    pars = {k: float(np.asarray(v).ravel()[0]) for k, v in t.get("Parameters", {}).items()}
+    idx = dict(PAR_NAMES, **_ALIASES)
+    par_index = {idx[k]: v for k, v in pars.items() if k in idx}
+    mask = None
+    if "MaskGlobal" in t and "Global" in t["MaskGlobal"]:
+        mask = np.ascontiguousarray(t["MaskGlobal"]["Global"], np.int32).ravel()
+    return dict(state=state, parameters=pars, par_index=par_index, mask=mask)
+
+
+def read_mask(path, n, m, l):
+    """readmask (src/ocean/topo.F90:41-75): per level one header line, then rows j = m+1 .. 0 of n+2 digits.
+    Returns int32[(l+2), (m+2), (n+2)] (k, j, i), the layout thcm_b200_create takes."""
+    lines = open(path).read().split("\n")
+    a = np.ones((l + 2, m + 2, n + 2), np.int32)
+    p = 0
+    for k in range(l + 2):
+        p += 1
+        for j in range(m + 1, -1, -1):
+            row = lines[p][:n + 2]
+            if len(row) != n + 2:
+                raise ValueError("%s: level %d row %d has %d columns, expected %d" % (path, k, j, len(row), n + 2))
+            a[k, j, :] = [int(ch) for ch in row]
+            p += 1
+    return a

@@ -67,7 +67,7 @@ struct TileRaw { // accessor concept X: raw neighbour state
 // Copy the compacted rows of 32 cells from the warp scratch (lane-major, STRIDE apart) to the CSR value array.
 // Consecutive lanes write consecutive doubles wherever consecutive rows are contiguous in the CSR.
 template <int NE>
-__device__ __forceinline__ void warp_copy_out(double* __restrict__ val, const double* scr, int base, int len, int lane) {
+__device__ __noinline__ void warp_copy_out(double* __restrict__ val, const double* scr, int base, int len, int lane) { // rare: kept out of the hot path's instruction footprint
 #pragma unroll
   for (int it = 0; it < NE; it++) {
     const int t = it * 32 + lane;
@@ -114,7 +114,7 @@ __device__ __forceinline__ void warp_copy_out_full(double* __restrict__ val, con
 
 // Same idea with run-time strides, for lines whose cells all have the SAME (clipped) row lengths: domain edges in j and
 // k, partially filled last tile in i.  `cs` = values per cell, `off`/`len` = this row's offset and length inside a cell.
-__device__ __forceinline__ void warp_copy_out_uniform(double* __restrict__ val, const double* scr, int lane, int nact, int cs, int off, int len) {
+__device__ __noinline__ void warp_copy_out_uniform(double* __restrict__ val, const double* scr, int lane, int nact, int cs, int off, int len) {
   if (lane < len) {
     const double* src = scr + lane;
     double* dst = val + off + lane;
@@ -217,14 +217,30 @@ __global__ void __launch_bounds__(NTHREADS, JAC_MINB) jac_kernel(const __grid_co
   const size_t cidx = active ? cell_index(S, i, j, k) : 0;
   Cell c; c.i = i; c.j = j; c.k = k; c.sig = active ? __ldg(a.sig + cidx) : 0ull;
   const int row0 = (int)(6 * cidx);
+  // Row offsets: a line whose 32 cells all carry complete rows (almost all lines) needs only the first offset of every cell --
+  // the cells are 104 values apart and the rows of a cell follow from the compile-time row lengths -- so one load per lane
+  // (plus the end of the last cell) replaces seven.  Anything else loads the remaining offsets after the tile is staged.
   int rp[7];
-#pragma unroll
-  for (int q = 0; q < 7; q++) rp[q] = active ? __ldg(a.rowptr + row0 + q) : 0;
+  rp[0] = active ? __ldg(a.rowptr + row0) : 0;
+  rp[6] = (active && lane == 31) ? __ldg(a.rowptr + row0 + 6) : 0;
 
   if (tile_is_plain(S, gi0, gj0, gk0)) stage_tile_plain<false>(a, sm, gi0, gj0, gk0);
   else stage_tile<false>(a, sm, gi0, gj0, gk0);
   __syncthreads();
   if (!line) return;
+  {
+    const int nxt = __shfl_down_sync(FULL, rp[0], 1);
+    if (lane < 31) rp[6] = nxt;                 // rows are contiguous: the next cell starts where this one ends
+    const bool special = a.sp.rowintcon >= row0 && a.sp.rowintcon < row0 + 6;
+    const bool full = __all_sync(FULL, active && rp[6] - rp[0] == CELL_NNZ && !special);
+    if (full) {
+      rp[1] = rp[0] + row_offset<VV>(); rp[2] = rp[0] + row_offset<WW>(); rp[3] = rp[0] + row_offset<PP>();
+      rp[4] = rp[0] + row_offset<TT>(); rp[5] = rp[0] + row_offset<SS>();
+    } else {
+#pragma unroll
+      for (int q = 1; q < 7; q++) rp[q] = active ? __ldg(a.rowptr + row0 + q) : 0;
+    }
+  }
   TileFields f; f.pu = sm; f.pv = sm + TCELLS; f.pw = sm + 2 * TCELLS; f.pt = sm + 3 * TCELLS; f.ps = sm + 4 * TCELLS;
   f.base = (lane + 1) + (lj + 1) * SX + (lk + 1) * SX * SY;
   double* scr = sm + 5 * TCELLS + warp * 32 * STRIDE;

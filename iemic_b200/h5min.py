@@ -1,7 +1,8 @@
 """Minimal reader for the HDF5 files EpetraExt::HDF5 writes (the reference's checkpoint format, src/utils/Model.H:149-310):
 superblock version 0, symbol-table groups (version-1 B-trees + local heaps), version-1 object headers, contiguous or
-compact datasets of little-endian doubles / 32-bit ints / fixed strings.  No h5py in this image; only used by
-make_fixtures.py to turn the reference's own golden state (test/ocean/ocean_reference.h5) into an .npz fixture."""
+compact datasets of little-endian doubles / 32-bit ints / fixed strings.  Pure Python + numpy (no h5py in this image).
+Used by iemic_b200.checkpoint (loading states the reference wrote) and by
+tests/golden/make_fixtures.py to turn the reference's own golden state (test/ocean/ocean_reference.h5) into a fixture."""
 import struct
 
 import numpy as np

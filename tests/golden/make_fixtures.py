@@ -2,7 +2,7 @@
 
 Also turns the reference's own golden state test/ocean/ocean_reference.h5 (the end state of the continuation of
 src/tests/reft_ocean.C, written by the reference itself) into tests/golden/ocean_reference.npz: state vector,
-continuation parameters and the land mask stored with it (read with the minimal HDF5 reader h5min.py).
+continuation parameters and the land mask stored with it (read with the minimal HDF5 reader iemic_b200/h5min.py).
 
 Run in the build container (the reference tree is not present on the GPU box):
     python tests/golden/make_fixtures.py
@@ -35,8 +35,8 @@ def read_mask(path, n, m, l):
 
 def reference_state():
     """test/ocean/ocean_reference.h5 -> ocean_reference.npz (State/Values, Parameters/*, MaskGlobal/Global)"""
-    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
-    from h5min import H5File
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
+    from iemic_b200.h5min import H5File
     src = "/root/reference/test/ocean/ocean_reference.h5"
     t = H5File(src).tree()
     names = sorted(k for k in t["Parameters"] if k != "Time")
