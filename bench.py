@@ -170,7 +170,8 @@ def run_reference(args):
     sample = "each step: %d host threads x one 48x19x12-cell block (oracle port, Jacobian+RHS), extrapolated by cell count to %s" % (threads, args.grid)
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1000.0 / v, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": "synthetic global 1-degree ocean %s (BASELINE config 4), Jacobian+RHS assembly" % args.grid},
+            "config": {"workload": "synthetic global 1-degree ocean %s (BASELINE config 4): Jacobian+RHS assembly per step" % args.grid,
+                       "grid": args.grid, "unknowns": 6 * ncell, "mask": args.mask},
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0, "wall_s": time.perf_counter() - t0}
