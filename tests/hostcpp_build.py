@@ -1,0 +1,24 @@
+"""Builds tests/continuation_dropin.cpp: the reference's UNMODIFIED Continuation<Model> (read in place from the reference
+tree, never copied) instantiated on the B200 host mirror.  The reference tree only exists in the build container, so the
+binary goes to tests/_build/ (git-ignored, shipped to the GPU box with the snapshot) and the GPU test only runs it."""
+import os
+import subprocess
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF_CONT = "/root/reference/src/continuation"
+EXE = os.path.join(ROOT, "tests", "_build", "continuation_dropin")
+
+
+def build_continuation_dropin():
+    """-> path of the binary, or None when the reference tree is absent"""
+    if not os.path.isdir(REF_CONT):
+        return EXE if os.path.exists(EXE) else None
+    os.makedirs(os.path.dirname(EXE), exist_ok=True)
+    host = os.path.join(ROOT, "iemic_b200", "host")
+    cmd = ["g++", "-std=c++17", "-O1", "-Wall", "-I", os.path.join(ROOT, "tests", "compat"), "-I", REF_CONT,
+           "-I", os.path.join(ROOT, "include"), "-I", host, os.path.join(ROOT, "tests", "continuation_dropin.cpp"),
+           "-L", os.path.join(ROOT, "iemic_b200", "lib"), "-liemic_b200", "-Wl,-rpath,$ORIGIN/../../iemic_b200/lib", "-o", EXE]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("continuation_dropin.cpp does not compile against the reference's Continuation.H:\n" + r.stderr[-4000:])
+    return EXE

@@ -24,6 +24,33 @@ def test_reference_gmressolver_instantiates_on_the_mirror():
     assert r.returncode == 0, r.stderr[-3000:]
 
 
+@pytest.mark.skipif(not os.path.isdir("/root/reference/src/continuation"), reason="reference tree not present (GPU box)")
+def test_reference_continuation_instantiates_on_the_mirror():
+    """Drop-in claim for the continuation driver, compiled and linked: the reference's UNMODIFIED Continuation<Model>
+    (src/continuation/Continuation.H, 1380 lines: Euler predictor, bordered Newton corrector, computeDFDPar, secant
+    destination detection, step control) with Model = std::shared_ptr<OceanB200>.  Teuchos / Utils / JDQZ come from the
+    test-only stand-ins in tests/compat."""
+    import hostcpp_build
+    exe = hostcpp_build.build_continuation_dropin()
+    assert exe and os.path.exists(exe)
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=120)   # no GPU here: must fail loudly, not fall back
+    assert r.returncode != 0 and "no CUDA device" in r.stdout
+
+
+@pytest.mark.gpu
+def test_reference_continuation_runs_on_gpu():
+    """First leg of the reference's integration test src/tests/intt_2dmoc.C:28-40 (3x6x6 2-D MOC box, continuation in
+    "Combined Forcing" 0 -> 1 with test/2dmoc/continuation_params.xml), driven by the reference's own Continuation.H on the
+    CUDA path; linear solves = restarted GMRES on the device with the device-built point-block Jacobi."""
+    import hostcpp_build
+    exe = hostcpp_build.build_continuation_dropin()
+    if not exe or not os.path.exists(exe):
+        pytest.skip("tests/_build/continuation_dropin was not built (needs the reference tree at build time)")
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "continuation status 0" in r.stdout and "continuation drop-in ok" in r.stdout
+
+
 @pytest.mark.gpu
 def test_host_mirror_runs_on_gpu(tmp_path):
     exe = str(tmp_path / "selftest")
