@@ -13,6 +13,7 @@
 #include "../../include/iemic_b200.h"
 #include "thcm_host.h"
 #include "kernels.h"
+#include "gmres_guard.h"
 #include "dist.h"
 
 using namespace thcm;
@@ -804,6 +805,7 @@ int gmres_b200_solve(thcm_b200_t* h, const double* d_b, double* d_x, int m, int 
   if (resid <= tol) { if (iters_out) *iters_out = 0; return 0; }
 
   std::vector<double> hbuf(m + 2);
+  static const bool guard_on = !(getenv("IEMIC_GMRES_GUARD") && getenv("IEMIC_GMRES_GUARD")[0] == '0');
   while (iter <= maxit) {
     // beta = ||r|| ; V0 = r / beta ; s = beta e1   (nrm2 holds ||r||^2)
     launch_cycle_init(nrm2, g.s, m, beta, st); L();
@@ -879,15 +881,36 @@ int gmres_b200_solve(thcm_b200_t* h, const double* d_b, double* d_x, int m, int 
     for (int q = 0; q < done_in_cycle; q++) if (hist_out) hist_out[nh++] = hbuf[q];
     if (done_in_cycle > 0) resid = hbuf[done_in_cycle - 1];
     if (!conv && resid < tol) conv = true;
-    // Update: y = H^-1 s ; x += Z y   (GMRESSolver.H:292-313)
+    // Update: y = H^-1 s ; x += Z y   (GMRESSolver.H:292-313), built in the work vector first: the explicit residual
+    // (GMRESSolver.H:228-242) decides whether it is taken as it is
+    auto candidate = [&](int ncols) -> int {
+      CU(cudaMemcpyAsync(g.tmp, d_x, n * sizeof(double), cudaMemcpyDeviceToDevice, st));
+      launch_multi_axpy_plus(flex ? g.Z : g.V, ld, ncols, g.y, g.tmp, n, st); L();
+      if (int rc = spmv_impl(h, g.tmp, g.r)) return rc;
+      launch_residual(d_b, g.r, n, st); L();
+      { const PeerRed pr = red(h); launch_dot(g.r, g.r, n, nrm2, h->rb, st, pr); L();
+      if (int rc = allreduce(h, nrm2, 1, pr)) return rc; }
+      CU(cudaMemcpyAsync(&r2, nrm2, sizeof(double), cudaMemcpyDeviceToHost, st));
+      CU(cudaStreamSynchronize(st));
+      return 0;
+    };
     launch_backsolve(g.H, m + 1, g.s, space, g.y, st); L();
-    launch_multi_axpy_plus(flex ? g.Z : g.V, ld, space + 1, g.y, d_x, n, st); L();
-    // true residual
-    CU(cudaMemcpyAsync(g.tmp, d_x, n * sizeof(double), cudaMemcpyDeviceToDevice, st));
-    if (int rc = spmv_impl(h, g.tmp, g.r)) return rc;
-    launch_residual(d_b, g.r, n, st); L();
-    { const PeerRed pr = red(h); launch_dot(g.r, g.r, n, nrm2, h->rb, st, pr); L();
-    if (int rc = allreduce(h, nrm2, 1, pr)) return rc; }
+    if (int rc = candidate(space + 1)) return rc;
+    if (guard_on && ortho != GMRES_B200_MGS && done_in_cycle > 0 && gmres_lost_accuracy(resid, std::sqrt(r2) / normb, tol)) {
+      // the least-squares coefficients outgrew what double precision carries (singular Jacobian, b outside its range):
+      // keep the leading columns the estimate of gmres_guard.h still trusts, return that iterate and stop
+      std::vector<double> hH((size_t)(m + 1) * done_in_cycle), hs(m + 1), ytr;
+      CU(cudaMemcpyAsync(hH.data(), g.H, hH.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
+      CU(cudaMemcpyAsync(hs.data(), g.s, hs.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
+      CU(cudaStreamSynchronize(st));
+      const int keep = gmres_truncate(hH.data(), m + 1, hs.data(), hbuf.data(), done_in_cycle, normb, ytr);
+      CU(cudaMemcpyAsync(g.y, ytr.data(), keep * sizeof(double), cudaMemcpyHostToDevice, st));
+      if (int rc = candidate(keep)) return rc;
+      CU(cudaMemcpyAsync(d_x, g.tmp, n * sizeof(double), cudaMemcpyDeviceToDevice, st));
+      ret = 2;
+      break;
+    }
+    CU(cudaMemcpyAsync(d_x, g.tmp, n * sizeof(double), cudaMemcpyDeviceToDevice, st));
     if (conv) { ret = 0; break; }
   }
   CU(cudaMemcpyAsync(&r2, nrm2, sizeof(double), cudaMemcpyDeviceToHost, st));

@@ -161,7 +161,12 @@ int thcm_b200_block_jacobi(thcm_b200_t* h, double* d_blockinv, int* nsingular);
  * the normalisation is fused into the second update: 6 kernels and 2 allreduces per Arnoldi step).  prec: right (flexible) preconditioner; BLOCKJACOBI takes nrows_local/6
  * inverted 6x6 blocks, row-major, in d_blockinv.  hist[it] receives resid_ after inner iteration it
  * (length >= maxit+1).  check_every: 1 tests convergence every iteration like the reference; 0 never leaves the
- * device until the cycle ends (fixed iteration count).  Return value: 0 converged, 1 not converged (like solve()). */
+ * device until the cycle ends (fixed iteration count).  Return value: 0 converged, 1 not converged (like solve()),
+ * 2 accuracy limit: in the CGS2 modes the explicit residual at the end of a cycle (GMRESSolver.H:228-242) is compared
+ * with the recurrence residual the reference accepts on; when it is more than max(10 tol, 100 x recurrence, 1e-8) -- a singular
+ * Jacobian with a right-hand side at the rounding floor of F -- the update keeps only the leading Krylov columns whose
+ * estimated residual is still attainable (iemic_b200/csrc/gmres_guard.h), d_x holds that iterate and the solve stops.
+ * The MGS mode keeps the reference's behaviour to the letter.  IEMIC_GMRES_GUARD=0 in the environment switches it off. */
 int gmres_b200_solve(thcm_b200_t* h, const double* d_b, double* d_x, int m, int maxit, double tol,
                      int ortho, int prec, const double* d_blockinv, int check_every,
                      double* hist, int* iters);

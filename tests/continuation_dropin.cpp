@@ -6,11 +6,11 @@
 // that test (:28-120), writing the two end states whose overturning streamfunction the reference asserts (psi_max = 14.7 Sv,
 // mirror symmetry of the branches).  Teuchos / Utils / JDQZ are replaced by the test-only stand-ins of tests/compat (a box
 // with Trilinos would use the real ones).
-// Status on B200: the first leg runs to its destination (status 0, ||F|| = 7e-13, 4 s; every GMRES solve converges to 1e-10
-// in 160-320 iterations).  In "chain" mode the second leg (CMPR -> -0.2) arrives within 8.8e-6 of the destination and then
-// aborts at the minimum step size inside the reference's secant destination process (the secant tangent degenerates once
-// ds falls below the Newton tolerance 1e-3); the legs behind it are therefore not asserted by any test -- the known
-// answer psi_max = 14.7 Sv is reproduced through tests/moc2d.py instead (tests/test_known_answer_2dmoc.py).
+// Linear solves: GMRES(500) on the device, CGS2, device-built point-block Jacobi.  The Jacobian of this configuration is
+// singular (no fixed pressure points); the solves of Newton's last steps have right-hand sides at the rounding floor of F and
+// end at the accuracy guard of the driver (iemic_b200/csrc/gmres_guard.h, return code 2) -- without it the second leg aborts
+// at the minimum step size inside the secant destination process (tests/test_continuation_oracle.py shows the same on the
+// CPU walk-through of the driver).
 //
 // Build (the test does this): g++ -std=c++17 -Itests/compat -I<reference>/src/continuation -Iinclude -Iiemic_b200/host
 //                             tests/continuation_dropin.cpp -Liemic_b200/lib -liemic_b200

@@ -22,3 +22,21 @@ def build_continuation_dropin():
     if r.returncode != 0:
         raise RuntimeError("continuation_dropin.cpp does not compile against the reference's Continuation.H:\n" + r.stderr[-4000:])
     return EXE
+
+
+ORACLE_EXE = os.path.join(ROOT, "tests", "_build", "continuation_oracle")
+
+
+def build_continuation_oracle():
+    """tests/continuation_oracle.cpp: the same unmodified Continuation<Model> on the CPU oracle (test infrastructure).
+    -> path of the binary, or None when the reference tree is absent"""
+    if not os.path.isdir(REF_CONT):
+        return ORACLE_EXE if os.path.exists(ORACLE_EXE) else None
+    os.makedirs(os.path.dirname(ORACLE_EXE), exist_ok=True)
+    cmd = ["g++", "-std=c++17", "-O2", "-I", os.path.join(ROOT, "tests", "compat"), "-I", REF_CONT,
+           os.path.join(ROOT, "tests", "continuation_oracle.cpp"), "-L", os.path.join(ROOT, "oracle"), "-lthcm_oracle",
+           "-Wl,-rpath,$ORIGIN/../../oracle", "-o", ORACLE_EXE]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("continuation_oracle.cpp does not compile against the reference's Continuation.H:\n" + r.stderr[-4000:])
+    return ORACLE_EXE

@@ -1,0 +1,56 @@
+"""The reference's own integration test of this path, src/tests/intt_2dmoc.C:28-137, run by the reference's UNMODIFIED
+Continuation<Model> (src/continuation/Continuation.H, compiled in place) on the CPU oracle: seven pseudo-arclength legs on the
+3x6x6 2-D MOC box, then the assertions the reference makes on the overturning streamfunction of the two end states
+(psi_max = 14.7 +- 0.1 Sv, psi_min = 0 +- 1e-4, the second state the mirror image of the first within 1e-4).  This pins the
+oracle's F and J (invariant I6) through the reference's own driver rather than a solver of ours.
+
+Two linear solvers: a dense LU (exact up to the pressure null vector), and a host walk-through of the product's GMRES driver
+(CGS2 + the accuracy guard of iemic_b200/csrc/gmres_guard.h).  Without the guard the CGS2 driver fails the second leg: the
+Jacobian is singular here (no fixed pressure points), Newton's last right-hand sides sit at the rounding floor of F, and a
+solve accepted on the recurrence residual returns a multiple of the null vector (same failure seen on the GPU)."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import hostcpp_build
+import moc2d
+from iemic_b200 import grids
+
+
+def _exe():
+    exe = hostcpp_build.build_continuation_oracle()
+    if exe is None:
+        pytest.skip("reference tree absent and no prebuilt tests/_build/continuation_oracle")
+    return exe
+
+
+def _run(tmp_path, mode, nlegs, env=None, timeout=600):
+    e = dict(os.environ)
+    e.update(env or {})
+    r = subprocess.run([_exe(), str(tmp_path), mode, str(nlegs)], capture_output=True, text=True, env=e, timeout=timeout)
+    return r.returncode, r.stdout
+
+
+def test_intt_2dmoc_chain_with_the_reference_continuation(tmp_path):
+    rc, out = _run(tmp_path, "lu", 7)
+    assert rc == 0 and "continuation on the oracle ok" in out, out[-2000:]
+    cfg = grids.moc2d_config(moc2d.N_, moc2d.M_, moc2d.L_)
+    x1 = np.fromfile(tmp_path / "state1.bin")
+    x2 = np.fromfile(tmp_path / "state2.bin")
+    pmin1, pmax1 = moc2d.psim(cfg, x1)
+    pmin2, pmax2 = moc2d.psim(cfg, x2)
+    assert abs(pmax1 - 14.7) <= 1e-1   # intt_2dmoc.C:96
+    assert abs(pmin1) <= 1e-4          # :97
+    assert abs(pmin1 + pmax2) <= 1e-4  # :127
+    assert abs(pmax1 + pmin2) <= 1e-4  # :128
+
+
+def test_product_gmres_driver_needs_the_accuracy_guard(tmp_path):
+    rc, out = _run(tmp_path, "cgs2", 2)
+    assert rc == 0, out[-2000:]
+    legs = [ln for ln in out.splitlines() if ln.startswith("leg ")]
+    assert len(legs) == 2 and all("status 0" in ln for ln in legs), out[-2000:]
+    rc0, out0 = _run(tmp_path, "cgs2", 2, env={"ORACLE_GUARD": "0"})
+    assert rc0 != 0 and "leg CMPR -> -0.2: status 1" in out0, out0[-2000:]

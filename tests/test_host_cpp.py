@@ -52,6 +52,27 @@ def test_reference_continuation_runs_on_gpu():
 
 
 @pytest.mark.gpu
+def test_reference_intt_2dmoc_chain_on_gpu(tmp_path):
+    """All seven legs of src/tests/intt_2dmoc.C:28-120 by the reference's own Continuation.H on the CUDA path, then the
+    reference's assertions on the overturning streamfunction of the two end states (:96-97, :127-128)."""
+    import numpy as np
+    import hostcpp_build
+    import moc2d
+    from iemic_b200 import grids
+    exe = hostcpp_build.build_continuation_dropin()
+    if not exe or not os.path.exists(exe):
+        pytest.skip("tests/_build/continuation_dropin was not built (needs the reference tree at build time)")
+    r = subprocess.run([exe, "chain", str(tmp_path)], capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "continuation drop-in ok" in r.stdout
+    cfg = grids.moc2d_config(moc2d.N_, moc2d.M_, moc2d.L_)
+    pmin1, pmax1 = moc2d.psim(cfg, np.fromfile(tmp_path / "state1.bin"))
+    pmin2, pmax2 = moc2d.psim(cfg, np.fromfile(tmp_path / "state2.bin"))
+    assert abs(pmax1 - 14.7) <= 1e-1 and abs(pmin1) <= 1e-4
+    assert abs(pmin1 + pmax2) <= 1e-4 and abs(pmax1 + pmin2) <= 1e-4
+
+
+@pytest.mark.gpu
 def test_host_mirror_runs_on_gpu(tmp_path):
     exe = str(tmp_path / "selftest")
     libdir = os.path.join(ROOT, "iemic_b200", "lib")
