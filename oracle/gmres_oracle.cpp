@@ -6,7 +6,11 @@
 // Vector concept (GMRESSolverDecl.H:7-16): dot/norm are sequential sums, update(a,A,b) is
 // this = a*A + b*this.
 //
-// parity unpinned: no reference test exercises src/gmressolver.
+// PARITY: pinned against the reference's own code.  No reference test exercises src/gmressolver, but the
+// header compiles here by itself: tests/gmres_reference.cpp instantiates the UNMODIFIED GMRESSolver.H (in place, from the
+// reference tree) on plain host vectors and tests/test_gmres_reference_pin.py requires return code, iteration count, final
+// recurrence residual and solution of this restatement to equal the reference's bit for bit (with and without the point-block
+// preconditioner, one cycle and restarted, stopped by tolerance and by the iteration limit).
 #include "thcm_oracle.h"
 #include <cmath>
 #include <vector>

@@ -6,7 +6,10 @@
 // Compile WITHOUT fp contraction (-ffp-contract=off): the reference is built for baseline
 // x86-64 (src/CMakeLists.txt:24, no -march), i.e. without FMA.
 //
-// parity unpinned: the reference cannot be built here; pinned by invariants I1-I6.
+// PARITY: the Fortran cannot be built here (no Fortran compiler).  Pinned by the golden state the reference
+// wrote (test/ocean/ocean_reference.h5 is a root of this F: I7), by the known answer of the reference's integration test
+// intt_2dmoc (I6: reached both by a solver of ours and by the reference's own unmodified Continuation.H driving this oracle,
+// tests/continuation_oracle.cpp) and by the invariants I1-I5; details in thcm_oracle.h.
 #include "thcm_oracle.h"
 #include <cmath>
 #include <cstdio>

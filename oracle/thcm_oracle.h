@@ -12,13 +12,16 @@
  * 127-128 -- psi_max = 14.7 +- 0.1 Sv, psi_min = 0 +- 1e-4 and the mirror symmetry of the two
  * branches after the chain of continuations on the 3x6x6 2-D MOC case (tests/test_known_answer_2dmoc.py
  * gets 14.704 Sv), which exercises lin, nlin_rhs, nlin_jac, boundaries, forcing, the integral
- * condition and Newton-consistency of the Jacobian together; (a') by the GOLDEN STATE the reference itself wrote,
+ * condition and Newton-consistency of the Jacobian together -- and tests/continuation_oracle.cpp reaches the same numbers
+ * (14.7043 Sv, 0, symmetry 5.7e-5) with the reference's own UNMODIFIED Continuation<Model> (src/continuation/Continuation.H,
+ * compiled in place) driving this oracle through all seven legs of that test (tests/test_continuation_oracle.py); (a') by the GOLDEN STATE the reference itself wrote,
  * test/ocean/ocean_reference.h5 (end of the 16^3 gateway continuation of src/tests/reft_ocean.C: land mask, periodic,
  * forcing type 2, convective adjustment with P_VC = 9.95): the oracle's residual at that state with the parameters stored
  * beside it is ||F||_2 = 7.7e-6 against ||F(0)||_2 = 19.8 -- 1e-11 in the momentum rows, 1e-15 in continuity -- i.e. a
  * root of the reference's F is a root of the oracle's F (tests/test_reference_state.py, fixture
  * tests/golden/ocean_reference.npz made by tests/golden/make_fixtures.py); and (b) by the invariants I1-I5 of
- * SURVEY.md section 8c (tests/test_oracle_invariants.py, tests/test_dist_cpu.py).  Not pinned by
+ * SURVEY.md section 8c (tests/test_oracle_invariants.py, tests/test_dist_cpu.py).  The GMRES restatement is pinned bit for
+ * bit against the reference's GMRESSolver.H itself, compiled and run here (tests/test_gmres_reference_pin.py).  Not pinned by
  * any reference number: the Jacobian values themselves (consistency with F only: I4 and the directional
  * difference at the golden state).
  *

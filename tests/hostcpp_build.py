@@ -40,3 +40,23 @@ def build_continuation_oracle():
     if r.returncode != 0:
         raise RuntimeError("continuation_oracle.cpp does not compile against the reference's Continuation.H:\n" + r.stderr[-4000:])
     return ORACLE_EXE
+
+
+GMRES_REF_EXE = os.path.join(ROOT, "tests", "_build", "gmres_reference")
+
+
+def build_gmres_reference():
+    """tests/gmres_reference.cpp: the reference's unmodified GMRESSolver.H on plain host vectors (pins oracle/gmres_oracle.cpp).
+    -> path of the binary, or None when the reference tree is absent"""
+    ref = "/root/reference/src/gmressolver"
+    if not os.path.isdir(ref):
+        return GMRES_REF_EXE if os.path.exists(GMRES_REF_EXE) else None
+    os.makedirs(os.path.dirname(GMRES_REF_EXE), exist_ok=True)
+    # the reference's serial PRINT macro takes one argument but is called with two (GMRESMacros.H:18): define it here;
+    # no FMA contraction, like the oracle
+    cmd = ["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-DPRINT(m,v)=do{}while(0)", "-I", os.path.join(ROOT, "tests", "compat"),
+           "-I", ref, os.path.join(ROOT, "tests", "gmres_reference.cpp"), "-o", GMRES_REF_EXE]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("gmres_reference.cpp does not compile against the reference's GMRESSolver.H:\n" + r.stderr[-4000:])
+    return GMRES_REF_EXE
