@@ -10,7 +10,8 @@
 // singular (no fixed pressure points); the solves of Newton's last steps have right-hand sides at the rounding floor of F and
 // end at the accuracy guard of the driver (iemic_b200/csrc/gmres_guard.h, return code 2) -- without it the second leg aborts
 // at the minimum step size inside the secant destination process (tests/test_continuation_oracle.py shows the same on the
-// CPU walk-through of the driver).
+// CPU walk-through of the driver).  On one B200 the seven legs take 21 s and end at psi_max = 14.7043 Sv, psi_min = 0, mirror
+// symmetry 5.6e-5 (profiles/r09_continuation_chain_gpu.txt; asserted by tests/test_host_cpp.py).
 //
 // Build (the test does this): g++ -std=c++17 -Itests/compat -I<reference>/src/continuation -Iinclude -Iiemic_b200/host
 //                             tests/continuation_dropin.cpp -Liemic_b200/lib -liemic_b200
