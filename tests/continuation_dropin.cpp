@@ -24,6 +24,7 @@
 #include <vector>
 #include "OceanB200.H"
 #include "Continuation.H"
+#include "continuation_cases.H"
 
 using namespace iemic_b200;
 
@@ -38,6 +39,20 @@ static void write_state(OceanB200& ocean, const std::string& path) {
 }
 
 int main(int argc, char** argv) {
+  if (argc > 2 && std::string(argv[1]) == "ocean") { // ocean <maskfile>: TEST(Ocean, Continuation), test_ocean.C:178-223
+    try {
+      const thcm_b200_config c = test_ocean_config<thcm_b200_config>();
+      const std::vector<int> mask = read_mask_file(argv[2], (size_t)(c.n + 2) * (c.m + 2) * (c.l + 2));
+      auto ocean = std::make_shared<OceanB200>(c, mask.data());
+      ocean->setSolverParameters(1e-10, 4000, 500, GMRES_B200_CGS2);
+      ocean->usePointBlockJacobi(true);
+      ocean->setVerbose(std::getenv("IEMIC_COMPAT_VERBOSE") != nullptr);
+      return run_test_ocean_continuation<Continuation<std::shared_ptr<OceanB200>>>(ocean) == 0 ? 0 : 1;
+    } catch (const std::exception& e) {
+      std::printf("continuation drop-in failed: %s\n", e.what());
+      return 1;
+    }
+  }
   const bool chain = argc > 2 && std::string(argv[1]) == "chain";
   const std::string outdir = chain ? argv[2] : "";
   const double destination = (!chain && argc > 1) ? std::atof(argv[1]) : 1.0;

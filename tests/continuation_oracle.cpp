@@ -201,6 +201,7 @@ class OracleModel {
 };
 
 #include "Continuation.H"
+#include "continuation_cases.H"
 
 static void write_state(OracleModel& m, const std::string& path) {
   auto x = m.getState('V');
@@ -211,6 +212,17 @@ static void write_state(OracleModel& m, const std::string& path) {
 }
 
 int main(int argc, char** argv) {
+  if (argc > 2 && std::string(argv[1]) == "ocean") { // ocean <maskfile> [mode]: TEST(Ocean, Continuation), test_ocean.C:178-223
+    try {
+      const thcm_oracle_config c = test_ocean_config<thcm_oracle_config>();
+      const std::vector<int> mask = read_mask_file(argv[2], (size_t)(c.n + 2) * (c.m + 2) * (c.l + 2));
+      auto ocean = std::make_shared<OracleModel>(c, mask.data(), argc > 3 ? argv[3] : "gmres");
+      return run_test_ocean_continuation<Continuation<std::shared_ptr<OracleModel>>>(ocean) == 0 ? 0 : 1;
+    } catch (const std::exception& e) {
+      std::printf("continuation on the oracle failed: %s\n", e.what());
+      return 1;
+    }
+  }
   const std::string outdir = argc > 1 ? argv[1] : ".";
   const std::string mode = argc > 2 ? argv[2] : "gmres";
   const int nlegs = argc > 3 ? std::atoi(argv[3]) : 7;

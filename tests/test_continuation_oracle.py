@@ -54,3 +54,35 @@ def test_product_gmres_driver_needs_the_accuracy_guard(tmp_path):
     assert len(legs) == 2 and all("status 0" in ln for ln in legs), out[-2000:]
     rc0, out0 = _run(tmp_path, "cgs2", 2, env={"ORACLE_GUARD": "0"})
     assert rc0 != 0 and "leg CMPR -> -0.2: status 1" in out0, out0[-2000:]
+
+
+def _natl8_mask_file(tmp_path):
+    import cases
+    cfg, mask, _ = cases.case("natl8")
+    path = tmp_path / "mask_natl8.bin"
+    np.asarray(mask, np.int32).tofile(path)
+    return str(path)
+
+
+def parse_test_ocean(out):
+    """-> (status, parameter value, ||x||, ||F||) of the line continuation_cases.H prints"""
+    import re
+    m = re.search(r"test_ocean continuation: status (-?\d+), Combined Forcing = (\S+), \|\|x\|\| = (\S+), \|\|F\|\| = (\S+)", out)
+    assert m, out[-2000:]
+    return int(m.group(1)), float(m.group(2)), float(m.group(3)), float(m.group(4))
+
+
+def test_test_ocean_continuation_with_the_reference_continuation(tmp_path):
+    """TEST(Ocean, Continuation), src/tests/test_ocean.C:178-223 (8x8x4 North Atlantic box, Newton-chord hybrid corrector,
+    five steps): the reference asserts status 0.  Run with the oracle's GMRESSolver restatement and with the walk-through of
+    the product's GMRES driver: same branch point."""
+    mask = _natl8_mask_file(tmp_path)
+    res = {}
+    for mode in ("gmres", "cgs2"):
+        r = subprocess.run([_exe(), "ocean", mask, mode], capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stdout[-2000:]
+        res[mode] = parse_test_ocean(r.stdout)
+        assert res[mode][0] == 0
+        assert res[mode][1] > 0.0 and res[mode][2] > 0.0
+    assert abs(res["gmres"][1] - res["cgs2"][1]) <= 1e-7 * abs(res["gmres"][1])
+    assert abs(res["gmres"][2] - res["cgs2"][2]) <= 1e-7 * res["gmres"][2]

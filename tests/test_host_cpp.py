@@ -73,6 +73,29 @@ def test_reference_intt_2dmoc_chain_on_gpu(tmp_path):
 
 
 @pytest.mark.gpu
+def test_reference_test_ocean_continuation_on_gpu(tmp_path):
+    """TEST(Ocean, Continuation), src/tests/test_ocean.C:178-223, by the reference's own Continuation.H on the CUDA path
+    (8x8x4 North Atlantic box with land, Newton-chord hybrid corrector, five steps; the reference asserts status 0), and the
+    same run on the CPU oracle: same point on the branch."""
+    import hostcpp_build
+    from test_continuation_oracle import _natl8_mask_file, parse_test_ocean
+    exe = hostcpp_build.build_continuation_dropin()
+    ora = hostcpp_build.build_continuation_oracle()
+    if not exe or not os.path.exists(exe) or not ora or not os.path.exists(ora):
+        pytest.skip("tests/_build programs were not built (they need the reference tree at build time)")
+    mask = _natl8_mask_file(tmp_path)
+    r = subprocess.run([exe, "ocean", mask], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    st, par, nx, nf = parse_test_ocean(r.stdout)
+    assert st == 0
+    o = subprocess.run([ora, "ocean", mask, "gmres"], capture_output=True, text=True, timeout=600)
+    assert o.returncode == 0, o.stdout[-3000:]
+    st_o, par_o, nx_o, nf_o = parse_test_ocean(o.stdout)
+    assert st_o == 0
+    assert abs(par - par_o) <= 1e-6 * abs(par_o) and abs(nx - nx_o) <= 1e-6 * nx_o
+
+
+@pytest.mark.gpu
 def test_host_mirror_runs_on_gpu(tmp_path):
     exe = str(tmp_path / "selftest")
     libdir = os.path.join(ROOT, "iemic_b200", "lib")
