@@ -18,7 +18,9 @@
  * test/ocean/ocean_reference.h5 (end of the 16^3 gateway continuation of src/tests/reft_ocean.C: land mask, periodic,
  * forcing type 2, convective adjustment with P_VC = 9.95): the oracle's residual at that state with the parameters stored
  * beside it is ||F||_2 = 7.7e-6 against ||F(0)||_2 = 19.8 -- 1e-11 in the momentum rows, 1e-15 in continuity -- i.e. a
- * root of the reference's F is a root of the oracle's F (tests/test_reference_state.py, fixture
+ * root of the reference's F is a root of the oracle's F, and conversely Newton on the oracle's F and J -- from that state, or
+ * from the zero state through a continuation (tests/golden/reft_from_scratch.py) -- ends on the golden vector: every u, v, w,
+ * T, S value within 4e-6, the per-field norms reft_ocean.C:62-79 compares within 6e-5 of its 1e-3 (tests/test_reference_state.py, fixture
  * tests/golden/ocean_reference.npz made by tests/golden/make_fixtures.py); and (b) by the invariants I1-I5 of
  * SURVEY.md section 8c (tests/test_oracle_invariants.py, tests/test_dist_cpu.py).  The GMRES restatement is pinned bit for
  * bit against the reference's GMRESSolver.H itself, compiled and run here (tests/test_gmres_reference_pin.py).  Not pinned by

@@ -223,6 +223,18 @@ int main(int argc, char** argv) {
       return 1;
     }
   }
+  if (argc > 3 && std::string(argv[1]) == "reft") { // reft <maskfile> <state out> [mode]: src/tests/reft_ocean.C:31-80
+    try {
+      const thcm_oracle_config c = reft_ocean_config<thcm_oracle_config>();
+      const std::vector<int> mask = read_mask_file(argv[2], (size_t)(c.n + 2) * (c.m + 2) * (c.l + 2));
+      auto ocean = std::make_shared<OracleModel>(c, mask.data(), argc > 4 ? argv[4] : "gmres");
+      const std::string out = argv[3];
+      return run_reft_ocean_continuation<Continuation<std::shared_ptr<OracleModel>>>(ocean, [&] { write_state(*ocean, out); }) == 0 ? 0 : 1;
+    } catch (const std::exception& e) {
+      std::printf("continuation on the oracle failed: %s\n", e.what());
+      return 1;
+    }
+  }
   const std::string outdir = argc > 1 ? argv[1] : ".";
   const std::string mode = argc > 2 ? argv[2] : "gmres";
   const int nlegs = argc > 3 ? std::atoi(argv[3]) : 7;
