@@ -2,11 +2,14 @@
 (src/utils/Model.H:149-232: groups "State", "Parameters", and for the ocean "MaskGlobal" etc., written through
 EpetraExt::HDF5) and the plain-text land-mask files of data/mkmask (readmask, src/ocean/topo.F90:41-75).
 
-Read-only: a state computed by a reference run can be loaded into the B200 path (Ocean.setPar / device vectors);
-writing the format back is not implemented."""
+load_state: a state computed by a reference run can be loaded into the B200 path (Ocean.setPar / device vectors).
+save_state: the same groups written back (State as an Epetra_MultiVector with a linear map, every parameter, the global
+land mask), in the file structure libhdf5 gives EpetraExt::HDF5 (iemic_b200.h5min.write); the ocean's surface flux
+diagnostics (Ocean.C:1946-1990) are not part of this path and are not written."""
 import numpy as np
 
 from .capi import PAR_NAMES
+from . import h5min
 from .h5min import H5File
 
 # names Model.H stores that THCM::par2int does not know under that spelling
@@ -46,3 +49,29 @@ def read_mask(path, n, m, l):
             a[k, j, :] = [int(ch) for ch in row]
             p += 1
     return a
+
+
+def save_state(path, state, parameters, mask=None, cfg=None):
+    """Model::saveStateToFile (src/utils/Model.H:254-310, EpetraExt::HDF5::Write of an Epetra_MultiVector and of scalars):
+    group "State" = {GlobalLength, NumVectors, Values (1 x N), __type__}, group "Parameters" = one double per name; with
+    cfg (the dict thcm_b200_create takes) the scalars of group "Grid" (:281-291; the coordinate arrays x, y, z, xu, yv, zw
+    are not written, loadStateFromFile does not read them); with a land mask int32[(l+2), (m+2), (n+2)] also
+    "MaskGlobal" = {Global, GlobalSize, Label, Surface} like Ocean::additionalExports (src/ocean/Ocean.C:1936-1944;
+    Surface: the top ocean level, n x m).  load_state reads it back."""
+    state = np.ascontiguousarray(state, np.float64).ravel()
+    tree = {
+        "State": {"GlobalLength": np.int32(state.size), "NumVectors": np.int32(1), "Values": state.reshape(1, -1),
+                  "__type__": np.array([b"Epetra_MultiVector"], "S19")},
+        "Parameters": {str(k): np.float64(v) for k, v in parameters.items()},
+    }
+    if cfg is not None:
+        tree["Grid"] = {k: np.int32(cfg[k]) for k in ("n", "m", "l")}
+        tree["Grid"].update(nun=np.int32(6), aux=np.int32(0))
+        tree["Grid"].update({k: np.float64(cfg[k]) for k in ("xmin", "xmax", "ymin", "ymax", "hdim")})
+    if mask is not None:
+        mask = np.ascontiguousarray(mask, np.int32)
+        if mask.ndim != 3:
+            raise ValueError("mask must have the shape (l+2, m+2, n+2)")
+        tree["MaskGlobal"] = {"Global": mask.ravel(), "GlobalSize": np.int32(mask.size), "Label": np.array([b"current"], "S8"),
+                              "Surface": mask[-2, 1:-1, 1:-1].ravel()}
+    h5min.write(path, tree)

@@ -152,3 +152,119 @@ if __name__ == "__main__":
             else:
                 print(" " * ind + k, v.dtype, v.shape, v.ravel()[:4])
     show(t)
+
+
+# ---- writer -----------------------------------------------------------------------------------------------------------
+# The same subset, written: superblock version 0, one symbol-table group per dict (version-1 B-tree with a single leaf, one
+# symbol node, local heap), version-1 object headers, contiguous datasets.  Layout decisions follow what libhdf5 1.8 writes
+# for such files (the reference's EpetraExt::HDF5 sits on it), so that files written here have the structure of the files
+# read above; "Group Leaf Node K" in the superblock is raised so that every group fits one symbol node.
+
+_LEAF_K, _INTERNAL_K = 32, 16
+
+
+def _pad8(b):
+    return b + b"\0" * (-len(b) % 8)
+
+
+def _msg(mtype, body, flags=0):
+    body = _pad8(body)
+    return struct.pack("<HHB3x", mtype, len(body), flags) + body
+
+
+def _ohdr(messages):
+    body = b"".join(messages)
+    return struct.pack("<BBHII4x", 1, 0, len(messages), 1, len(body)) + body
+
+
+def _datatype(dtype):
+    dtype = np.dtype(dtype)
+    if dtype.kind == "f" and dtype.itemsize == 8:
+        return struct.pack("<B3BI", 0x11, 0x20, 0x3F, 0x00, 8) + struct.pack("<HHBBBBI", 0, 64, 52, 11, 0, 52, 1023)
+    if dtype.kind in "iu" and dtype.itemsize in (4, 8):
+        return struct.pack("<B3BI", 0x10, 0x08 if dtype.kind == "i" else 0x00, 0, 0, dtype.itemsize) + struct.pack("<HH", 0, 8 * dtype.itemsize)
+    if dtype.kind == "S":
+        return struct.pack("<B3BI", 0x13, 0x00, 0, 0, dtype.itemsize)
+    raise NotImplementedError("dtype %s" % dtype)
+
+
+class _Writer:
+    def __init__(self):
+        self.buf = bytearray(96)  # superblock + root symbol table entry, filled in at the end
+
+    def alloc(self, data):
+        self.buf += b"\0" * (-len(self.buf) % 8)
+        addr = len(self.buf)
+        self.buf += data
+        return addr
+
+    def dataset(self, arr):
+        arr = np.asarray(arr)
+        if arr.dtype.kind == "U":
+            arr = arr.astype("S")
+        if arr.dtype.kind == "f":
+            arr = arr.astype("<f8")
+        elif arr.dtype.kind in "iu":
+            arr = arr.astype("<i4" if arr.dtype.itemsize <= 4 else "<i8")
+        raw = np.ascontiguousarray(arr).tobytes()
+        addr = self.alloc(raw) if raw else UNDEF
+        # like the files libhdf5 writes for EpetraExt: maximum dimensions present (= dimensions) for arrays, fill value
+        # message version 2 "early allocation, write if set, defined with size 0"
+        dims = b"".join(struct.pack("<Q", s) for s in arr.shape)
+        space = struct.pack("<BBB5x", 1, arr.ndim, 1 if arr.ndim else 0) + dims + (dims if arr.ndim else b"")
+        msgs = [_msg(0x01, space), _msg(0x03, _datatype(arr.dtype), flags=1), _msg(0x05, struct.pack("<BBBBI", 2, 1, 2, 1, 0)),
+                _msg(0x08, struct.pack("<BBQQ", 3, 1, addr, len(raw)))]
+        return self.alloc(_ohdr(msgs))
+
+    def group(self, members):
+        """members: {name: dict | array}; -> (object header address, B-tree address, heap address)"""
+        assert len(members) <= 2 * _LEAF_K, "too many members for one symbol node"
+        children = {}
+        for name in sorted(members, key=lambda s: s.encode()):
+            v = members[name]
+            children[name] = self.group(v) if isinstance(v, dict) else (self.dataset(v), None, None)
+        # local heap: the empty name at offset 0, then the names, then one free block
+        seg = bytearray(8)
+        offs = {}
+        for name in children:
+            offs[name] = len(seg)
+            seg += _pad8(name.encode() + b"\0")
+        free_off = len(seg)
+        seg += struct.pack("<QQ", 1, 16)  # last free block: next = 1 (H5HL_FREE_NULL), size of this block
+        heap_hdr = self.alloc(bytes(32))
+        seg_addr = self.alloc(bytes(seg))
+        self.buf[heap_hdr:heap_hdr + 32] = b"HEAP" + struct.pack("<B3xQQQ", 0, len(seg), free_off, seg_addr)
+        # symbol node
+        snod = bytearray(b"SNOD" + struct.pack("<BBH", 1, 0, len(children)))
+        for name, (ohdr, bt, hp) in children.items():
+            if bt is None:
+                snod += struct.pack("<QQII16x", offs[name], ohdr, 0, 0)
+            else:
+                snod += struct.pack("<QQIIQQ", offs[name], ohdr, 1, 0, bt, hp)
+        snod += bytes(8 + 40 * 2 * _LEAF_K - len(snod))
+        snod_addr = self.alloc(bytes(snod))
+        # B-tree: one leaf node with one child; keys are heap offsets of the names bounding the child
+        last = offs[list(children)[-1]] if children else 0
+        node = bytearray(b"TREE" + struct.pack("<BBHQQ", 0, 0, 1 if children else 0, UNDEF, UNDEF))
+        node += struct.pack("<QQQ", 0, snod_addr, last)
+        node += bytes(24 + 8 * (2 * _INTERNAL_K + 1) + 8 * 2 * _INTERNAL_K - len(node))
+        bt_addr = self.alloc(bytes(node))
+        ohdr = self.alloc(_ohdr([_msg(0x11, struct.pack("<QQ", bt_addr, heap_hdr))]))
+        return ohdr, bt_addr, heap_hdr
+
+    def finish(self, root):
+        ohdr, bt, hp = root
+        sb = b"\x89HDF\r\n\x1a\n" + struct.pack("<BBBBBBBBHHI", 0, 0, 0, 0, 0, 8, 8, 0, _LEAF_K, _INTERNAL_K, 0)
+        sb += struct.pack("<QQQQ", 0, UNDEF, len(self.buf), UNDEF)
+        sb += struct.pack("<QQIIQQ", 0, ohdr, 1, 0, bt, hp)
+        assert len(sb) == 96
+        self.buf[:96] = sb
+        return bytes(self.buf)
+
+
+def write(path, tree):
+    """tree: nested dict, groups -> dicts, datasets -> arrays (float64, int32/int64, fixed strings) or scalars"""
+    w = _Writer()
+    data = w.finish(w.group(tree))
+    with open(path, "wb") as f:
+        f.write(data)
