@@ -56,39 +56,18 @@ int main(int argc, char** argv) {
   const bool chain = argc > 2 && std::string(argv[1]) == "chain";
   const std::string outdir = chain ? argv[2] : "";
   const double destination = (!chain && argc > 1) ? std::atof(argv[1]) : 1.0;
-  const double d2r = 3.14159265358979323846 / 180.0;
-  const int n = 3, m = 6, l = 6; // test/2dmoc/ocean_params.xml
-  thcm_b200_config c{};
-  c.n = n; c.m = m; c.l = l;
-  c.xmin = 286 * d2r; c.xmax = 350 * d2r; c.ymin = -60 * d2r; c.ymax = 60 * d2r;
-  c.periodic = 1; c.hdim = 4000.0; c.qz = 1.0; c.alphaT = 1.0e-4; c.alphaS = 7.6e-4;
-  c.ih = 0; c.vmix = 1; c.tap = 1; c.rho_mixing = 0; c.coriolis_on = 0; c.forcing_type = 1;
-  c.tres = 1; c.sres = 0; c.iza = 2; c.ite = 1; c.its = 1; c.coupled_T = 0; c.coupled_S = 0;
-  c.int_sign = -1; c.intcond_i = -1; c.intcond_j = -1; c.fix_pressure_points = 0;
-  std::vector<int> mask((size_t)(n + 2) * (m + 2) * (l + 2), 1); // LAND ring, OCEAN inside, PERIO in the x border columns
-  for (int k = 1; k <= l; k++) for (int j = 1; j <= m; j++) for (int i = 0; i <= n + 1; i++)
-    mask[(size_t)i + (size_t)(n + 2) * (j + (size_t)(m + 2) * k)] = (i == 0 || i == n + 1) ? 3 : 0;
+  const thcm_b200_config c = moc2d_config<thcm_b200_config>(); // test/2dmoc/ocean_params.xml
+  const std::vector<int> mask = moc2d_mask(c.n, c.m, c.l);
   try {
     auto ocean = std::make_shared<OceanB200>(c, mask.data());
-    // "Starting Parameters" of test/2dmoc/ocean_params.xml
-    ocean->setPar("Combined Forcing", 0.0); ocean->setPar("Solar Forcing", 0.0); ocean->setPar("Salinity Forcing", 0.0);
-    ocean->setPar("Wind Forcing", 0.0); ocean->setPar("Temperature Forcing", 10.0); ocean->setPar("SPL1", 2.0e3);
-    ocean->setPar("SPL2", 0.01); ocean->setPar("P_VC", 0.0); ocean->setPar("Rossby-Number", 0.0); ocean->setPar("CMPR", 0.0);
-    ocean->setPar("Horizontal Ekman-Number", 371.764); ocean->setPar("Rayleigh-Number", 15.6869);
+    moc2d_starting_parameters(ocean); // "Starting Parameters" of test/2dmoc/ocean_params.xml
     // the linear solver of this path: restarted GMRES on the device with the device-built point-block Jacobi
     ocean->setSolverParameters(1e-10, 4000, 500, GMRES_B200_CGS2);
     ocean->usePointBlockJacobi(true);
     ocean->setVerbose(std::getenv("IEMIC_COMPAT_VERBOSE") != nullptr);
 
-    Teuchos::ParameterList pars("Continuation parameters"); // test/2dmoc/continuation_params.xml
-    pars.set("continuation parameter", "Combined Forcing");
-    pars.set("initial step size", 1.0e-1); pars.set("minimum step size", 1.0e-8); pars.set("maximum step size", 1.0);
-    pars.set("increase step size", 2.0); pars.set("decrease step size", 2.0); pars.set("destination 0", destination);
-    pars.set("maximum number of steps", -1); pars.set("Newton tolerance", 1.0e-3); pars.set("destination tolerance", 1.0e-6);
-    pars.set("maximum Newton iterations", 15); pars.set("backtracking steps", 5); pars.set("corrector residual test", 'D');
-    pars.set("epsilon increment", 1.0e-6); pars.set("state tangent scaling", 1.0);
-    pars.set("enable Newton Chord hybrid solve", false); pars.set("backtracking increase", 1.0); pars.set("tangent type", 'S');
-    pars.set("predictor bound", 100.0);
+    Teuchos::ParameterList pars = moc2d_continuation_params(); // test/2dmoc/continuation_params.xml
+    pars.set("destination 0", destination);
 
     Continuation<std::shared_ptr<OceanB200>> continuation(ocean, pars);
     const int status = continuation.run();

@@ -212,6 +212,7 @@ static void write_state(OracleModel& m, const std::string& path) {
 }
 
 int main(int argc, char** argv) {
+  if (argc > 1 && std::string(argv[1]) == "cases") { print_cases<thcm_oracle_config>(); return 0; } // for tests/test_params.py
   if (argc > 2 && std::string(argv[1]) == "ocean") { // ocean <maskfile> [mode]: TEST(Ocean, Continuation), test_ocean.C:178-223
     try {
       const thcm_oracle_config c = test_ocean_config<thcm_oracle_config>();
@@ -238,34 +239,13 @@ int main(int argc, char** argv) {
   const std::string outdir = argc > 1 ? argv[1] : ".";
   const std::string mode = argc > 2 ? argv[2] : "gmres";
   const int nlegs = argc > 3 ? std::atoi(argv[3]) : 7;
-  const double d2r = 3.14159265358979323846 / 180.0;
-  const int n = 3, m = 6, l = 6; // test/2dmoc/ocean_params.xml
-  thcm_oracle_config c{};
-  c.n = n; c.m = m; c.l = l;
-  c.xmin = 286 * d2r; c.xmax = 350 * d2r; c.ymin = -60 * d2r; c.ymax = 60 * d2r;
-  c.periodic = 1; c.hdim = 4000.0; c.qz = 1.0; c.alphaT = 1.0e-4; c.alphaS = 7.6e-4;
-  c.ih = 0; c.vmix = 1; c.tap = 1; c.rho_mixing = 0; c.coriolis_on = 0; c.forcing_type = 1;
-  c.tres = 1; c.sres = 0; c.iza = 2; c.ite = 1; c.its = 1; c.coupled_T = 0; c.coupled_S = 0;
-  c.int_sign = -1; c.intcond_i = -1; c.intcond_j = -1; c.fix_pressure_points = 0;
-  std::vector<int> mask((size_t)(n + 2) * (m + 2) * (l + 2), 1);
-  for (int k = 1; k <= l; k++) for (int j = 1; j <= m; j++) for (int i = 0; i <= n + 1; i++)
-    mask[(size_t)i + (size_t)(n + 2) * (j + (size_t)(m + 2) * k)] = (i == 0 || i == n + 1) ? 3 : 0;
+  const thcm_oracle_config c = moc2d_config<thcm_oracle_config>(); // test/2dmoc/ocean_params.xml
+  const std::vector<int> mask = moc2d_mask(c.n, c.m, c.l);
   try {
     auto ocean = std::make_shared<OracleModel>(c, mask.data(), mode);
-    ocean->setPar("Combined Forcing", 0.0); ocean->setPar("Solar Forcing", 0.0); ocean->setPar("Salinity Forcing", 0.0);
-    ocean->setPar("Wind Forcing", 0.0); ocean->setPar("Temperature Forcing", 10.0); ocean->setPar("SPL1", 2.0e3);
-    ocean->setPar("SPL2", 0.01); ocean->setPar("P_VC", 0.0); ocean->setPar("Rossby-Number", 0.0); ocean->setPar("CMPR", 0.0);
-    ocean->setPar("Horizontal Ekman-Number", 371.764); ocean->setPar("Rayleigh-Number", 15.6869);
+    moc2d_starting_parameters(ocean); // "Starting Parameters" of test/2dmoc/ocean_params.xml
 
-    Teuchos::ParameterList pars("Continuation parameters"); // test/2dmoc/continuation_params.xml
-    pars.set("continuation parameter", "Combined Forcing");
-    pars.set("initial step size", 1.0e-1); pars.set("minimum step size", 1.0e-8); pars.set("maximum step size", 1.0);
-    pars.set("increase step size", 2.0); pars.set("decrease step size", 2.0); pars.set("destination 0", 1.0);
-    pars.set("maximum number of steps", -1); pars.set("Newton tolerance", 1.0e-3); pars.set("destination tolerance", 1.0e-6);
-    pars.set("maximum Newton iterations", 15); pars.set("backtracking steps", 5); pars.set("corrector residual test", 'D');
-    pars.set("epsilon increment", 1.0e-6); pars.set("state tangent scaling", 1.0);
-    pars.set("enable Newton Chord hybrid solve", false); pars.set("backtracking increase", 1.0); pars.set("tangent type", 'S');
-    pars.set("predictor bound", 100.0);
+    Teuchos::ParameterList pars = moc2d_continuation_params(); // test/2dmoc/continuation_params.xml
 
     struct Leg { const char* par; double dest, ds; const char* save; };
     const Leg legs[] = {{"Combined Forcing", 1.0, 0.1, nullptr}, {"CMPR", -0.2, -0.5, nullptr}, {"Salinity Forcing", 0.02, 0.5, nullptr},

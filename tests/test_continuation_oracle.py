@@ -5,7 +5,7 @@ Continuation<Model> (src/continuation/Continuation.H, compiled in place) on the 
 oracle's F and J (invariant I6) through the reference's own driver rather than a solver of ours.
 
 Two linear solvers: a dense LU (exact up to the pressure null vector), and a host walk-through of the product's GMRES driver
-(CGS2 + the accuracy guard of iemic_b200/csrc/gmres_guard.h).  Without the guard the CGS2 driver fails the second leg: the
+(CGS2 + the accuracy guard of iemic_b200/csrc/gmres_guard.h).  Without the guard the CGS2 driver fails the first or the second leg: the
 Jacobian is singular here (no fixed pressure points), Newton's last right-hand sides sit at the rounding floor of F, and a
 solve accepted on the recurrence residual returns a multiple of the null vector (same failure seen on the GPU)."""
 import os
@@ -53,7 +53,8 @@ def test_product_gmres_driver_needs_the_accuracy_guard(tmp_path):
     legs = [ln for ln in out.splitlines() if ln.startswith("leg ")]
     assert len(legs) == 2 and all("status 0" in ln for ln in legs), out[-2000:]
     rc0, out0 = _run(tmp_path, "cgs2", 2, env={"ORACLE_GUARD": "0"})
-    assert rc0 != 0 and "leg CMPR -> -0.2: status 1" in out0, out0[-2000:]
+    # which solve goes wrong first depends on the last bits of the set-up (leg 1 or leg 2); one of them does
+    assert rc0 != 0 and ": status 1" in out0, out0[-2000:]
 
 
 def _natl8_mask_file(tmp_path):

@@ -1,0 +1,103 @@
+"""The reference's XML parameter files, read unchanged (iemic_b200/params.py), against what the test-suite hard-codes: the
+Python cases (tests/cases.py, iemic_b200/grids.py) and the C++ set-ups of the Continuation harness
+(tests/continuation_cases.H, printed by `continuation_oracle cases`).  The reference tree only exists in the build container."""
+import math
+import os
+import subprocess
+
+import pytest
+
+import cases
+from iemic_b200 import params
+
+REF = "/root/reference"
+needs_ref = pytest.mark.skipif(not os.path.isdir(os.path.join(REF, "test", "ocean")), reason="reference checkout not present")
+
+
+def _same_cfg(a, b):
+    assert set(a) == set(b), set(a) ^ set(b)
+    for k in a:
+        assert a[k] == b[k], (k, a[k], b[k])
+
+
+@needs_ref
+@pytest.mark.parametrize("xml,case,mask", [
+    ("test/ocean/ocean_params.xml", "natl8", "mask_natl8"),
+    ("test/2dmoc/ocean_params.xml", "2dmoc", None),
+    ("test/matrix/ocean_params.xml", None, "test6x6x4"),
+])
+def test_thcm_config_from_the_reference_files(xml, case, mask):
+    cfg, start, mask_file = params.thcm_config(params.read_parameter_list(os.path.join(REF, xml)))
+    assert mask_file == mask
+    if case:
+        c2, _, _ = cases.case(case)
+        _same_cfg(cfg, c2)
+    assert start["SPL2"] == 0.01 and "Combined Forcing" in start
+
+
+@needs_ref
+def test_reft_ocean_config_is_the_golden_state_case():
+    cfg, start, mask_file = params.thcm_config(params.read_parameter_list(os.path.join(REF, "test/ocean/reft_ocean_params.xml")))
+    _same_cfg(cfg, cases.reference_state()[0])   # "Mixing" = 2 maps to the always-on operator, see params.thcm_config
+    assert mask_file == "mask_gateway" and start["Salinity Forcing"] == 0.1
+
+
+@needs_ref
+def test_unsupported_options_fail_loudly():
+    with pytest.raises(ValueError, match="idealized forcing"):      # Levitus data files
+        params.thcm_config(params.read_parameter_list(os.path.join(REF, "run/ocean/global/ocean_params.xml")))
+    with pytest.raises(ValueError, match="not implemented"):         # salinity perturbation mask
+        params.thcm_config(params.read_parameter_list(os.path.join(REF, "run/2dmoc/ocean_params.xml")))
+    with pytest.raises(ValueError, match="unknown THCM parameters"):  # stale names: the reference's validation rejects them too
+        params.thcm_config(params.read_parameter_list(os.path.join(REF, "parameterfiles/ocean_params.xml")))
+    with pytest.raises(ValueError, match="type"):
+        params.thcm_config({"THCM": {"Global Grid-Size n": "16"}})
+
+
+def test_defaults_without_a_file():
+    cfg, start, mask_file = params.thcm_config({})
+    assert (cfg["n"], cfg["m"], cfg["l"]) == (16, 16, 16) and cfg["rho_mixing"] == 1 and not cfg["periodic"]
+    assert cfg["xmin"] == 286.0 * math.pi / 180.0 and start == {} and mask_file is None
+
+
+def _harness_cases():
+    import hostcpp_build
+    exe = hostcpp_build.build_continuation_oracle()
+    if exe is None:
+        pytest.skip("tests/_build/continuation_oracle not built")
+    out = subprocess.run([exe, "cases"], capture_output=True, text=True, check=True).stdout
+    res, cur = {}, None
+    for line in out.splitlines():
+        if line.startswith("CASE "):
+            cur = res.setdefault(line[5:], {"cfg": {}, "cont": {}})
+        elif line.startswith("cfg "):
+            _, k, v = line.split(" ", 2)
+            cur["cfg"][k] = float(v)
+        elif line.startswith("cont "):
+            k, v = line[5:].split(" = ", 1)
+            cur["cont"][k] = v
+    return res
+
+
+@needs_ref
+@pytest.mark.parametrize("name,ocean_xml,cont_xml", [
+    ("test_ocean", "test/ocean/ocean_params.xml", "test/ocean/continuation_params.xml"),
+    ("reft_ocean", "test/ocean/reft_ocean_params.xml", "test/ocean/reft_continuation_params.xml"),
+    ("2dmoc", "test/2dmoc/ocean_params.xml", "test/2dmoc/continuation_params.xml"),
+])
+def test_harness_cases_are_the_reference_files(name, ocean_xml, cont_xml):
+    h = _harness_cases()[name]
+    cfg, _, _ = params.thcm_config(params.read_parameter_list(os.path.join(REF, ocean_xml)))
+    assert set(h["cfg"]) == set(cfg)
+    for k, v in cfg.items():
+        assert h["cfg"][k] == float(v), (k, h["cfg"][k], v)   # bit for bit, bounds included
+    cont = params.read_parameter_list(os.path.join(REF, cont_xml))
+    assert set(h["cont"]) == set(cont), set(h["cont"]) ^ set(cont)
+    for k, v in cont.items():
+        got = h["cont"][k]
+        if isinstance(v, bool):
+            assert got == ("1" if v else "0"), k
+        elif isinstance(v, (int, float)):
+            assert float(got) == float(v), (k, got, v)
+        else:
+            assert got == v, (k, got, v)
