@@ -101,3 +101,89 @@ def test_harness_cases_are_the_reference_files(name, ocean_xml, cont_xml):
             assert float(got) == float(v), (k, got, v)
         else:
             assert got == v, (k, got, v)
+
+
+# ---- the same front end in C++ (iemic_b200/host/ParameterListXML.H), through tests/xml_frontend.cpp -------------------------
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def xml_frontend(tmp_path_factory):
+    exe = str(tmp_path_factory.mktemp("xml") / "xml_frontend")
+    subprocess.run(["g++", "-std=c++17", "-Wall", "-O1", "-I", os.path.join(ROOT, "include"), "-I", os.path.join(ROOT, "iemic_b200", "host"),
+                    os.path.join(ROOT, "tests", "xml_frontend.cpp"), "-o", exe], check=True)
+    return exe
+
+
+@needs_ref
+@pytest.mark.parametrize("xml,shape", [("test/ocean/ocean_params.xml", (8, 8, 4)), ("test/2dmoc/ocean_params.xml", (3, 6, 6)),
+                                       ("test/ocean/reft_ocean_params.xml", (16, 16, 16)), ("test/matrix/ocean_params.xml", (6, 6, 4))])
+def test_cpp_front_end_equals_the_python_one(xml_frontend, tmp_path, xml, shape):
+    import numpy as np
+    from iemic_b200 import checkpoint
+    path = os.path.join(REF, xml)
+    cfg, start, mask_file = params.thcm_config(params.read_parameter_list(path))
+    out_mask = str(tmp_path / "mask.bin")
+    r = subprocess.run([xml_frontend, path, os.path.join(REF, "data", "mkmask"), out_mask], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout
+    got_cfg, got_start, got_mask = {}, {}, None
+    for line in r.stdout.splitlines():
+        if line.startswith("cfg "):
+            _, k, v = line.split(" ", 2)
+            got_cfg[k] = float(v)
+        elif line.startswith("start "):
+            k, v = line[6:].split(" = ")
+            got_start[k] = float(v)
+        elif line.startswith("mask "):
+            got_mask = line[5:] or None
+    assert (cfg["n"], cfg["m"], cfg["l"]) == shape
+    assert got_cfg == {k: float(v) for k, v in cfg.items()}
+    assert got_start == start and got_mask == mask_file
+    if mask_file:
+        n, m, l = shape
+        a = checkpoint.read_mask(os.path.join(REF, "data", "mkmask", mask_file), n, m, l)
+        assert np.array_equal(np.fromfile(out_mask, np.int32).reshape(a.shape), a)
+
+
+@needs_ref
+def test_cpp_front_end_rejects_what_the_python_one_rejects(xml_frontend):
+    for xml, msg in (("run/ocean/global/ocean_params.xml", "idealized forcing"), ("run/2dmoc/ocean_params.xml", "not implemented"),
+                     ("parameterfiles/ocean_params.xml", "unknown THCM parameter")):
+        r = subprocess.run([xml_frontend, os.path.join(REF, xml)], capture_output=True, text=True)
+        assert r.returncode == 3 and msg in r.stdout, (xml, r.stdout)
+
+
+@needs_ref
+def test_cpp_reader_sees_every_parameter(xml_frontend):
+    """all parameter files under test/ and run/ of the reference: same names, types and values as the Python reader"""
+    import glob
+
+    def flat(d, prefix=""):
+        out = {}
+        for k, v in d.items():
+            if isinstance(v, dict):
+                out.update(flat(v, prefix + k + "/"))
+            else:
+                out[prefix + k] = v
+        return out
+
+    files = sorted(glob.glob(os.path.join(REF, "test", "*", "*.xml")) + glob.glob(os.path.join(REF, "run", "*", "*.xml")))
+    assert len(files) > 40
+    checked = 0
+    for f in files:
+        try:
+            want = flat(params.read_parameter_list(f))
+        except Exception:
+            continue   # not a ParameterList file (or a type neither reader handles)
+        r = subprocess.run([xml_frontend, "--list", f], capture_output=True, text=True)
+        assert r.returncode == 0, (f, r.stdout)
+        got = {}
+        for line in r.stdout.splitlines():
+            k, rest = line.split(" = ", 1)
+            typ, _, val = rest.partition(" ")
+            got[k] = {"bool": lambda s: bool(int(s)), "int": int, "double": float, "char": str, "string": str}[typ](val)
+        assert set(got) == set(want), (f, set(got) ^ set(want))
+        for k in want:
+            assert got[k] == want[k] and type(got[k]) is type(want[k]), (f, k, got[k], want[k])
+        checked += 1
+    assert checked > 40
