@@ -153,6 +153,17 @@ class Ocean:
         self.nrows, self.nvec, self.nnz, self.nglobal = a.value, b.value, c.value, d.value
         self.ncell = self.nrows // 6
 
+    @classmethod
+    def from_xml(cls, ocean_params_file, mask_dir=".", **kw):
+        """Ocean::Ocean(comm, oceanParams) for this path: the reference's ocean parameter file and land-mask file, unchanged
+        (iemic_b200.params.ocean_setup); "Starting Parameters" are applied."""
+        from . import params
+        cfg, mask, start = params.ocean_setup(ocean_params_file, mask_dir)
+        o = cls(cfg, mask, **kw)
+        for name, value in start.items():
+            o.setPar(name, value)
+        return o
+
     def close(self):
         if getattr(self, "h", None):
             lib().thcm_b200_destroy(self.h)

@@ -119,3 +119,22 @@ def thcm_config(ocean_params):
     start = {k: float(v) for k, v in p.get("Starting Parameters", {}).items() if not (isinstance(v, float) and math.isnan(v))}
     mask_file = g["Land Mask"] if g["Read Land Mask"] else None
     return cfg, start, mask_file
+
+
+def ocean_setup(ocean_params_file, mask_dir="."):
+    """Everything Ocean's constructor needs from the reference's files: -> (cfg, mask int32[(l+2), (m+2), (n+2)], starting
+    parameters).  The land mask is read from mask_dir (the reference's data/mkmask) when the file asks for one; "Topography" = 1
+    without a mask is the box without land (depth3land, topo.F90:167-177); other topographies need data files this path
+    does not have.  (C++: OceanB200::fromXML.)"""
+    import os
+    from . import checkpoint, grids
+    lst = read_parameter_list(ocean_params_file)
+    cfg, start, mask_file = thcm_config(lst)
+    n, m, l = cfg["n"], cfg["m"], cfg["l"]
+    if mask_file:
+        mask = checkpoint.read_mask(os.path.join(mask_dir, mask_file), n, m, l)
+    elif lst.get("THCM", lst).get("Topography", 1) == 1:
+        mask = grids.no_land_mask(n, m, l, bool(cfg["periodic"]))
+    else:
+        raise ValueError("topography data files are not part of this path; give a land mask")
+    return cfg, mask, start

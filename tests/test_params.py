@@ -187,3 +187,19 @@ def test_cpp_reader_sees_every_parameter(xml_frontend):
             assert got[k] == want[k] and type(got[k]) is type(want[k]), (f, k, got[k], want[k])
         checked += 1
     assert checked > 40
+
+
+@needs_ref
+def test_ocean_setup_reads_files_and_masks():
+    import numpy as np
+    from iemic_b200 import grids
+    from iemic_b200.capi import PAR_NAMES
+    cfg, mask, start = params.ocean_setup(os.path.join(REF, "test/ocean/ocean_params.xml"), os.path.join(REF, "data", "mkmask"))
+    c2, m2, _ = cases.case("natl8")
+    _same_cfg(cfg, c2)
+    assert np.array_equal(mask, np.asarray(m2).reshape(mask.shape))
+    assert all(k in PAR_NAMES for k in start)      # Ocean.from_xml passes these names to setPar
+    cfg, mask, start = params.ocean_setup(os.path.join(REF, "test/2dmoc/ocean_params.xml"))   # Topography 1, no mask file
+    assert np.array_equal(mask, grids.no_land_mask(3, 6, 6, True))
+    assert start["Horizontal Ekman-Number"] == 371.764
+
