@@ -47,6 +47,7 @@ inline int gmres_truncate(const double* R, int ldr, const double* s, const doubl
     if (!(est[j - 1] >= 0.0)) est[j - 1] = INFINITY; // NaN / Inf from a zero pivot
     if (est[j - 1] < best) best = est[j - 1];
   }
+  if (!(best < INFINITY)) { y.clear(); return 0; } // no usable sub-problem (zero pivots throughout): keep the start vector
   int keep = k;
   for (int j = 1; j <= k; j++) if (est[j - 1] <= 2.0 * best) { keep = j; break; }
   solve(keep);
