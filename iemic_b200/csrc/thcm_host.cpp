@@ -479,24 +479,29 @@ void Host::build_forcing(bool surface_only) {
   };
   // thcm_forcing_integral_ (THCM.C:2704-2740): a GLOBAL surface integral; every rank holds the global mask, so it is
   // evaluated redundantly in the reference's summation order instead of through an allreduce
+  // Same operations and summation order as the reference; cos(y_j) and the profiles are evaluated once per latitude
+  // instead of once per cell (a parameter change runs this twice per Newton step, Continuation.H:405-410).
+  std::vector<double> cosy(m + 2, 0.0);
+  for (int j = 1; j <= m; j++) cosy[j] = std::cos(y[j]);
   auto qint = [&](const std::vector<double>& field) {
     double lf = 0.0, ls = 0.0;
     for (int j = 1; j <= m; j++) for (int i = 1; i <= n; i++) {
-      lf = field[(size_t)(i - 1) + (size_t)n * (j - 1)] * std::cos(y[j]) * (1 - lm(i, j, l)) + lf;
-      ls = std::cos(y[j]) * (1 - lm(i, j, l)) + ls;
+      const int ocean = 1 - lm(i, j, l);
+      lf = field[(size_t)(i - 1) + (size_t)n * (j - 1)] * cosy[j] * ocean + lf;
+      ls = cosy[j] * ocean + ls;
     }
     return lf / ls;
   };
   const double sigma = par[P_COMB] * par[P_WIND] * par[P_AL_T];
-  for (int j = j1; j <= std::min(j2, m - 1); j++) for (int i = i1; i <= i2; i++) {
-    frc[row(i, j, l, UU)] = sigma * wfun(yv[j], 1);
-    frc[row(i, j, l, VV)] = sigma * wfun(yv[j], 2);
+  for (int j = j1; j <= std::min(j2, m - 1); j++) {
+    const double fu = sigma * wfun(yv[j], 1), fv = sigma * wfun(yv[j], 2);
+    for (int i = i1; i <= i2; i++) { frc[row(i, j, l, UU)] = fu; frc[row(i, j, l, VV)] = fv; }
   }
   std::vector<double> tatm((size_t)n * m, 0.0), emip((size_t)n * m, 0.0), zero2((size_t)n * m, 0.0);
   const double etabi = par[P_COMB] * par[P_TEMP] * (1 - TRES + TRES * par[P_BIOT]);
   double temcor = 0.0;
   if (cfg.coupled_T == 0) {
-    for (int j = 1; j <= m; j++) for (int i = 1; i <= n; i++) tatm[(size_t)(i - 1) + (size_t)n * (j - 1)] = temfun(y[j]);
+    for (int j = 1; j <= m; j++) { const double tj = temfun(y[j]); for (int i = 1; i <= n; i++) tatm[(size_t)(i - 1) + (size_t)n * (j - 1)] = tj; }
     if (TRES == 0) temcor = qint(tatm);
     for (int j = j1; j <= j2; j++) for (int i = i1; i <= i2; i++) frc[row(i, j, l, TT)] = etabi * (tatm[(size_t)(i - 1) + (size_t)n * (j - 1)] - temcor);
   }
@@ -504,7 +509,7 @@ void Host::build_forcing(bool surface_only) {
   // with the unset albe0 = 0; only meaningful once set_atmos_parameters exists, kept at 0 here.
   const double gamma = par[P_COMB] * par[P_SALT] * (1 - SRES + SRES * par[P_BIOT]);
   double salcor = 0.0, adapted_salcor = 0.0, spertcor = 0.0;
-  for (int j = 1; j <= m; j++) for (int i = 1; i <= n; i++) emip[(size_t)(i - 1) + (size_t)n * (j - 1)] = salfun(y[j]) * (1 - lm(i, j, l));
+  for (int j = 1; j <= m; j++) { const double sj = salfun(y[j]); for (int i = 1; i <= n; i++) emip[(size_t)(i - 1) + (size_t)n * (j - 1)] = sj * (1 - lm(i, j, l)); }
   if (SRES == 0) { salcor = qint(emip); adapted_salcor = qint(zero2); spertcor = qint(zero2); }
   for (int j = j1; j <= j2; j++) for (int i = i1; i <= i2; i++)
     frc[row(i, j, l, SS)] = gamma * (1 - par[P_HMTP]) * (emip[(size_t)(i - 1) + (size_t)n * (j - 1)] - salcor) +
