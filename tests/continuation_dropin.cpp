@@ -39,6 +39,21 @@ static void write_state(OceanB200& ocean, const std::string& path) {
 }
 
 int main(int argc, char** argv) {
+  if (argc > 4 && std::string(argv[1]) == "xml") { // xml <ocean_params.xml> <continuation_params.xml> <mask dir>: run_ocean.C:44-75
+    try {
+      auto make = [&](const thcm_b200_config& c, const std::vector<int>& mask) {
+        auto ocean = std::make_shared<OceanB200>(c, mask.data());
+        ocean->setSolverParameters(1e-10, 4000, 500, GMRES_B200_CGS2);
+        ocean->usePointBlockJacobi(true);
+        ocean->setVerbose(std::getenv("IEMIC_COMPAT_VERBOSE") != nullptr);
+        return ocean;
+      };
+      return run_ocean_from_files<Continuation<std::shared_ptr<OceanB200>>, thcm_b200_config>(argv[2], argv[3], argv[4], make) == 0 ? 0 : 1;
+    } catch (const std::exception& e) {
+      std::printf("continuation drop-in failed: %s\n", e.what());
+      return 1;
+    }
+  }
   if (argc > 2 && std::string(argv[1]) == "ocean") { // ocean <maskfile>: TEST(Ocean, Continuation), test_ocean.C:178-223
     try {
       const thcm_b200_config c = test_ocean_config<thcm_b200_config>();

@@ -212,6 +212,16 @@ static void write_state(OracleModel& m, const std::string& path) {
 }
 
 int main(int argc, char** argv) {
+  if (argc > 4 && std::string(argv[1]) == "xml") { // xml <ocean_params.xml> <continuation_params.xml> <mask dir> [mode]
+    try {
+      const std::string mode = argc > 5 ? argv[5] : "gmres";
+      auto make = [&](const thcm_oracle_config& c, const std::vector<int>& mask) { return std::make_shared<OracleModel>(c, mask.data(), mode); };
+      return run_ocean_from_files<Continuation<std::shared_ptr<OracleModel>>, thcm_oracle_config>(argv[2], argv[3], argv[4], make) == 0 ? 0 : 1;
+    } catch (const std::exception& e) {
+      std::printf("continuation on the oracle failed: %s\n", e.what());
+      return 1;
+    }
+  }
   if (argc > 1 && std::string(argv[1]) == "cases") { print_cases<thcm_oracle_config>(); return 0; } // for tests/test_params.py
   if (argc > 2 && std::string(argv[1]) == "ocean") { // ocean <maskfile> [mode]: TEST(Ocean, Continuation), test_ocean.C:178-223
     try {

@@ -51,9 +51,9 @@ def build_continuation_oracle():
     os.makedirs(os.path.dirname(ORACLE_EXE), exist_ok=True)
     if _fresh(ORACLE_EXE, os.path.join(ROOT, "tests", "continuation_oracle.cpp"), os.path.join(ROOT, "tests", "continuation_cases.H"),
               os.path.join(ROOT, "tests", "compat"), os.path.join(ROOT, "iemic_b200", "csrc", "gmres_guard.h"),
-              os.path.join(ROOT, "oracle", "thcm_oracle.h"), REF_CONT):
+              os.path.join(ROOT, "oracle", "thcm_oracle.h"), os.path.join(ROOT, "iemic_b200", "host"), REF_CONT):
         return ORACLE_EXE
-    cmd = ["g++", "-std=c++17", "-O2", "-I", os.path.join(ROOT, "tests", "compat"), "-I", REF_CONT,
+    cmd = ["g++", "-std=c++17", "-O2", "-I", os.path.join(ROOT, "tests", "compat"), "-I", REF_CONT, "-I", os.path.join(ROOT, "include"),
            os.path.join(ROOT, "tests", "continuation_oracle.cpp"), "-L", os.path.join(ROOT, "oracle"), "-lthcm_oracle",
            "-Wl,-rpath,$ORIGIN/../../oracle", "-o", ORACLE_EXE]
     r = subprocess.run(cmd, capture_output=True, text=True)

@@ -87,3 +87,33 @@ def test_test_ocean_continuation_with_the_reference_continuation(tmp_path):
         assert res[mode][1] > 0.0 and res[mode][2] > 0.0
     assert abs(res["gmres"][1] - res["cgs2"][1]) <= 1e-7 * abs(res["gmres"][1])
     assert abs(res["gmres"][2] - res["cgs2"][2]) <= 1e-7 * res["gmres"][2]
+
+
+REF = "/root/reference"
+
+
+@pytest.mark.skipif(not os.path.isdir(os.path.join(REF, "test", "2dmoc")), reason="reference checkout not present")
+def test_run_ocean_flow_from_the_reference_files(tmp_path):
+    """The flow of the reference's executable src/main/run_ocean.C:44-75 (without the eigen-solver): ocean_params.xml,
+    continuation_params.xml and the land-mask file read unchanged (iemic_b200/host/ParameterListXML.H), then the reference's
+    Continuation::run().  Same results as the hard-coded set-ups of the other tests, to the last printed digit."""
+    import re
+    exe = _exe()
+    masks = os.path.join(REF, "data", "mkmask")
+    r = subprocess.run([exe, "xml", os.path.join(REF, "test/2dmoc/ocean_params.xml"), os.path.join(REF, "test/2dmoc/continuation_params.xml"),
+                        masks, "lu"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:]
+    m = re.search(r"run_ocean: status 0, Combined Forcing = (\S+), \|\|x\|\| = (\S+),", r.stdout)
+    assert m, r.stdout[-2000:]
+    rc, out = _run(tmp_path, "lu", 1)
+    h = re.search(r"leg Combined Forcing -> 1: status 0, value (\S+), \|\|x\|\| = (\S+),", out)
+    assert rc == 0 and h, out[-2000:]
+    assert m.group(1) == h.group(1) and abs(float(m.group(2)) - float(h.group(2))) <= 1e-6 * float(h.group(2))
+    # test/ocean: 8x8x4 box with the land mask file of data/mkmask
+    r = subprocess.run([exe, "xml", os.path.join(REF, "test/ocean/ocean_params.xml"), os.path.join(REF, "test/ocean/continuation_params.xml"),
+                        masks, "gmres"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:]
+    m = re.search(r"run_ocean: status 0, Combined Forcing = (\S+), \|\|x\|\| = (\S+),", r.stdout)
+    o = subprocess.run([exe, "ocean", _natl8_mask_file(tmp_path), "gmres"], capture_output=True, text=True, timeout=600)
+    st, par, nx, nf = parse_test_ocean(o.stdout)
+    assert st == 0 and float(m.group(1)) == par and float(m.group(2)) == nx
