@@ -37,7 +37,7 @@ class HostVector { // the Epetra_Vector subset Continuation.H uses
 class OracleModel {
  public:
   typedef std::shared_ptr<HostVector> VectorPtr;
-  OracleModel(const thcm_oracle_config& c, const int* mask, const std::string& mode) : lu_(mode == "lu"), cgs2_(mode == "cgs2") {
+  OracleModel(const thcm_oracle_config& c, const int* mask, const std::string& mode) : lu_(mode == "lu" || mode == "guardcheck"), cgs2_(mode == "cgs2") {
     o_ = thcm_oracle_create(&c, mask);
     if (!o_) throw std::runtime_error("thcm_oracle_create failed");
     n_ = (size_t)thcm_oracle_ndim(o_);
@@ -57,7 +57,8 @@ class OracleModel {
     if (lu_) { solve_lu(b->v); return; }
     std::vector<double> binv = block_inverses();
     static const double tol = std::getenv("ORACLE_GMRES_TOL") ? std::atof(std::getenv("ORACLE_GMRES_TOL")) : 1e-10;
-    if (cgs2_) { solve_cgs2(b->v, binv, tol); return; }
+    static const bool guard = !(std::getenv("ORACLE_GUARD") && std::getenv("ORACLE_GUARD")[0] == '0');
+    if (cgs2_) { solve_cgs2(b->v, binv, tol, guard); return; }
     std::vector<double> hist(20000, 0.0);
     int iters = 0;
     const int m = (int)std::min<size_t>(n_, 500);
@@ -137,8 +138,7 @@ class OracleModel {
     sol_->v = x;
   }
   // the product's driver (iemic_b200/csrc/capi.cu, gmres_b200_solve) on the host: same order of operations, plain loops
-  void solve_cgs2(const std::vector<double>& b, const std::vector<double>& binv, double tol) {
-    static const bool guard = !(std::getenv("ORACLE_GUARD") && std::getenv("ORACLE_GUARD")[0] == '0');
+  int solve_cgs2(const std::vector<double>& b, const std::vector<double>& binv, double tol, bool guard) {
     const size_t n = n_;
     const int m = (int)std::min<size_t>(n, 500), maxit = 4000, ldh = m + 1;
     std::vector<double>& x = sol_->v;
@@ -191,7 +191,23 @@ class OracleModel {
       if (conv) rc = 0;
     }
     if (std::getenv("IEMIC_COMPAT_VERBOSE")) std::printf("OracleModel: CGS2 GMRES rc = %d, i = %d\n", rc, iter);
+    return rc;
   }
+ public:
+  // one linear solve at the rounding floor of F, with and without the accuracy guard: J of the current state (singular:
+  // constant-pressure null vector), b = F(state) (noise with a component outside the range of J)
+  void guardcheck() {
+    computeRHS(); computeJacobian();
+    const std::vector<double> b = rhs_->v, binv = block_inverses();
+    double nb = 0; for (double v : b) nb += v * v; nb = std::sqrt(nb);
+    for (int guard = 1; guard >= 0; guard--) {
+      std::fill(sol_->v.begin(), sol_->v.end(), 0.0);
+      const int rc = solve_cgs2(b, binv, 1e-10, guard != 0);
+      double nx = 0; for (double v : sol_->v) nx += v * v; nx = std::sqrt(nx);
+      std::printf("guardcheck: guard %d, rc %d, ||b|| = %.3e, ||x|| = %.3e\n", guard, rc, nb, nx);
+    }
+  }
+ private:
   thcm_oracle* o_ = nullptr;
   size_t n_ = 0;
   bool lu_, cgs2_;
@@ -277,6 +293,7 @@ int main(int argc, char** argv) {
       if (st != 0 || std::fabs(ocean->getPar(g.par) - g.dest) > 1e-5) return 1;
       if (g.save) write_state(*ocean, outdir + "/" + g.save);
     }
+    if (mode == "guardcheck") ocean->guardcheck();
     std::printf("continuation on the oracle ok\n");
   } catch (const std::exception& e) {
     std::printf("continuation on the oracle failed: %s\n", e.what());

@@ -48,14 +48,27 @@ def test_intt_2dmoc_chain_with_the_reference_continuation(tmp_path):
 
 
 def test_product_gmres_driver_needs_the_accuracy_guard(tmp_path):
+    import re
+    # the chain's first two legs with the walk-through of the product's GMRES driver (guard on)
     rc, out = _run(tmp_path, "cgs2", 2)
     assert rc == 0, out[-2000:]
     legs = [ln for ln in out.splitlines() if ln.startswith("leg ")]
     assert len(legs) == 2 and all("status 0" in ln for ln in legs), out[-2000:]
-    rc0, out0 = _run(tmp_path, "cgs2", 2, env={"ORACLE_GUARD": "0"})
-    # which solve goes wrong first depends on the last bits of the set-up (leg 1 or leg 2); one of them does
-    assert rc0 != 0 and ": status 1" in out0, out0[-2000:]
-
+    # one solve at the rounding floor of F at the end of leg 1, guard on and off.  Off: the recurrence residual "converges"
+    # (rc 0) to an update that is a multiple of the null vector, nine orders of magnitude larger than the guarded one.  (With
+    # ORACLE_GUARD=0 the chain itself aborts at the minimum step size in leg 1 or 2, depending on the last bits of the set-up.)
+    rc, out = _run(tmp_path, "guardcheck", 1)
+    assert rc == 0, out[-2000:]
+    res = {int(g): (int(r), float(nb), float(nx)) for g, r, nb, nx in
+           re.findall(r"guardcheck: guard (\d), rc (\d+), \|\|b\|\| = (\S+), \|\|x\|\| = (\S+)", out)}
+    assert set(res) == {0, 1}, out[-2000:]
+    (rc_on, nb, x_on), (rc_off, _, x_off) = res[1], res[0]
+    assert nb < 1e-10                      # F at its rounding floor
+    # b is inconsistent beyond the tolerance, so no solver can honestly return 0 here.  Guard on: "accuracy limit" (2; 1 if the
+    # iteration merely stagnated) with an update of the order of ||b||.  Guard off: never a small update reported as converged
+    # (on this machine: rc 0 with ||x|| = 0.19).
+    assert rc_on in (1, 2) and x_on <= 1e4 * nb
+    assert not (rc_off == 0 and x_off <= 1e4 * nb)
 
 def _natl8_mask_file(tmp_path):
     import cases
