@@ -40,7 +40,9 @@ def build_continuation_dropin():
     return EXE
 
 
-ORACLE_EXE = os.path.join(ROOT, "tests", "_build", "continuation_oracle")
+# reference code compiled here (Continuation.H / GMRESSolver.H, read in place) that does not touch the product: oracle/_ref/
+# (git-ignored, shipped to the GPU box like the other built files)
+ORACLE_EXE = os.path.join(ROOT, "oracle", "_ref", "continuation_oracle")
 
 
 def build_continuation_oracle():
@@ -55,14 +57,14 @@ def build_continuation_oracle():
         return ORACLE_EXE
     cmd = ["g++", "-std=c++17", "-O2", "-I", os.path.join(ROOT, "tests", "compat"), "-I", REF_CONT, "-I", os.path.join(ROOT, "include"),
            os.path.join(ROOT, "tests", "continuation_oracle.cpp"), "-L", os.path.join(ROOT, "oracle"), "-lthcm_oracle",
-           "-Wl,-rpath,$ORIGIN/../../oracle", "-o", ORACLE_EXE]
+           "-Wl,-rpath,$ORIGIN/..", "-o", ORACLE_EXE]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("continuation_oracle.cpp does not compile against the reference's Continuation.H:\n" + r.stderr[-4000:])
     return ORACLE_EXE
 
 
-GMRES_REF_EXE = os.path.join(ROOT, "tests", "_build", "gmres_reference")
+GMRES_REF_EXE = os.path.join(ROOT, "oracle", "_ref", "gmres_reference")
 
 
 def build_gmres_reference():

@@ -22,7 +22,7 @@ from iemic_b200 import grids
 def _exe():
     exe = hostcpp_build.build_continuation_oracle()
     if exe is None:
-        pytest.skip("reference tree absent and no prebuilt tests/_build/continuation_oracle")
+        pytest.skip("reference tree absent and no prebuilt oracle/_ref/continuation_oracle")
     return exe
 
 

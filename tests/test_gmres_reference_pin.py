@@ -16,7 +16,7 @@ import oracle_lib as ol
 def _reference(tmp_path, rp, col, val, b, m, maxit, tol, binv):
     exe = hostcpp_build.build_gmres_reference()
     if exe is None:
-        pytest.skip("reference tree absent and no prebuilt tests/_build/gmres_reference")
+        pytest.skip("reference tree absent and no prebuilt oracle/_ref/gmres_reference")
     n = rp.size - 1
     prob, out = tmp_path / "problem.bin", tmp_path / "out.bin"
     with open(prob, "wb") as f:

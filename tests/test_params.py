@@ -64,7 +64,7 @@ def _harness_cases():
     import hostcpp_build
     exe = hostcpp_build.build_continuation_oracle()
     if exe is None:
-        pytest.skip("tests/_build/continuation_oracle not built")
+        pytest.skip("oracle/_ref/continuation_oracle not built")
     out = subprocess.run([exe, "cases"], capture_output=True, text=True, check=True).stdout
     res, cur = {}, None
     for line in out.splitlines():
