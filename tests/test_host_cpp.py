@@ -12,6 +12,8 @@ INC = ["-I", os.path.join(ROOT, "include"), "-I", HOST]
 
 def test_host_mirror_compiles():
     subprocess.run(["g++", "-std=c++17", "-Wall", "-fsyntax-only"] + INC + [os.path.join(HOST, "selftest.cpp")], check=True)
+    # the reference builds with -std=c++1y / c++14 (src/CMakeLists.txt:24,30): the mirror, its XML front end included, must too
+    subprocess.run(["g++", "-std=c++14", "-Wall", "-fsyntax-only"] + INC + [os.path.join(HOST, "selftest.cpp")], check=True)
 
 
 @pytest.mark.skipif(not os.path.isdir(REF_GMRES), reason="reference tree not present (GPU box)")

@@ -12,11 +12,12 @@ using namespace iemic_b200;
 static void show(const ParameterList& p, const std::string& prefix) {
   for (auto& kv : p.values()) {
     std::printf("%s%s = ", prefix.c_str(), kv.first.c_str());
-    if (auto b = std::get_if<bool>(&kv.second)) std::printf("bool %d\n", (int)*b);
-    else if (auto i = std::get_if<int>(&kv.second)) std::printf("int %d\n", *i);
-    else if (auto d = std::get_if<double>(&kv.second)) std::printf("double %.17g\n", *d);
-    else if (auto c = std::get_if<char>(&kv.second)) std::printf("char %c\n", *c);
-    else std::printf("string %s\n", std::get<std::string>(kv.second).c_str());
+    const ParameterValue& v = kv.second;
+    if (v.is<bool>()) std::printf("bool %d\n", (int)v.as<bool>());
+    else if (v.is<int>()) std::printf("int %d\n", v.as<int>());
+    else if (v.is<double>()) std::printf("double %.17g\n", v.as<double>());
+    else if (v.is<char>()) std::printf("char %c\n", v.as<char>());
+    else std::printf("string %s\n", v.as<std::string>().c_str());
   }
   for (auto& kv : p.sublists()) show(kv.second, prefix + kv.first + "/");
 }
