@@ -70,7 +70,7 @@ struct thcm_b200 {
   long long launches = 0;
   bool timing = false;
   std::vector<TimedEv> evs;
-  double t_total[4] = {0, 0, 0, 0}; long long t_count[4] = {0, 0, 0, 0};
+  double t_total[6] = {0, 0, 0, 0, 0, 0}; long long t_count[6] = {0, 0, 0, 0, 0, 0}; // 0 rhs, 1 jac, 2 spmv, 3 orthogonalisation, 4 fused jac+rhs
   long long nrows() const { return (long long)host->nrows_local(); }
   long long nvec() const { return (long long)host->nvec_local(); }
 };
@@ -432,6 +432,17 @@ int jac_part(thcm_b200* h, const double* d_x, int part, int kz0 = 0, int nkz = 0
   }
   return check_launch(h, "jac_kernel");
 }
+// Jacobian and residual of one state in ONE kernel: the residual operator is built from the tile the Jacobian pass staged.
+int asm_part(thcm_b200* h, const double* d_x, double* d_F, int part, int kz0 = 0, int nkz = 0) {
+  AsmArgs a = asm_args(h, d_x);
+  a.F = d_F; a.part = part; a.kz0 = kz0; a.nkz = nkz;
+  {
+    Timed t(h, 4);
+    launch_asm(a, h->stream);
+    h->launches++;
+  }
+  return check_launch(h, "asm_kernel");
+}
 } // namespace
 
 extern "C" {
@@ -457,10 +468,18 @@ int thcm_b200_exchange_mode(thcm_b200_t* h) {
 int thcm_b200_assemble(thcm_b200_t* h, double* d_x, double* d_F, int jacobian) {
   CHECK_H(h);
   if (int rc = refresh_device(h)) return rc;
+  static const bool fused = !(getenv("IEMIC_ASM_FUSED") && getenv("IEMIC_ASM_FUSED")[0] == '0');
   if (!h->dist) {
+    if (d_F && jacobian && fused) { if (int rc = asm_part(h, d_x, d_F, 0)) return rc; return rhs_epilogue(h, d_x, d_F); }
     if (d_F) { if (int rc = rhs_part(h, d_x, d_F, 0)) return rc; if (int rc = rhs_epilogue(h, d_x, d_F)) return rc; }
     if (jacobian) if (int rc = jac_part(h, d_x, 0)) return rc;
     return 0;
+  }
+  if (d_F && jacobian && fused && !getenv("IEMIC_ASM_PLAN")) { // halo exchange, then the fused kernel
+    h->launches += dist_halo_launches(h->dist);
+    if (dist_halo_exchange(h->dist, d_x, h->stream) != 0) return fail(IEMIC_B200_ENCCL, dist_last_error());
+    if (int rc = asm_part(h, d_x, d_F, 0)) return rc;
+    return rhs_epilogue(h, d_x, d_F);
   }
   // Plans (IEMIC_ASM_PLAN, default 1; measured on 8 B200 at 1 degree: 0.141 / 0.128 / 0.137 ms per assembly):
   //   0  halo exchange, Jacobian, residual, one after the other on the handle's stream
@@ -593,9 +612,10 @@ int thcm_b200_assemble_host(thcm_b200_t* h, const double* x, double* F, int jaco
   auto work = [&](int s) -> int {                                       // kernels of slab s; needs the levels of slab s+1 on board
     const int kz0 = s * per, nkz = std::min(per, ntz - kz0);
     if (nkz <= 0) return 0;
-    if (jacobian) if (int rc = jac_part(h, h->d_xs, 0, kz0, nkz)) return rc;
+    if (jacobian && F) { if (int rc = asm_part(h, h->d_xs, h->d_ys, 0, kz0, nkz)) return rc; }
+    else if (jacobian) { if (int rc = jac_part(h, h->d_xs, 0, kz0, nkz)) return rc; }
     if (F) {
-      if (int rc = rhs_part(h, h->d_xs, h->d_ys, 0, nullptr, kz0, nkz)) return rc;
+      if (!jacobian) if (int rc = rhs_part(h, h->d_xs, h->d_ys, 0, nullptr, kz0, nkz)) return rc;
       const bool last = kz0 + nkz >= ntz;
       if (last) if (int rc = rhs_epilogue(h, h->d_xs, h->d_ys)) return rc; // integral condition / pressure rows live in the top level
       CU(cudaEventRecord(h->ev_slab[nslab + s], h->stream));
@@ -946,12 +966,12 @@ int thcm_b200_timing_enable(thcm_b200_t* h, int on) { CHECK_H(h); if (!on) flush
 int thcm_b200_timing_reset(thcm_b200_t* h) {
   CHECK_H(h);
   flush_timing(h);
-  for (int q = 0; q < 4; q++) { h->t_total[q] = 0; h->t_count[q] = 0; }
+  for (int q = 0; q < 6; q++) { h->t_total[q] = 0; h->t_count[q] = 0; }
   return 0;
 }
 int thcm_b200_timing_get(thcm_b200_t* h, int which, double* total_ms, int64_t* count) {
   CHECK_H(h);
-  if (which < 0 || which > 3) return fail(IEMIC_B200_EINVAL, "which must be 0..3");
+  if (which < 0 || which > 5) return fail(IEMIC_B200_EINVAL, "which must be 0..5");
   if (int rc = flush_timing(h)) return rc;
   if (total_ms) *total_ms = h->t_total[which];
   if (count) *count = h->t_count[which];

@@ -26,8 +26,10 @@ struct AsmArgs {
 int asm_tile_levels();    // model levels per tile layer
 void launch_jac(const AsmArgs& a, cudaStream_t st);
 void launch_rhs(const AsmArgs& a, cudaStream_t st);
+void launch_asm(const AsmArgs& a, cudaStream_t st); // Jacobian and residual of the same state in one pass over the staged tiles
 int jac_smem_bytes();
 int rhs_smem_bytes();
+int asm_smem_bytes();
 
 // integral condition (THCM.C:1006-1018): F[row] = sign * (sum_c coef[c]*x[6c+5] - corr); partial sums per block,
 // finished (after the optional allreduce) by intcond_finish.

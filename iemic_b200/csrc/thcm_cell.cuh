@@ -19,12 +19,25 @@ template <int A> THCM_HD void save_centre(Row<A>& r, double* dst) {
   if constexpr (Row<A>::template has<5, SS>()) dst[5] = r.template at<5, SS>();
 }
 
-// Jacobian row A of cell c -> `out` (first stored value of the row in the static CSR), returns diag(B) entry.
-// The integral-condition row is left untouched (its dense values are static, written by jac_intcond_row).
-template <int A, class F, class Out>
-THCM_HD double jac_row(const Scalars& S, const Tables& T, const Cell& c, const F& f, const SpecialRows& sp, int row, Out out,
-                       const MixFD* fd = nullptr) {
-  Row<A> r;
+// diag(B) entry of row A: fillcolB (assemble.F90:18-54) times "Mass" = 1 (THCM.C:1150-1153); the rows the C++ glue overwrites
+// (integral condition THCM.C:2137-2139, fixed pressure points THCM.C:2201-2238) carry 0.
+template <int A> THCM_HD double diagb_entry(const Scalars& S, uint64_t sig, const SpecialRows& sp, int row) {
+  double b = 0.0;
+  if (!sbit(sig, SIG_NOTOCEAN)) {
+    if (A == UU) b = sbit(sig, SIG_BU) ? -S.epsr : 0.0;
+    if (A == VV) b = sbit(sig, SIG_BV) ? -S.epsr : 0.0;
+    if (A == TT || A == SS) b = -1.0;
+  }
+  if (row == sp.rowintcon) b = 0.0;
+  if (A == PP && (row == sp.rowPfix1 || row == sp.rowPfix2)) b = 0.0;
+  return b;
+}
+
+// Jacobian row A of cell c, built in registers (static pattern order).  Returns false when the row must not be stored:
+// the integral-condition row is left untouched (its dense values are static, written once by the host).
+template <int A, class F>
+THCM_HD bool jac_row_build(Row<A>& r, const Scalars& S, const Tables& T, const Cell& c, const F& f, const SpecialRows& sp, int row,
+                           const MixFD* fd = nullptr) {
   if (sbit(c.sig, SIG_NOTOCEAN)) { // `boundaries` turns every row of a non-ocean cell into an identity row (boundary.F90:383-391)
     r.clear();
     r.template at<5, A>() = 1.0;
@@ -33,27 +46,27 @@ THCM_HD double jac_row(const Scalars& S, const Tables& T, const Cell& c, const F
     if ((uint32_t)c.sig != 0u) apply_boundaries<A>(r, c.sig); // bits 0..31: a land neighbour somewhere in the stencil
     filter_row<A>(r);
   }
-  // fillcolB (assemble.F90:18-54) times "Mass" = 1 (THCM.C:1150-1153)
-  double b = 0.0;
-  if (!sbit(c.sig, SIG_NOTOCEAN)) {
-    if (A == UU) b = sbit(c.sig, SIG_BU) ? -S.epsr : 0.0;
-    if (A == VV) b = sbit(c.sig, SIG_BV) ? -S.epsr : 0.0;
-    if (A == TT || A == SS) b = -1.0;
-  }
   if (row == sp.rowintcon) {                              // intcond_S, THCM.C:2137-2139
     if constexpr (A == SS) { if (sp.side) save_centre<A>(r, sp.side); } // the integral row replaces an S row
-    return 0.0;
+    return false;
   }
   if constexpr (A == PP) {
     if (row == sp.rowPfix1 || row == sp.rowPfix2) { // fixPressurePoints, THCM.C:2201-2238
       if (sp.side) save_centre<A>(r, sp.side + (row == sp.rowPfix1 ? 6 : 12));
       r.clear();
       r.template at<5, PP>() = 1.0;
-      b = 0.0;
     }
   }
-  emit_row<A>(r, S, c, out);
-  return b;
+  return true;
+}
+
+// Jacobian row A of cell c -> `out` (first stored value of the row in the static CSR), returns diag(B) entry.
+template <int A, class F, class Out>
+THCM_HD double jac_row(const Scalars& S, const Tables& T, const Cell& c, const F& f, const SpecialRows& sp, int row, Out out,
+                       const MixFD* fd = nullptr) {
+  Row<A> r;
+  if (jac_row_build<A, F>(r, S, T, c, f, sp, row, fd)) emit_row<A>(r, S, c, out);
+  return diagb_entry<A>(S, c.sig, sp, row);
 }
 
 // Residual row A of cell c: F = -( (-Au - mix + Frc) * (1-landm) )   (usrc.F90:559-574, THCM.C:1003)

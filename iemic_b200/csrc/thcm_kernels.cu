@@ -1,17 +1,24 @@
 // thcm_kernels.cu -- fused THCM residual and Jacobian assembly for sm_100a.
 //
 // Replaces the Fortran pipeline An=Al; nlin_*; vmix_*; boundaries; assemble; matAvec of the reference
-// (src/ocean/usrc.F90:432-586) by two kernels that never materialise the stencil tensor:
+// (src/ocean/usrc.F90:432-586) by kernels that never materialise the stencil tensor:
 //
-//   jac_kernel : one thread block per 32x4x2 tile of cells.  The ghosted fields u,v,w,T,S that usol produces
+//   asm_kernel<JAC,RHS> : one thread block per 32x4x2 tile of cells.  The ghosted fields u,v,w,T,S that usol produces
 //                (usrc.F90:997-1104) are staged once per tile in shared memory (radius-1 halo); each warp then owns a
-//                line of 32 cells in i and walks the six rows U,V,W,P,T,S.  A row's <=24 entries are built in
-//                registers (thcm_rows.cuh), compacted into a per-warp shared-memory scratch and copied to the static
-//                CSR with fully coalesced 8-byte stores: the six rows of a cell, and the cells of a line, are
-//                contiguous in the CSR value array, so a warp writes one contiguous ~26 KB run.
-//                HBM traffic per cell: 48 B state + 8 B signature + 28 B row offsets in, 832 B values + 48 B diag(B) out.
-//   rhs_kernel : same tiling; additionally stages the raw (un-zeroed) u,v,w,p so that the assembled row can be
-//                contracted with the state in the reference's storage order (matAvec), then F = A(x)x + mix - Frc.
+//                line of 32 cells in i and walks the six rows U,V,W,P,T,S.
+//                JAC: a row's <=24 entries are built in registers (thcm_rows.cuh) and written, in their final CSR
+//                order, into the lane's own 208-byte slot of a per-warp shared-memory scratch.  The six rows of a cell
+//                are contiguous in the static CSR, so every lane hands its piece (U 192 B, V 176 B, W+P 144 B, T 160 B,
+//                S 160 B) to the TMA engine with one cp.async.bulk.global.shared::cta: no transposition, no per-element
+//                store instructions.  A land cell is one 832-byte bulk copy from a constant block, and a tile of land
+//                cells does not stage anything.  Lines whose rows are clipped by the domain edge (or whose first value
+//                is not 16-byte aligned) keep the lane-transposed copy-out with ordinary stores.
+//                RHS: the residual operator A_rhs(x) (nlin_rhs, a different operator than the Jacobian,
+//                usrc.F90:775-870) is built from the SAME staged tile right after the Jacobian row, contracted with the
+//                raw state in the reference's storage order (matAvec), and F = A(x)x + mix - Frc leaves through 16-byte
+//                stores.  HBM traffic per cell (fused): 48 B state + 8 B signature + 48 B forcing in, 832 B values +
+//                48 B diag(B) + 48 B residual out.
+//   <true,false> is the Jacobian alone, <false,true> the residual alone (line searches, computeDFDPar).
 //
 // Compiled with -fmad=false: the reference's Fortran is built without FMA contraction for baseline x86-64, and
 // keeping every product and sum separately rounded makes these kernels agree with the CPU oracle bit for bit
@@ -28,12 +35,19 @@ namespace {
 #ifndef JAC_TJ
 #define JAC_TJ 4
 #endif
+#ifndef ASM_BULK
+#define ASM_BULK 1
+#endif
 constexpr int TI = 32, TJ = JAC_TJ, TK = JAC_TK;
 constexpr int SX = TI + 2, SY = TJ + 2, SZ = TK + 2;
 constexpr int TCELLS = SX * SY * SZ; // 816 staged cells per tile
 constexpr int NWARP = TJ * TK;       // one warp per line of the tile
 constexpr int NTHREADS = NWARP * 32;
-constexpr int STRIDE = 25;           // scratch doubles per lane: odd, so 8-byte accesses are bank-conflict free
+constexpr int STRIDE = 26;           // scratch doubles per lane: 208 B, so every lane's slot is 16-byte aligned (bulk copies; 16-byte
+                                     // shared stores free of bank conflicts: 52 words per lane -> 8 lanes cover the 32 banks).
+                                     // A smaller even stride works too (emit_slot hands back what does not fit), as long as the
+                                     // ordinary-store path below finds room for a whole row per lane.
+static_assert(STRIDE >= 24 && STRIDE % 2 == 0, "a U row has 24 entries; slots must stay 16-byte aligned");
 constexpr unsigned FULL = 0xffffffffu;
 #ifndef JAC_MINB
 #define JAC_MINB 2
@@ -64,26 +78,15 @@ struct TileRaw { // accessor concept X: raw neighbour state
   }
 };
 
-// Copy the compacted rows of 32 cells from the warp scratch (lane-major, STRIDE apart) to the CSR value array.
-// Consecutive lanes write consecutive doubles wherever consecutive rows are contiguous in the CSR.
-template <int NE>
-__device__ __noinline__ void warp_copy_out(double* __restrict__ val, const double* scr, int base, int len, int lane) { // rare: kept out of the hot path's instruction footprint
-#pragma unroll
-  for (int it = 0; it < NE; it++) {
-    const int t = it * 32 + lane;
-    const int cell = t / NE, q = t - cell * NE;
-    const int b = __shfl_sync(FULL, base, cell);
-    const int ln = __shfl_sync(FULL, len, cell);
-#ifdef JAC_NO_STORE
-    if (q < ln && scr[cell * STRIDE + q] == 1.2345e300) __stcs(val + (size_t)b + q, 0.0);
-#else
-    if (q < ln) __stcs(val + (size_t)b + q, scr[cell * STRIDE + q]);
-#endif
-  }
+// ---- TMA bulk copies shared -> global (cp.async.bulk, SASS UBLKCP): per-thread bulk groups ----
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void bulk_s2g(double* gdst, const double* ssrc, unsigned bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"((unsigned)__cvta_generic_to_shared(ssrc)), "r"(bytes)
+               : "memory");
 }
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); } // sources may be rewritten
 
-// Fast flavour for a warp whose 32 cells all carry complete rows (no domain edge, no dense row): the cell blocks are
-// CELL_NNZ apart, so addresses follow from the lane-0 offset alone -- no shuffles, no predicates.
 constexpr int CELL_NNZ = RowDef<UU>::NE + RowDef<VV>::NE + RowDef<WW>::NE + RowDef<PP>::NE + RowDef<TT>::NE + RowDef<SS>::NE; // 104
 template <int A> constexpr int row_offset() {
   int o = 0;
@@ -94,26 +97,25 @@ template <int A> constexpr int row_offset() {
   if (A > TT) o += RowDef<TT>::NE;
   return o;
 }
-// Lanes 0..NE-1 move one cell's row per step: both addresses are "register + compile-time immediate", i.e. one LDS and
-// one STG per cell and no index arithmetic at all.  Each store covers NE*8 contiguous bytes (56..192 B).
-template <int NE, int OFF>
-__device__ __forceinline__ void warp_copy_out_full(double* __restrict__ val, const double* scr, int lane) {
-  if (lane < NE) {
-    const double* src = scr + lane;
-    double* dst = val + OFF + lane;
+template <int A> constexpr int centre_pos() { return row_offset<A>() + find_ent<A>(5, A); } // the diagonal entry inside a cell's 104 values
+template <int A, int SIDE> constexpr int centre_seam() { return row_offset<A>() + seam_pos<A>(find_ent<A>(5, A), SIDE); } // same, cell on the periodic seam
+
+// ---- copy-out with ordinary stores, for the lines the bulk path does not take ----
+// Copy the compacted rows of 32 cells from the warp scratch (lane-major, STRIDE apart) to the CSR value array.
+// Consecutive lanes write consecutive doubles wherever consecutive rows are contiguous in the CSR.
+template <int NE>
+__device__ __noinline__ void warp_copy_out(double* __restrict__ val, const double* scr, int base, int len, int lane) { // rare: kept out of the hot path's instruction footprint
 #pragma unroll
-    for (int cell = 0; cell < 32; cell++) {
-#ifdef JAC_NO_STORE
-      if (src[cell * STRIDE] == 1.2345e300) __stcs(dst + cell * CELL_NNZ, 0.0);
-#else
-      __stcs(dst + cell * CELL_NNZ, src[cell * STRIDE]);
-#endif
-    }
+  for (int it = 0; it < NE; it++) {
+    const int t = it * 32 + lane;
+    const int cell = t / NE, q = t - cell * NE;
+    const int b = __shfl_sync(FULL, base, cell);
+    const int ln = __shfl_sync(FULL, len, cell);
+    if (q < ln) __stcs(val + (size_t)b + q, scr[cell * STRIDE + q]);
   }
 }
-
-// Same idea with run-time strides, for lines whose cells all have the SAME (clipped) row lengths: domain edges in j and
-// k, partially filled last tile in i.  `cs` = values per cell, `off`/`len` = this row's offset and length inside a cell.
+// Lines whose active cells all have the SAME row lengths (complete cells at an odd offset, domain edges in j and k):
+// lanes 0..len-1 move one cell's row per step.  `cs` = values per cell, `off`/`len` = this row's offset and length inside a cell.
 __device__ __noinline__ void warp_copy_out_uniform(double* __restrict__ val, const double* scr, int lane, int nact, int cs, int off, int len) {
   if (lane < len) {
     const double* src = scr + lane;
@@ -125,26 +127,75 @@ __device__ __noinline__ void warp_copy_out_uniform(double* __restrict__ val, con
     }
   }
 }
-enum { COPY_GENERAL = 0, COPY_UNIFORM = 1, COPY_FULL = 2 };
+enum { COPY_GENERAL = 0, COPY_UNIFORM = 1, COPY_BULK = 2 };
 struct CopyPlan { int mode, b0, nact, cs; };
 
-template <int A>
-__device__ __forceinline__ double do_jac_row(const AsmArgs& a, const Cell& c, const TileFields& f, bool active, int row0,
-                                             const int (&rp)[7], double* scr, int lane, const CopyPlan& cp, const MixFD* fd = nullptr) {
-  double b = 0.0;
-  int len = 0;
-  if (active) {
-    b = jac_row<A>(a.S, a.T, c, f, a.sp, row0 + A - 1, scr + lane * STRIDE, fd);
-    len = (row0 + A - 1 == a.sp.rowintcon) ? 0 : rp[A] - rp[A - 1];
+// A complete row into the lane's scratch slot in final order (SIDE 0: static order, 1 / 2: cell on the periodic seam at
+// i = 1 / i = n, compile-time permutation); entries that do not fit the slot are returned in `tail`.
+template <int A, int SIDE, bool ALIGNED>
+__device__ __forceinline__ void emit_slot(const Row<A>& r, double* out, double (&tail)[2]) {
+  constexpr int NE = Row<A>::NE, NS = NE < STRIDE ? NE : STRIDE;
+  if constexpr (SIDE == 0) {
+    if constexpr (ALIGNED) {
+      double2* o2 = reinterpret_cast<double2*>(out);
+#pragma unroll
+      for (int q = 0; q + 1 < NS; q += 2) o2[q / 2] = make_double2(r.a[q], r.a[q + 1]);
+      if constexpr (NS & 1) out[NS - 1] = r.a[NS - 1];
+    } else {
+#pragma unroll
+      for (int q = 0; q < NS; q++) out[q] = r.a[q];
+    }
+    if constexpr (NE > STRIDE) { tail[0] = r.a[STRIDE]; tail[1] = r.a[STRIDE + 1]; }
+  } else {
+    static_for<0, NE>([&](auto q) {
+      constexpr int e = decltype(q)::value;
+      constexpr int pos = seam_pos<A>(e, SIDE - 1);
+      if constexpr (pos < STRIDE) out[pos] = r.a[e];
+      else tail[pos - STRIDE] = r.a[e];
+    });
   }
-  __syncwarp();
-  if (cp.mode == COPY_FULL) warp_copy_out_full<RowDef<A>::NE, row_offset<A>()>(a.val + (size_t)cp.b0, scr, lane);
-  else if (cp.mode == COPY_UNIFORM) {
-    const int off = __shfl_sync(FULL, rp[A - 1] - rp[0], 0), ln = __shfl_sync(FULL, rp[A] - rp[A - 1], 0);
-    warp_copy_out_uniform(a.val + (size_t)cp.b0, scr, lane, cp.nact, cp.cs, off, ln);
-  } else warp_copy_out<RowDef<A>::NE>(a.val, scr, rp[A - 1], len, lane);
-  __syncwarp();
-  return b;
+}
+
+// Jacobian row A of the line: registers -> scratch -> CSR.
+template <int A>
+__device__ __forceinline__ void jac_row_out(const AsmArgs& a, const Cell& c, const TileFields& f, bool active, int row0, double* scr, int lane,
+                                            const CopyPlan& cp, const MixFD* fd) {
+  Row<A> r;
+  bool store = false;
+  if (active) store = jac_row_build<A, TileFields>(r, a.S, a.T, c, f, a.sp, row0 + A - 1, fd);
+  double* mine = scr + lane * STRIDE;
+  if (cp.mode == COPY_BULK) {
+    // every lane owns its slot and its cell's values: no exchange between lanes, hence no warp synchronisation
+    constexpr int PRE = (A == PP) ? RowDef<WW>::NE : 0;        // the P row rides behind the W row (7 + 11 values = 144 B)
+    if (A != PP) bulk_wait_read();                             // the previous piece has left the slot
+    if (store) {
+      static_assert(RowDef<A>::NE <= STRIDE + 2 && PRE + RowDef<PP>::NE <= STRIDE, "piece does not fit the scratch slot");
+      double tail[2] = {0.0, 0.0};
+      if (!row_has_seam(a.S, c)) emit_slot<A, 0, (PRE % 2 == 0)>(r, mine + PRE, tail);
+      else if (c.i == 1) emit_slot<A, 1, false>(r, mine + PRE, tail);
+      else emit_slot<A, 2, false>(r, mine + PRE, tail);
+      if (A != WW) {
+        constexpr int OFF = (A == PP) ? row_offset<WW>() : row_offset<A>();
+        constexpr int NB = (PRE + RowDef<A>::NE) < STRIDE ? (PRE + RowDef<A>::NE) : STRIDE;
+        double* dst = a.val + (size_t)cp.b0 + (size_t)lane * CELL_NNZ + OFF;
+        fence_proxy_async();
+        bulk_s2g(dst, mine, NB * 8);
+        bulk_commit();
+        if constexpr (RowDef<A>::NE > STRIDE) __stcs(reinterpret_cast<double2*>(dst + STRIDE), make_double2(tail[0], tail[1])); // 16-byte aligned: even offset
+      }
+    }
+  } else {
+    // rare path: the row offsets are (re)loaded here instead of being kept in registers across the whole kernel
+    int p0 = 0, len = 0;
+    if (active) { p0 = __ldg(a.rowptr + row0 + A - 1); len = store ? __ldg(a.rowptr + row0 + A) - p0 : 0; }
+    if (store) emit_row<A>(r, a.S, c, mine);
+    __syncwarp();
+    if (cp.mode == COPY_UNIFORM) {
+      const int off = __shfl_sync(FULL, p0, 0) - cp.b0, ln = __shfl_sync(FULL, len, 0);
+      warp_copy_out_uniform(a.val + (size_t)cp.b0, scr, lane, cp.nact, cp.cs, off, ln);
+    } else warp_copy_out<RowDef<A>::NE>(a.val, scr, p0, len, lane);
+    __syncwarp();
+  }
 }
 
 // Fill the shared-memory tile.  (Issuing all of a thread's loads before consuming them -- stage_plan/stage_apply --
@@ -198,10 +249,60 @@ __device__ __forceinline__ void stage_tile_plain(const AsmArgs& a, double* sm, i
   }
 }
 
-__global__ void __launch_bounds__(NTHREADS, JAC_MINB) jac_kernel(const __grid_constant__ AsmArgs a) {
-  extern __shared__ double sm[];
+// Residual of a non-ocean cell: the row is the identity (boundary.F90:383-391), so Au = x(row) and there is no mixing
+// term; what rhs_row returns for it, without the row machinery.
+__device__ __forceinline__ double rhs_land(uint64_t sig, double xraw, double frc) {
+  const double Au = 1.0 * xraw + 0.0;
+  double B = -Au - 0.0 + frc - 0.0;
+  B = B * (sbit(sig, SIG_LANDVAL) ? 0.0 : 1.0);
+  return B * -1.0;
+}
+__device__ __forceinline__ void store6(double* dst, const double (&v)[6]) { // 48 B per cell: 16-byte aligned when the vector is
+  if (((size_t)dst & 15) == 0) {
+    double2* p = reinterpret_cast<double2*>(dst);
+    __stcs(p, make_double2(v[0], v[1])); __stcs(p + 1, make_double2(v[2], v[3])); __stcs(p + 2, make_double2(v[4], v[5]));
+  } else {
+#pragma unroll
+    for (int q = 0; q < 6; q++) __stcs(dst + q, v[q]);
+  }
+}
+__device__ __forceinline__ void load6(const double* src, double (&v)[6]) {
+  if (((size_t)src & 15) == 0) {
+    const double2* p = reinterpret_cast<const double2*>(src);
+    const double2 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
+    v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y; v[4] = c.x; v[5] = c.y;
+  } else {
+#pragma unroll
+    for (int q = 0; q < 6; q++) v[q] = __ldg(src + q);
+  }
+}
+// A land cell in one go: six identity rows (one 832-byte bulk copy from the constant block), diag(B) = 0, residual from the
+// cell's own state.
+template <bool JAC, bool RHS>
+__device__ __forceinline__ void land_cell(const AsmArgs& a, const Cell& c, int row0, int p0, const double* ident, const double (&xown)[6], const double (&frc)[6]) {
+  if (JAC) {
+    const int side = !row_has_seam(a.S, c) ? 0 : (c.i == 1 ? 1 : 2);
+    bulk_s2g(a.val + (size_t)p0, ident + side * CELL_NNZ, CELL_NNZ * 8);
+    bulk_commit();
+    const double z[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+    store6(a.diagB + row0, z);
+  }
+  if (RHS) {
+    double Fv[6];
+#pragma unroll
+    for (int q = 0; q < 6; q++) Fv[q] = rhs_land(c.sig, xown[q], frc[q]);
+    store6(a.F + row0, Fv);
+  }
+  if (JAC) bulk_wait_read();
+}
+
+template <bool JAC, bool RHS>
+__global__ void __launch_bounds__(NTHREADS, JAC_MINB) asm_kernel(const __grid_constant__ AsmArgs a) {
+  extern __shared__ __align__(16) double sm[];
+  constexpr int NF = RHS ? 9 : 5;                     // staged field arrays
+  constexpr int SCRW = JAC ? 32 * STRIDE : 0;         // scratch doubles per warp
   const Scalars& S = a.S;
-  const int bx = blockIdx.x % a.ntx, by = (blockIdx.x / a.ntx) % a.nty, bz = blockIdx.x / (a.ntx * a.nty) + a.kz0;
+  const int bx = blockIdx.x, by = blockIdx.y, bz = blockIdx.z + a.kz0;
   if (a.part) { // overlap with the halo exchange: rim tiles wait for it, the others do not (block-uniform exit)
     const bool rim = bx == 0 || bx == a.ntx - 1 || by == 0 || by == a.nty - 1;
     if (rim != (a.part == 2)) return;
@@ -212,146 +313,130 @@ __global__ void __launch_bounds__(NTHREADS, JAC_MINB) jac_kernel(const __grid_co
   const int i = gi0 + lane, j = gj0 + lj, k = gk0 + lk;
   const bool line = j < S.jo0 + S.mloc && k <= S.l; // warp-uniform
   const bool active = line && i < S.io0 + S.nloc;
-  // this thread's own cell: signature and row offsets are requested before the tile is staged so that their latency
-  // hides behind the staging loads
   const size_t cidx = active ? cell_index(S, i, j, k) : 0;
   Cell c; c.i = i; c.j = j; c.k = k; c.sig = active ? __ldg(a.sig + cidx) : 0ull;
   const int row0 = (int)(6 * cidx);
-  // Row offsets: a line whose 32 cells all carry complete rows (almost all lines) needs only the first offset of every cell --
-  // the cells are 104 values apart and the rows of a cell follow from the compile-time row lengths -- so one load per lane
-  // (plus the end of the last cell) replaces seven.  Anything else loads the remaining offsets after the tile is staged.
-  int rp[7];
-  rp[0] = active ? __ldg(a.rowptr + row0) : 0;
-  rp[6] = (active && lane == 31) ? __ldg(a.rowptr + row0 + 6) : 0;
+  // first and one-past-last value of the cell: a cell whose six rows are complete (all but domain-edge cells) has CELL_NNZ
+  // values and its rows follow from the compile-time row lengths
+  int p0 = 0, pe = 0;
+  if (JAC && active) { p0 = __ldg(a.rowptr + row0); pe = __ldg(a.rowptr + row0 + 6); }
+  const bool special = a.sp.rowintcon >= row0 && a.sp.rowintcon < row0 + 6;
+  const bool pfix = a.sp.rowPfix1 == row0 + 3 || a.sp.rowPfix2 == row0 + 3;
+  const bool bulk_cell = ASM_BULK && pe - p0 == CELL_NNZ && (p0 & 1) == 0 && !special && ((size_t)a.val & 15) == 0;
 
-  if (tile_is_plain(S, gi0, gj0, gk0)) stage_tile_plain<false>(a, sm, gi0, gj0, gk0);
-  else stage_tile<false>(a, sm, gi0, gj0, gk0);
+  // the 104 values of a land cell (six identity rows) in the three column orders a cell can have: static, periodic seam at
+  // i = 1 (west neighbours sort last), seam at i = n (east neighbours sort first)
+  double* ident = sm + NF * TCELLS + NWARP * SCRW;
+  if (JAC) {
+    for (int t = threadIdx.x; t < 3 * CELL_NNZ; t += NTHREADS) {
+      const int side = t / CELL_NNZ, q = t - side * CELL_NNZ;
+      bool one;
+      if (side == 0)
+        one = q == centre_pos<UU>() || q == centre_pos<VV>() || q == centre_pos<WW>() || q == centre_pos<PP>() || q == centre_pos<TT>() || q == centre_pos<SS>();
+      else if (side == 1)
+        one = q == centre_seam<UU, 0>() || q == centre_seam<VV, 0>() || q == centre_seam<WW, 0>() || q == centre_seam<PP, 0>() || q == centre_seam<TT, 0>() ||
+              q == centre_seam<SS, 0>();
+      else
+        one = q == centre_seam<UU, 1>() || q == centre_seam<VV, 1>() || q == centre_seam<WW, 1>() || q == centre_seam<PP, 1>() || q == centre_seam<TT, 1>() ||
+              q == centre_seam<SS, 1>();
+      ident[t] = one ? 1.0 : 0.0;
+    }
+    fence_proxy_async();
+  }
+
+  // A tile of land cells (a third of the 1-degree grid) needs no neighbour: nothing is staged.
+  const bool easy_land = !active || (sbit(c.sig, SIG_NOTOCEAN) && (!JAC || (bulk_cell && !pfix)));
+  if (__syncthreads_and(easy_land)) {
+    if (active) {
+      double xown[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0}, frc[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+      if (RHS) { load6(a.x + row0, xown); load6(a.frc + row0, frc); }
+      land_cell<JAC, RHS>(a, c, row0, p0, ident, xown, frc);
+    }
+    return;
+  }
+
+  if (tile_is_plain(S, gi0, gj0, gk0)) stage_tile_plain<RHS>(a, sm, gi0, gj0, gk0);
+  else stage_tile<RHS>(a, sm, gi0, gj0, gk0);
   __syncthreads();
   if (!line) return;
-  {
-    const int nxt = __shfl_down_sync(FULL, rp[0], 1);
-    if (lane < 31) rp[6] = nxt;                 // rows are contiguous: the next cell starts where this one ends
-    const bool special = a.sp.rowintcon >= row0 && a.sp.rowintcon < row0 + 6;
-    const bool full = __all_sync(FULL, active && rp[6] - rp[0] == CELL_NNZ && !special);
-    if (full) {
-      rp[1] = rp[0] + row_offset<VV>(); rp[2] = rp[0] + row_offset<WW>(); rp[3] = rp[0] + row_offset<PP>();
-      rp[4] = rp[0] + row_offset<TT>(); rp[5] = rp[0] + row_offset<SS>();
-    } else {
-#pragma unroll
-      for (int q = 1; q < 7; q++) rp[q] = active ? __ldg(a.rowptr + row0 + q) : 0;
-    }
-  }
-  TileFields f; f.pu = sm; f.pv = sm + TCELLS; f.pw = sm + 2 * TCELLS; f.pt = sm + 3 * TCELLS; f.ps = sm + 4 * TCELLS;
-  f.base = (lane + 1) + (lj + 1) * SX + (lk + 1) * SX * SY;
-  double* scr = sm + 5 * TCELLS + warp * 32 * STRIDE;
 
-  // how this warp's rows go out: all 32 cells complete (compile-time strides), all active cells alike (run-time strides),
-  // or anything else (non-periodic i edge, dense integral row): per-element shuffles
-  CopyPlan cp;
-  cp.b0 = __shfl_sync(FULL, rp[0], 0);
-  cp.cs = __shfl_sync(FULL, rp[6] - rp[0], 0);
-  cp.nact = __popc(__ballot_sync(FULL, active));
-  {
-    bool same = rp[0] == cp.b0 + lane * cp.cs && !(a.sp.rowintcon >= row0 && a.sp.rowintcon < row0 + 6);
-#pragma unroll
-    for (int q = 1; q <= 6; q++) { // the shuffle must be executed by every lane: no short-circuit in front of it
-      const int ref = __shfl_sync(FULL, rp[q] - rp[0], 0);
-      same = (rp[q] - rp[0] == ref) && same;
-    }
-    const bool uniform = __all_sync(FULL, !active || same);
-    cp.mode = !uniform ? COPY_GENERAL : ((cp.nact == 32 && cp.cs == CELL_NNZ) ? COPY_FULL : COPY_UNIFORM);
-  }
-  double b[6];
-  b[0] = do_jac_row<UU>(a, c, f, active, row0, rp, scr, lane, cp);
-  b[1] = do_jac_row<VV>(a, c, f, active, row0, rp, scr, lane, cp);
-  b[2] = do_jac_row<WW>(a, c, f, active, row0, rp, scr, lane, cp);
-  b[3] = do_jac_row<PP>(a, c, f, active, row0, rp, scr, lane, cp);
-  // convective-adjustment finite differences: evaluated once, shared by the T and the S row
-  MixFD fd;
-  if (active && S.vmix_on && !sbit(c.sig, SIG_NOTOCEAN))
-    thcm_mix_fd(S, a.T, c, f.t(0, 0, -1), f.s(0, 0, -1), f.t(0, 0, 0), f.s(0, 0, 0), f.t(0, 0, 1), f.s(0, 0, 1), fd);
-  b[4] = do_jac_row<TT>(a, c, f, active, row0, rp, scr, lane, cp, &fd);
-  b[5] = do_jac_row<SS>(a, c, f, active, row0, rp, scr, lane, cp, &fd);
-
-  // diag(B): the active cells of a line are consecutive rows -> one contiguous, coalesced run
-  if (active) {
-#pragma unroll
-    for (int q = 0; q < 6; q++) scr[lane * 6 + q] = b[q];
-  }
-  __syncwarp();
-  const int nact = __popc(__ballot_sync(FULL, active));
-  const int base = __shfl_sync(FULL, row0, 0);
-#pragma unroll
-  for (int it = 0; it < 6; it++) {
-    const int t = it * 32 + lane;
-    if (t < 6 * nact) __stcs(a.diagB + (size_t)base + t, scr[t]);
-  }
-}
-
-#ifndef RHS_MINB
-#define RHS_MINB 2
-#endif
-__global__ void __launch_bounds__(NTHREADS, RHS_MINB) rhs_kernel(const __grid_constant__ AsmArgs a) {
-  extern __shared__ double sm[];
-  const Scalars& S = a.S;
-  const int bx = blockIdx.x % a.ntx, by = (blockIdx.x / a.ntx) % a.nty, bz = blockIdx.x / (a.ntx * a.nty) + a.kz0;
-  if (a.part) { // overlap with the halo exchange: rim tiles wait for it, the others do not (block-uniform exit)
-    const bool rim = bx == 0 || bx == a.ntx - 1 || by == 0 || by == a.nty - 1;
-    if (rim != (a.part == 2)) return;
-  }
-  const int gi0 = S.io0 + bx * TI, gj0 = S.jo0 + by * TJ, gk0 = 1 + bz * TK;
-  if (tile_is_plain(S, gi0, gj0, gk0)) stage_tile_plain<true>(a, sm, gi0, gj0, gk0);
-  else stage_tile<true>(a, sm, gi0, gj0, gk0);
-  __syncthreads();
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int lj = warp % TJ, lk = warp / TJ;
-  const int i = gi0 + lane, j = gj0 + lj, k = gk0 + lk;
-  if (j >= S.jo0 + S.mloc || k > S.l) return;
-  const bool active = i < S.io0 + S.nloc;
-  const size_t cidx = active ? cell_index(S, i, j, k) : 0;
-  Cell c; c.i = i; c.j = j; c.k = k; c.sig = active ? a.sig[cidx] : 0ull;
   TileFields f; f.pu = sm; f.pv = sm + TCELLS; f.pw = sm + 2 * TCELLS; f.pt = sm + 3 * TCELLS; f.ps = sm + 4 * TCELLS;
   f.base = (lane + 1) + (lj + 1) * SX + (lk + 1) * SX * SY;
   TileRaw xr; xr.ru = sm + 5 * TCELLS; xr.rv = sm + 6 * TCELLS; xr.rw = sm + 7 * TCELLS; xr.rp = sm + 8 * TCELLS;
   xr.rt = f.pt; xr.rs = f.ps; xr.base = f.base;
-  const size_t row0 = 6 * cidx;
-  double* scr = sm + 9 * TCELLS + warp * 32 * 6;
+  double* scr = sm + NF * TCELLS + warp * SCRW;
 
-  // forcing of this line: one coalesced run of 6*nact doubles, read through the scratch
-  const int nact = __popc(__ballot_sync(FULL, active));
-  const size_t base = __shfl_sync(FULL, (unsigned long long)row0, 0);
+  // How this warp's rows go out: every active cell complete at a 16-byte aligned offset -> bulk copies; all active cells
+  // alike (same clipped row lengths, evenly spaced) -> lanes walk the cells with run-time strides; anything else
+  // (non-periodic i edge, dense integral row) -> per-element shuffles.
+  CopyPlan cp; cp.mode = COPY_GENERAL; cp.b0 = 0; cp.nact = 0; cp.cs = 0;
+  if (JAC) {
+    cp.nact = __popc(__ballot_sync(FULL, active));
+    cp.b0 = __shfl_sync(FULL, p0, 0);
+    cp.cs = __shfl_sync(FULL, pe - p0, 0);
+    if (__all_sync(FULL, !active || (bulk_cell && p0 == cp.b0 + lane * CELL_NNZ))) cp.mode = COPY_BULK;
+    else {
+      bool same = p0 == cp.b0 + lane * cp.cs && !special;
 #pragma unroll
-  for (int it = 0; it < 6; it++) {
-    const int t = it * 32 + lane;
-    if (t < 6 * nact) scr[t] = __ldcs(a.frc + base + t);
+      for (int q = 1; q <= 6; q++) { // the shuffle must be executed by every lane: no short-circuit in front of it
+        const int mine = active ? __ldg(a.rowptr + row0 + q) - p0 : 0;
+        const int ref = __shfl_sync(FULL, mine, 0);
+        same = (mine == ref) && same;
+      }
+      cp.mode = __all_sync(FULL, !active || same) ? COPY_UNIFORM : COPY_GENERAL;
+    }
+    // a line of land cells inside a tile that has ocean: nothing to build
+    if (cp.mode == COPY_BULK && __all_sync(FULL, !active || (sbit(c.sig, SIG_NOTOCEAN) && !pfix))) {
+      if (active) {
+        double xown[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0}, frc[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+        if (RHS) {
+#pragma unroll
+          for (int q = 0; q < 6; q++) xown[q] = xr.raw(0, 0, 0, q + 1);
+          load6(a.frc + row0, frc);
+        }
+        land_cell<JAC, RHS>(a, c, row0, p0, ident, xown, frc);
+      }
+      return;
+    }
   }
-  __syncwarp();
-  double Fv[6];
+
+  // convective adjustment: the base evaluation is the residual's mixing term, the six perturbed ones give the
+  // forward-difference Jacobian entries shared by the T and the S row
+  MixFD fd; fd.bt = 0.0; fd.bs = 0.0;
+  double Fv[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+  // the row's forcing is requested before the Jacobian row is built, which hides its latency
+#define ASM_ROW(A, FDP, MIXV)                                                                      \
+  {                                                                                                \
+    double frc = 0.0;                                                                              \
+    if (RHS && active) frc = __ldg(a.frc + row0 + A - 1);                                          \
+    if (JAC) jac_row_out<A>(a, c, f, active, row0, scr, lane, cp, FDP);                            \
+    if (RHS && active) Fv[A - 1] = rhs_row<A>(S, a.T, c, f, xr, frc, MIXV);                        \
+  }
+  ASM_ROW(UU, nullptr, 0.0)
+  ASM_ROW(VV, nullptr, 0.0)
+  ASM_ROW(WW, nullptr, 0.0)
+  ASM_ROW(PP, nullptr, 0.0)
+  if (JAC) {
+    if (active && S.vmix_on && !sbit(c.sig, SIG_NOTOCEAN))
+      thcm_mix_fd(S, a.T, c, f.t(0, 0, -1), f.s(0, 0, -1), f.t(0, 0, 0), f.s(0, 0, 0), f.t(0, 0, 1), f.s(0, 0, 1), fd);
+  } else if (active && S.vmix_on) {
+    thcm_mix(S, a.T, c, f.t(0, 0, -1), f.s(0, 0, -1), f.t(0, 0, 0), f.s(0, 0, 0), f.t(0, 0, 1), f.s(0, 0, 1), fd.bt, fd.bs);
+  }
+  ASM_ROW(TT, &fd, fd.bt)
+  ASM_ROW(SS, &fd, fd.bs)
+#undef ASM_ROW
+
+  // diag(B) and the residual: 48 contiguous bytes per cell, three 16-byte stores per lane
   if (active) {
-    double frc[6];
-#pragma unroll
-    for (int q = 0; q < 6; q++) frc[q] = scr[lane * 6 + q];
-    double mt = 0.0, ms = 0.0;
-    if (S.vmix_on) thcm_mix(S, a.T, c, f.t(0, 0, -1), f.s(0, 0, -1), f.t(0, 0, 0), f.s(0, 0, 0), f.t(0, 0, 1), f.s(0, 0, 1), mt, ms);
-    Fv[0] = rhs_row<UU>(S, a.T, c, f, xr, frc[0], 0.0);
-    Fv[1] = rhs_row<VV>(S, a.T, c, f, xr, frc[1], 0.0);
-    Fv[2] = rhs_row<WW>(S, a.T, c, f, xr, frc[2], 0.0);
-    Fv[3] = rhs_row<PP>(S, a.T, c, f, xr, frc[3], 0.0);
-    Fv[4] = rhs_row<TT>(S, a.T, c, f, xr, frc[4], mt);
-    Fv[5] = rhs_row<SS>(S, a.T, c, f, xr, frc[5], ms);
+    if (JAC) {
+      double b[6];
+      b[0] = diagb_entry<UU>(S, c.sig, a.sp, row0); b[1] = diagb_entry<VV>(S, c.sig, a.sp, row0 + 1); b[2] = diagb_entry<WW>(S, c.sig, a.sp, row0 + 2);
+      b[3] = diagb_entry<PP>(S, c.sig, a.sp, row0 + 3); b[4] = diagb_entry<TT>(S, c.sig, a.sp, row0 + 4); b[5] = diagb_entry<SS>(S, c.sig, a.sp, row0 + 5);
+      store6(a.diagB + row0, b);
+    }
+    if (RHS) store6(a.F + row0, Fv);
   }
-  __syncwarp();
-  if (active) {
-#pragma unroll
-    for (int q = 0; q < 6; q++) scr[lane * 6 + q] = Fv[q];
-  }
-  __syncwarp();
-#pragma unroll
-  for (int it = 0; it < 6; it++) {
-    const int t = it * 32 + lane;
-    if (t < 6 * nact) __stcs(a.F + base + t, scr[t]);
-  }
+  if (JAC && cp.mode == COPY_BULK) bulk_wait_read(); // the scratch must outlive the copies that read it
 }
 
 // ---- integral condition: sum over ocean S dofs of coef*x (THCM.C:1006-1018) ----
@@ -374,30 +459,35 @@ __global__ void intcond_finish_kernel(const double* dotval, double sign, double 
   if (p1 >= 0) F[p1] = 0.0;
   if (p2 >= 0) F[p2] = 0.0;
 }
+
+template <bool JAC, bool RHS> constexpr int asm_smem() {
+  return ((RHS ? 9 : 5) * TCELLS + (JAC ? NWARP * 32 * STRIDE + 3 * CELL_NNZ : 0)) * (int)sizeof(double);
+}
+template <bool JAC, bool RHS> void launch_asm_t(const AsmArgs& a0, cudaStream_t st) {
+  AsmArgs a = a0;
+  a.ntx = (a.S.nloc + TI - 1) / TI; a.nty = (a.S.mloc + TJ - 1) / TJ; a.ntz = (a.S.l + TK - 1) / TK;
+  if (a.nkz <= 0) a.kz0 = 0;
+  constexpr int smem = asm_smem<JAC, RHS>();
+  static unsigned long long attr_done = 0; // one bit per device: the attribute belongs to the device's copy of the function
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!(attr_done >> (dev & 63) & 1ull)) {
+    cudaFuncSetAttribute(asm_kernel<JAC, RHS>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    attr_done |= 1ull << (dev & 63);
+  }
+  const dim3 grid(a.ntx, a.nty, a.nkz > 0 ? a.nkz : a.ntz);
+  asm_kernel<JAC, RHS><<<grid, NTHREADS, smem, st>>>(a);
+}
 } // namespace
 
-int jac_smem_bytes() { return (5 * TCELLS + NWARP * 32 * STRIDE) * (int)sizeof(double); }
-int rhs_smem_bytes() { return (9 * TCELLS + NWARP * 32 * 6) * (int)sizeof(double); }
-
-static int grid_of(const AsmArgs& a) { return a.ntx * a.nty * (a.nkz > 0 ? a.nkz : a.ntz); }
+int jac_smem_bytes() { return asm_smem<true, false>(); }
+int rhs_smem_bytes() { return asm_smem<false, true>(); }
+int asm_smem_bytes() { return asm_smem<true, true>(); }
 int asm_tile_levels() { return TK; }
 
-void launch_jac(const AsmArgs& a0, cudaStream_t st) {
-  AsmArgs a = a0;
-  a.ntx = (a.S.nloc + TI - 1) / TI; a.nty = (a.S.mloc + TJ - 1) / TJ; a.ntz = (a.S.l + TK - 1) / TK;
-  if (a.nkz <= 0) a.kz0 = 0;
-  static bool attr = false;
-  if (!attr) { cudaFuncSetAttribute(jac_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, jac_smem_bytes()); attr = true; }
-  jac_kernel<<<grid_of(a), NTHREADS, jac_smem_bytes(), st>>>(a);
-}
-void launch_rhs(const AsmArgs& a0, cudaStream_t st) {
-  AsmArgs a = a0;
-  a.ntx = (a.S.nloc + TI - 1) / TI; a.nty = (a.S.mloc + TJ - 1) / TJ; a.ntz = (a.S.l + TK - 1) / TK;
-  if (a.nkz <= 0) a.kz0 = 0;
-  static bool attr = false;
-  if (!attr) { cudaFuncSetAttribute(rhs_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, rhs_smem_bytes()); attr = true; }
-  rhs_kernel<<<grid_of(a), NTHREADS, rhs_smem_bytes(), st>>>(a);
-}
+void launch_jac(const AsmArgs& a, cudaStream_t st) { launch_asm_t<true, false>(a, st); }
+void launch_rhs(const AsmArgs& a, cudaStream_t st) { launch_asm_t<false, true>(a, st); }
+void launch_asm(const AsmArgs& a, cudaStream_t st) { launch_asm_t<true, true>(a, st); }
 void launch_intcond_dot(const double* coefS, const double* x, long long ncell, double* partial, cudaStream_t st) {
   intcond_dot_kernel<<<1, 1024, 0, st>>>(coefS, x, ncell, partial);
 }

@@ -736,6 +736,17 @@ template <int A> constexpr int seam_rank(int e, int side) {
     }
   return cnt;
 }
+// Seam cells whose nine (dk,dj) groups are all present (1 < j < m, 1 < k < l): positions are compile-time constants.
+template <int A> constexpr int group_prefix(int g) {
+  int acc = 0;
+  for (int q = 0; q < g; q++) acc += group_size<A>(q);
+  return acc;
+}
+template <int A> constexpr int seam_pos(int e, int side) { return group_prefix<A>(slot_group(RowDef<A>::e[e].slot)) + seam_rank<A>(e, side); }
+template <int A, class Out> THCM_HD void emit_row_seam_inner(const Row<A>& r, bool west, Out out) {
+  if (west) static_for<0, Row<A>::NE>([&](auto q) { constexpr int e = decltype(q)::value; out[seam_pos<A>(e, 0)] = r.a[e]; });
+  else static_for<0, Row<A>::NE>([&](auto q) { constexpr int e = decltype(q)::value; out[seam_pos<A>(e, 1)] = r.a[e]; });
+}
 // `out` points at the first value of this row (rowptr[row]).
 template <int A, class Out> THCM_HD void emit_row(const Row<A>& r, const Scalars& S, const Cell& c, Out out) {
   const bool seam = row_has_seam(S, c);

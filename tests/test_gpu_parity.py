@@ -67,6 +67,44 @@ def test_jacobian_parity(name, kind):
     assert err.max() <= 1e-6, err.max()
 
 
+@pytest.mark.parametrize("name", CASES)
+@pytest.mark.parametrize("kind", ["random", "smooth"])
+def test_fused_assembly_parity(name, kind):
+    """thcm_b200_assemble (Jacobian + residual in ONE kernel, TMA copy-out) against the oracle with the bars of the two
+    tests above, and bit for bit against the stand-alone residual / Jacobian kernels."""
+    import torch
+    cfg, mask, O, G = cases.make_pair(name)
+    x = cases.state(cfg, mask, seed=7, kind=kind)
+    Fo = O.rhs(x)
+    vo, bo = O.jac(x)
+    Fs = G.computeRHS_host(x)
+    vs, bs = G.computeJacobian_host(x)
+    poison = np.full(G.nnz, 777.0)
+    rp, col = O.graph()
+    if cfg["sres"] == 0:  # the dense integral row is static: written once at set-up, never by the kernels
+        r = int(np.argmax(np.diff(rp)))
+        poison[rp[r]:rp[r + 1]] = vs[rp[r]:rp[r + 1]]
+    G.set_values_host(poison)
+    dx = torch.zeros(G.nvec, dtype=torch.float64, device="cuda")
+    dx[:G.nrows] = torch.from_numpy(x).cuda()
+    dF = torch.full((G.nvec,), 555.0, dtype=torch.float64, device="cuda")
+    G.assemble(dx, dF, jacobian=True)
+    G.sync()
+    Fg = dF[:G.nrows].cpu().numpy()
+    vg, bg = G.values_host()
+    assert np.array_equal(Fg, Fs) and np.array_equal(vg, vs) and np.array_equal(bg, bs), "fused kernel differs from the stand-alone kernels"
+    ts = _mix_rows(cfg, Fo.size)
+    assert np.array_equal(Fo[~ts], Fg[~ts])
+    assert np.abs(Fo - Fg).max() <= 1e-12 * np.abs(Fo).max()
+    assert np.array_equal(bo, bg)
+    rows = np.repeat(np.arange(rp.size - 1), np.diff(rp))
+    tracer = (rows % 6 >= 4) & (col % 6 >= 4)
+    assert np.array_equal(vo[~tracer], vg[~tracer])
+    full = np.zeros(rp.size - 1)
+    full[np.diff(rp) > 0] = np.maximum.reduceat(np.abs(vo), rp[:-1][np.diff(rp) > 0])
+    assert (np.abs(vo - vg) / np.maximum(full[rows], 1e-300)).max() <= 1e-6
+
+
 @pytest.mark.parametrize("name", ["natl8", "2dmoc", "rand_periodic", "global4"])
 def test_spmv_bit_exact(name):
     import oracle_lib as ol

@@ -4,9 +4,12 @@ rep, kern, obj = sys.argv[1], sys.argv[2], sys.argv[3]
 top = int(sys.argv[4]) if len(sys.argv) > 4 else 40
 tmp = tempfile.mkdtemp()
 subprocess.run(["cuobjdump", "-xelf", "all", os.path.abspath(obj)], cwd=tmp, check=True, stdout=subprocess.DEVNULL)
-cub = [f for f in os.listdir(tmp) if f.endswith(".cubin")][0]
-dis = subprocess.run(["nvdisasm", "-g", "-c", os.path.join(tmp, cub)], capture_output=True, text=True).stdout.split("\n")
-start = [i for i, l in enumerate(dis) if l.startswith(".text.") and kern in l][0]
+for cub in sorted(f for f in os.listdir(tmp) if f.endswith(".cubin")):
+    dis = subprocess.run(["nvdisasm", "-g", "-c", os.path.join(tmp, cub)], capture_output=True, text=True).stdout.split("\n")
+    hit = [i for i, l in enumerate(dis) if l.startswith(".text.") and kern in l]
+    if hit:
+        break
+start = hit[0]
 cur, off2line = None, {}
 for l in dis[start + 1:]:
     if l.startswith("//-----"):
