@@ -130,6 +130,30 @@ __device__ __noinline__ void warp_copy_out_uniform(double* __restrict__ val, con
 enum { COPY_GENERAL = 0, COPY_UNIFORM = 1, COPY_BULK = 2 };
 struct CopyPlan { int mode, b0, nact, cs; };
 
+// Lines of complete cells at a 16-byte aligned offset: NP doubles per cell (NP even) at offset OFF inside the cell's
+// CELL_NNZ values.  Lane = (group g, chunk q); group g moves cells g, g+G, ... : one LDS.128 + one STG.128 per step.
+template <int NP, int OFF>
+__device__ __forceinline__ void warp_copy_vec(double* __restrict__ val_line, const double* scr, int lane, int nact) {
+  static_assert(NP % 2 == 0 && OFF % 2 == 0 && NP <= STRIDE, "16-byte pieces");
+  constexpr int NC = NP / 2, G = 32 / NC;
+  const int g = lane / NC, q = lane - g * NC;
+  if (g < G) {
+    const double2* src = reinterpret_cast<const double2*>(scr + g * STRIDE) + q;
+    double2* dst = reinterpret_cast<double2*>(val_line + g * CELL_NNZ + OFF) + q;
+    if (nact == 32) {
+#pragma unroll
+      for (int cc = 0; cc < 32; cc += G) {
+        if (cc + G <= 32) __stcs(dst + cc * (CELL_NNZ / 2), src[cc * (STRIDE / 2)]);
+        else if (cc + g < 32) __stcs(dst + cc * (CELL_NNZ / 2), src[cc * (STRIDE / 2)]);
+      }
+    } else {
+#pragma unroll 4
+      for (int cc = 0; cc < 32; cc += G)
+        if (cc + g < nact) __stcs(dst + cc * (CELL_NNZ / 2), src[cc * (STRIDE / 2)]);
+    }
+  }
+}
+
 // A complete row into the lane's scratch slot in final order (SIDE 0: static order, 1 / 2: cell on the periodic seam at
 // i = 1 / i = n, compile-time permutation); entries that do not fit the slot are returned in `tail`.
 template <int A, int SIDE, bool ALIGNED>
@@ -165,24 +189,21 @@ __device__ __forceinline__ void jac_row_out(const AsmArgs& a, const Cell& c, con
   if (active) store = jac_row_build<A, TileFields>(r, a.S, a.T, c, f, a.sp, row0 + A - 1, fd);
   double* mine = scr + lane * STRIDE;
   if (cp.mode == COPY_BULK) {
-    // every lane owns its slot and its cell's values: no exchange between lanes, hence no warp synchronisation
+    // Complete cells at a 16-byte aligned offset: the row goes into the lane's slot in final order with 16-byte shared
+    // stores, then the warp moves the piece of all its cells with 16-byte loads and streaming stores -- lanes are split in
+    // groups of NE/2, a group moves one cell's piece per step, all offsets are immediates.
     constexpr int PRE = (A == PP) ? RowDef<WW>::NE : 0;        // the P row rides behind the W row (7 + 11 values = 144 B)
-    if (A != PP) bulk_wait_read();                             // the previous piece has left the slot
     if (store) {
-      static_assert(RowDef<A>::NE <= STRIDE + 2 && PRE + RowDef<PP>::NE <= STRIDE, "piece does not fit the scratch slot");
-      double tail[2] = {0.0, 0.0};
+      double tail[2];
       if (!row_has_seam(a.S, c)) emit_slot<A, 0, (PRE % 2 == 0)>(r, mine + PRE, tail);
       else if (c.i == 1) emit_slot<A, 1, false>(r, mine + PRE, tail);
       else emit_slot<A, 2, false>(r, mine + PRE, tail);
-      if (A != WW) {
-        constexpr int OFF = (A == PP) ? row_offset<WW>() : row_offset<A>();
-        constexpr int NB = (PRE + RowDef<A>::NE) < STRIDE ? (PRE + RowDef<A>::NE) : STRIDE;
-        double* dst = a.val + (size_t)cp.b0 + (size_t)lane * CELL_NNZ + OFF;
-        fence_proxy_async();
-        bulk_s2g(dst, mine, NB * 8);
-        bulk_commit();
-        if constexpr (RowDef<A>::NE > STRIDE) __stcs(reinterpret_cast<double2*>(dst + STRIDE), make_double2(tail[0], tail[1])); // 16-byte aligned: even offset
-      }
+    }
+    if constexpr (A != WW) {
+      constexpr int OFF = (A == PP) ? row_offset<WW>() : row_offset<A>();
+      __syncwarp();
+      warp_copy_vec<PRE + RowDef<A>::NE, OFF>(a.val + (size_t)cp.b0, scr, lane, cp.nact);
+      __syncwarp();
     }
   } else {
     // rare path: the row offsets are (re)loaded here instead of being kept in registers across the whole kernel
@@ -276,24 +297,34 @@ __device__ __forceinline__ void load6(const double* src, double (&v)[6]) {
     for (int q = 0; q < 6; q++) v[q] = __ldg(src + q);
   }
 }
-// A land cell in one go: six identity rows (one 832-byte bulk copy from the constant block), diag(B) = 0, residual from the
-// cell's own state.
+// A line of land cells: six identity rows per cell.  The 832 bytes of a cell come from a constant block in shared memory
+// through the TMA engine (cp.async.bulk is a uniform-datapath instruction: ONE lane issues the copies of the whole line);
+// diag(B) = 0, residual from the cell's own state.
 template <bool JAC, bool RHS>
-__device__ __forceinline__ void land_cell(const AsmArgs& a, const Cell& c, int row0, int p0, const double* ident, const double (&xown)[6], const double (&frc)[6]) {
+__device__ __forceinline__ void land_line(const AsmArgs& a, const Cell& c, bool active, int row0, int b0, int nact, int lane, const double* ident,
+                                          const double (&xown)[6], const double (&frc)[6]) {
   if (JAC) {
-    const int side = !row_has_seam(a.S, c) ? 0 : (c.i == 1 ? 1 : 2);
-    bulk_s2g(a.val + (size_t)p0, ident + side * CELL_NNZ, CELL_NNZ * 8);
-    bulk_commit();
-    const double z[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-    store6(a.diagB + row0, z);
+    const bool seam = a.S.periodic && a.S.nloc == a.S.n; // the first / last cell of the row then has its own column order
+    if (lane == 0) {
+      for (int cc = 0; cc < nact; cc++) {
+        const int gi = c.i + cc;
+        const int side = !seam ? 0 : (gi == 1 ? 1 : (gi == a.S.n ? 2 : 0));
+        bulk_s2g(a.val + (size_t)b0 + (size_t)cc * CELL_NNZ, ident + side * CELL_NNZ, CELL_NNZ * 8);
+      }
+      bulk_commit();
+    }
+    if (active) {
+      const double z[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+      store6(a.diagB + row0, z);
+    }
   }
-  if (RHS) {
+  if (RHS && active) {
     double Fv[6];
 #pragma unroll
     for (int q = 0; q < 6; q++) Fv[q] = rhs_land(c.sig, xown[q], frc[q]);
     store6(a.F + row0, Fv);
   }
-  if (JAC) bulk_wait_read();
+  if (JAC && lane == 0) bulk_wait_read(); // the block's shared memory must outlive the copies that read it
 }
 
 template <bool JAC, bool RHS>
@@ -347,11 +378,9 @@ __global__ void __launch_bounds__(NTHREADS, JAC_MINB) asm_kernel(const __grid_co
   // A tile of land cells (a third of the 1-degree grid) needs no neighbour: nothing is staged.
   const bool easy_land = !active || (sbit(c.sig, SIG_NOTOCEAN) && (!JAC || (bulk_cell && !pfix)));
   if (__syncthreads_and(easy_land)) {
-    if (active) {
-      double xown[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0}, frc[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-      if (RHS) { load6(a.x + row0, xown); load6(a.frc + row0, frc); }
-      land_cell<JAC, RHS>(a, c, row0, p0, ident, xown, frc);
-    }
+    double xown[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0}, frc[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+    if (RHS && active) { load6(a.x + row0, xown); load6(a.frc + row0, frc); }
+    land_line<JAC, RHS>(a, c, active, row0, __shfl_sync(FULL, p0, 0), __popc(__ballot_sync(FULL, active)), lane, ident, xown, frc);
     return;
   }
 
@@ -387,15 +416,13 @@ __global__ void __launch_bounds__(NTHREADS, JAC_MINB) asm_kernel(const __grid_co
     }
     // a line of land cells inside a tile that has ocean: nothing to build
     if (cp.mode == COPY_BULK && __all_sync(FULL, !active || (sbit(c.sig, SIG_NOTOCEAN) && !pfix))) {
-      if (active) {
-        double xown[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0}, frc[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-        if (RHS) {
+      double xown[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0}, frc[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+      if (RHS && active) {
 #pragma unroll
-          for (int q = 0; q < 6; q++) xown[q] = xr.raw(0, 0, 0, q + 1);
-          load6(a.frc + row0, frc);
-        }
-        land_cell<JAC, RHS>(a, c, row0, p0, ident, xown, frc);
+        for (int q = 0; q < 6; q++) xown[q] = xr.raw(0, 0, 0, q + 1);
+        load6(a.frc + row0, frc);
       }
+      land_line<JAC, RHS>(a, c, active, row0, cp.b0, cp.nact, lane, ident, xown, frc);
       return;
     }
   }
@@ -436,7 +463,6 @@ __global__ void __launch_bounds__(NTHREADS, JAC_MINB) asm_kernel(const __grid_co
     }
     if (RHS) store6(a.F + row0, Fv);
   }
-  if (JAC && cp.mode == COPY_BULK) bulk_wait_read(); // the scratch must outlive the copies that read it
 }
 
 // ---- integral condition: sum over ocean S dofs of coef*x (THCM.C:1006-1018) ----
