@@ -52,6 +52,9 @@ constexpr unsigned FULL = 0xffffffffu;
 #ifndef JAC_MINB
 #define JAC_MINB 2
 #endif
+#ifndef RHS_MINB
+#define RHS_MINB 3   // residual alone: 80 registers (112 bytes of spills) and 24 warps per SM beat 94 registers and 16 (0.172 -> 0.154 ms at 1 degree)
+#endif
 
 struct TileFields { // accessor concept F of thcm_rows.cuh over the shared-memory tile
   const double *pu, *pv, *pw, *pt, *ps;
@@ -242,30 +245,33 @@ __device__ __forceinline__ void stage_tile(const AsmArgs& a, double* sm, int gi0
 __device__ __forceinline__ bool tile_is_plain(const Scalars& S, int gi0, int gj0, int gk0) {
   return gi0 - 1 >= S.io0 && gi0 + TI <= S.io0 + S.nloc - 1 && gj0 - 1 >= S.jo0 && gj0 + TJ <= S.jo0 + S.mloc - 1 && gk0 >= 2 && gk0 + TK <= S.l;
 }
-template <bool RHS>
-__device__ __forceinline__ void stage_tile_plain(const AsmArgs& a, double* sm, int gi0, int gj0, int gk0) {
+struct PlainLoads { double2 q[(TCELLS + NTHREADS - 1) / NTHREADS][3]; uint64_t sg[(TCELLS + NTHREADS - 1) / NTHREADS]; };
+__device__ __forceinline__ void stage_plain_issue(const AsmArgs& a, PlainLoads& L, int gi0, int gj0, int gk0) {
   const Scalars& S = a.S;
   constexpr int NIT = (TCELLS + NTHREADS - 1) / NTHREADS;
   const size_t base = ((size_t)(gk0 - 2) * S.mloc + (gj0 - 1 - S.jo0)) * S.nloc + (gi0 - 1 - S.io0); // tile cell (0,0,0)
-  double2 q[NIT][3];
-  uint64_t sg[NIT];
 #pragma unroll
   for (int it = 0; it < NIT; it++) {
     const int t = min((int)threadIdx.x + it * NTHREADS, TCELLS - 1);
     const int ti = t % SX, tj = (t / SX) % SY, tk = t / (SX * SY);
     const size_t c = base + ((size_t)tk * S.mloc + tj) * S.nloc + ti;
     const double2* p = reinterpret_cast<const double2*>(a.x + 6 * c);
-    q[it][0] = __ldg(p); q[it][1] = __ldg(p + 1); q[it][2] = __ldg(p + 2);
-    sg[it] = __ldg(a.sig + c);
+    L.q[it][0] = __ldg(p); L.q[it][1] = __ldg(p + 1); L.q[it][2] = __ldg(p + 2);
+    L.sg[it] = __ldg(a.sig + c);
   }
+}
+template <bool RHS>
+__device__ __forceinline__ void stage_plain_apply(const AsmArgs& a, const PlainLoads& L, double* sm, int gk0) {
+  const Scalars& S = a.S;
+  constexpr int NIT = (TCELLS + NTHREADS - 1) / NTHREADS;
 #pragma unroll
   for (int it = 0; it < NIT; it++) {
     const int t = threadIdx.x + it * NTHREADS;
     if (t < TCELLS) {
-      const bool live = sbit(sg[it], SIG_LIVE), top = gk0 + t / (SX * SY) - 1 == S.l;
-      sm[t] = live ? q[it][0].x : 0.0; sm[TCELLS + t] = live ? q[it][0].y : 0.0; sm[2 * TCELLS + t] = top ? 0.0 : q[it][1].x;
-      sm[3 * TCELLS + t] = q[it][2].x; sm[4 * TCELLS + t] = q[it][2].y;
-      if (RHS) { sm[5 * TCELLS + t] = q[it][0].x; sm[6 * TCELLS + t] = q[it][0].y; sm[7 * TCELLS + t] = q[it][1].x; sm[8 * TCELLS + t] = q[it][1].y; }
+      const bool live = sbit(L.sg[it], SIG_LIVE), top = gk0 + t / (SX * SY) - 1 == S.l;
+      sm[t] = live ? L.q[it][0].x : 0.0; sm[TCELLS + t] = live ? L.q[it][0].y : 0.0; sm[2 * TCELLS + t] = top ? 0.0 : L.q[it][1].x;
+      sm[3 * TCELLS + t] = L.q[it][2].x; sm[4 * TCELLS + t] = L.q[it][2].y;
+      if (RHS) { sm[5 * TCELLS + t] = L.q[it][0].x; sm[6 * TCELLS + t] = L.q[it][0].y; sm[7 * TCELLS + t] = L.q[it][1].x; sm[8 * TCELLS + t] = L.q[it][1].y; }
     }
   }
 }
@@ -328,7 +334,7 @@ __device__ __forceinline__ void land_line(const AsmArgs& a, const Cell& c, bool 
 }
 
 template <bool JAC, bool RHS>
-__global__ void __launch_bounds__(NTHREADS, JAC_MINB) asm_kernel(const __grid_constant__ AsmArgs a) {
+__global__ void __launch_bounds__(NTHREADS, JAC ? JAC_MINB : RHS_MINB) asm_kernel(const __grid_constant__ AsmArgs a) {
   extern __shared__ __align__(16) double sm[];
   constexpr int NF = RHS ? 9 : 5;                     // staged field arrays
   constexpr int SCRW = JAC ? 32 * STRIDE : 0;         // scratch doubles per warp
@@ -375,6 +381,13 @@ __global__ void __launch_bounds__(NTHREADS, JAC_MINB) asm_kernel(const __grid_co
     fence_proxy_async();
   }
 
+  // Tiles whose cells (halo layer included) are all owned, interior cells of the global grid -- most tiles -- have their
+  // staging loads issued BEFORE the vote below, so that the loads of the cell's own signature / row offsets (which the
+  // vote needs) and the tile's loads are one round trip to memory, not two.
+  const bool plain = tile_is_plain(S, gi0, gj0, gk0);
+  PlainLoads L;
+  if (plain) stage_plain_issue(a, L, gi0, gj0, gk0);
+
   // A tile of land cells (a third of the 1-degree grid) needs no neighbour: nothing is staged.
   const bool easy_land = !active || (sbit(c.sig, SIG_NOTOCEAN) && (!JAC || (bulk_cell && !pfix)));
   if (__syncthreads_and(easy_land)) {
@@ -384,7 +397,7 @@ __global__ void __launch_bounds__(NTHREADS, JAC_MINB) asm_kernel(const __grid_co
     return;
   }
 
-  if (tile_is_plain(S, gi0, gj0, gk0)) stage_tile_plain<RHS>(a, sm, gi0, gj0, gk0);
+  if (plain) stage_plain_apply<RHS>(a, L, sm, gk0);
   else stage_tile<RHS>(a, sm, gi0, gj0, gk0);
   __syncthreads();
   if (!line) return;

@@ -11,7 +11,7 @@ G = ib.Ocean(cfg, mask)
 for k, v in grids.STARTING_PARS["global"].items(): G.setPar(k, v)
 x = torch.from_numpy(grids.synthetic_state(n, m, l, mask, kind=os.environ.get("STATE", "random"))).cuda()
 F = torch.empty_like(x)
-for _ in range(3): G.computeJacobian(x); G.computeRHS(x, F)
+for _ in range(3): G.computeJacobian(x); G.computeRHS(x, F); G.assemble(x, F, jacobian=True)
 torch.cuda.synchronize()
 def t(fn, reps=20):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

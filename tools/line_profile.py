@@ -21,12 +21,17 @@ for l in dis[start + 1:]:
     m = re.match(r"\s+/\*([0-9a-f]{4,6})\*/", l)
     if m:
         off2line[int(m.group(1), 16)] = cur
-src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-name", "regex:" + kern], capture_output=True, text=True).stdout
+src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(src.split("\n")))
-hi = [i for i, r in enumerate(rows) if r and r[0] == "Address"][0]
+kre = os.environ.get("KNAME", "")   # substring of the demangled kernel name (first match)
+kn = [i for i, r in enumerate(rows) if r and r[0] == "Kernel Name" and kre in r[1]][0]
+hi = [i for i, r in enumerate(rows) if i > kn and r and r[0] == "Address"][0]
 hdr = rows[hi]
 ie, ns = hdr.index("Instructions Executed"), hdr.index("# Samples")
-data = [r for r in rows[hi + 1:] if len(r) >= len(hdr) and r[0].startswith("0x")]
+data = []
+for r in rows[hi + 1:]:
+    if len(r) >= len(hdr) and r[0].startswith("0x"): data.append(r)
+    elif data: break
 base = int(data[0][0], 16)
 agg, samp = collections.Counter(), collections.Counter()
 for r in data:
