@@ -766,6 +766,15 @@ int vec_b200_dot(thcm_b200_t* h, const double* a, const double* b, double* resul
   CU(cudaStreamSynchronize(h->stream));
   return 0;
 }
+int vec_b200_dot_noalloc(const double* d_a, const double* d_b, int64_t n, double* d_out, void* stream) {
+  if (!d_a || !d_b || !d_out) return fail(IEMIC_B200_EINVAL, "vec_b200_dot_noalloc: null pointer");
+  if (n < 0 || n > dot_noalloc_max_n())
+    return fail(IEMIC_B200_EINVAL, "vec_b200_dot_noalloc: n = " + std::to_string((long long)n) + " is outside 0.." + std::to_string(dot_noalloc_max_n()) +
+                                       " (the static reduction scratch of this entry point is sized for that)");
+  const int e = launch_dot_noalloc(d_a, d_b, n, d_out, (cudaStream_t)stream);
+  if (e != 0) return fail(IEMIC_B200_ECUDA, std::string("vec_b200_dot_noalloc: ") + cudaGetErrorString((cudaError_t)e));
+  return 0;
+}
 int vec_b200_norm2(thcm_b200_t* h, const double* a, double* result) {
   int rc = vec_b200_dot(h, a, a, result);
   if (rc == 0) *result = std::sqrt(*result);

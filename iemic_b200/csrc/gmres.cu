@@ -370,6 +370,29 @@ __global__ void sqrt_store_kernel(const double* nrm2, double* out) {
   if (threadIdx.x == 0) *out = sqrt(*nrm2);
 }
 
+// ---- dot product without any allocation (vec_b200_dot_noalloc; no counterpart in the reference) ----
+// Block partials and the arrival ticket live in a file-scope device array that every GPU loading the library holds until
+// exit (NOALLOC_SLOTS * 8 bytes = 16.6 KB).  Every call shares it: calls that overlap on one GPU race.
+constexpr int NOALLOC_MAXBLK = 2048;               // block partials [0, NOALLOC_MAXBLK)
+constexpr int NOALLOC_SLOTS = NOALLOC_MAXBLK + 32;  // + one 256-byte aligned line for the ticket
+static __device__ __align__(256) double g_noalloc_scratch[NOALLOC_SLOTS];
+
+__global__ void __launch_bounds__(RT) dot_noalloc_kernel(const double* __restrict__ a, const double* __restrict__ b, long long n, double* out,
+                                                         double* scratch) {
+  double* partial = scratch;
+  unsigned int* ticket = reinterpret_cast<unsigned int*>(scratch + NOALLOC_MAXBLK);
+  const bool vec = (((size_t)a | (size_t)b) & 15) == 0;
+  const long long n2 = vec ? (n >> 1) : 0;
+  double acc[1] = {0.0};
+  for (long long i = (long long)blockIdx.x * RT + threadIdx.x; i < n2; i += (long long)gridDim.x * RT) {
+    const double2 x = reinterpret_cast<const double2*>(a)[i], y = reinterpret_cast<const double2*>(b)[i];
+    acc[0] = fma(x.y, y.y, fma(x.x, y.x, acc[0]));
+  }
+  for (long long i = 2 * n2 + (long long)blockIdx.x * RT + threadIdx.x; i < n; i += (long long)gridDim.x * RT) acc[0] = fma(a[i], b[i], acc[0]); // odd tail / unaligned vectors
+  block_publish<1>(acc, 1, partial, 1, 0);
+  if (last_block(ticket)) final_sum(partial, 1, 1, out);
+}
+
 int g_red_blocks = 0;
 int grid_for(long long n) {
   long long need = ((n >> 1) + RT - 1) / RT;
@@ -386,6 +409,31 @@ int red_blocks() {
     g_red_blocks = sms * 8; // 8 resident blocks of 256 threads per SM: one full wave
   }
   return g_red_blocks;
+}
+
+long long dot_noalloc_max_n() { return 1ll << 30; }
+// Returns 0, or a cudaError_t.  In host code the array's name is only a stand-in: the device address comes from
+// cudaGetSymbolAddress, asked once per device with that device current.
+int launch_dot_noalloc(const double* a, const double* b, long long n, double* out, cudaStream_t st) {
+  static double* dev_ptr[64] = {nullptr};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 0 || dev >= 64) return (int)cudaErrorInvalidDevice;
+  if (!dev_ptr[dev]) {
+    double* p = nullptr;
+    e = cudaGetSymbolAddress((void**)&p, g_noalloc_scratch);
+    if (e != cudaSuccess) return (int)e;
+    dev_ptr[dev] = p;
+  }
+  double* scratch = dev_ptr[dev];
+  // the array keeps the last call's contents: the ticket must start at zero (an aborted launch may have left it counting)
+  e = cudaMemsetAsync(scratch + NOALLOC_MAXBLK, 0, 32 * sizeof(double), st);
+  if (e != cudaSuccess) return (int)e;
+  int grid = grid_for(n);
+  if (grid > NOALLOC_MAXBLK) grid = NOALLOC_MAXBLK;
+  dot_noalloc_kernel<<<grid, RT, 0, st>>>(a, b, n, out, scratch);
+  return (int)cudaGetLastError();
 }
 
 void launch_multi_dot(const double* V, long long ldv, int nv, const double* w, long long n, double* out, RedBuf rb, cudaStream_t st, const PeerRed& pr,

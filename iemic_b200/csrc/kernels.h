@@ -112,6 +112,9 @@ void launch_multi_axpy_dot(const double* V, long long ldv, int nv, const double*
 void launch_axpy_dot(const double* hprev, const double* vprev, const double* vnext, double* w, long long n, double* out, RedBuf rb, cudaStream_t st,
                      const PeerRed& pr = PeerRed{});
 void launch_dot(const double* a, const double* b, long long n, double* out, RedBuf rb, cudaStream_t st, const PeerRed& pr = PeerRed{});
+// same product with the reduction scratch in a static device array (no allocation anywhere); returns 0 or a cudaError_t
+int launch_dot_noalloc(const double* a, const double* b, long long n, double* out, cudaStream_t st);
+long long dot_noalloc_max_n();
 // y = alpha * x with alpha = (inv ? 1/s[0] : s[0]) read on the device ; s may be sqrt'ed first (sq: s[0] holds a squared norm)
 void launch_scale_copy(const double* x, double* y, long long n, const double* s, int inv, int sq, cudaStream_t st);
 void launch_update(double a, const double* A, double b, double* y, long long n, cudaStream_t st); // y = a*A + b*y

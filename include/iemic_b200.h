@@ -121,6 +121,13 @@ int thcm_b200_spmv_host(thcm_b200_t* h, const double* x, double* y);
 
 /* ---- vector kernels (Epetra_Vector subset): all device pointers, length = nrows_local, results global ---- */
 int vec_b200_dot(thcm_b200_t* h, const double* d_a, const double* d_b, double* result);
+/* No counterpart in the reference: added for callers that must not allocate (CUDA graph
+ * capture, tight serving loops).  Same product as vec_b200_dot on ONE GPU, without a handle: d_out[0] = sum_i d_a[i]*d_b[i] is
+ * left on the device, the call is asynchronous on `stream` (a cudaStream_t, may be 0), and nothing is allocated anywhere -- the
+ * reduction scratch is a static 16.6 KB device array inside the library that every GPU loading it holds until exit.
+ * 0 <= n <= 2^30, otherwise IEMIC_B200_EINVAL.  All calls share that array: calls that overlap on one GPU (different streams,
+ * threads or processes' contexts apart) race; order them on one stream. */
+int vec_b200_dot_noalloc(const double* d_a, const double* d_b, int64_t n, double* d_out, void* stream);
 int vec_b200_norm2(thcm_b200_t* h, const double* d_a, double* result);
 int vec_b200_update(thcm_b200_t* h, double a, const double* d_A, double b, double* d_this); /* this = a*A + b*this */
 int vec_b200_scale(thcm_b200_t* h, double a, double* d_this);
