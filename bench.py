@@ -40,6 +40,7 @@ def parse():
     ap.add_argument("--mask", default="global", choices=["global", "none"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--skip-gmres", action="store_true")
+    ap.add_argument("--write-parity-ref", action="store_true", help="one GPU only: record J1_norm2 / gmres_hist of this run as the committed reference")
     return ap.parse_args()
 
 
@@ -112,70 +113,216 @@ def alg_bytes(ncell, nrows, nnz, m):
     return jac, rhs, spmv, cycle
 
 
-def cpu_sample(threads, sample_grid=(48, 19, 12), min_seconds=8.0):
-    """Times the CPU oracle (structure-faithful port of the reference's Fortran) on `threads` host threads, each
-    assembling its own sample_grid block; returns cells/s for Jacobian+RHS, SpMV non-zeros/s, MGS-GMRES iteration
-    cost.  This is the one place outside tests/ that executes oracle/ (checker timed as the CPU baseline)."""
-    sys.path.insert(0, os.path.join(ROOT, "tests"))
-    import oracle_lib as ol
-    from iemic_b200 import grids
-    n, m, l = sample_grid
-    cfg = grids.global_config(n, m, l)
-    mask = grids.upsample_mask(grids.fixture_mask("mask_global_96x38x12"), n, m, l)
-    x = grids.synthetic_state(n, m, l, mask, seed=1)
-    res = [None] * threads
-
-    def work(t):
-        O = ol.Oracle(cfg, mask)
-        for k, v in grids.STARTING_PARS["global"].items():
-            O.set_par(k, v)
-        O.rhs(x); O.jac(x)  # warm-up
-        t0 = time.perf_counter(); cnt = 0
-        while True:
-            O.jac(x); O.rhs(x); cnt += 1
-            if time.perf_counter() - t0 > min_seconds:
+def probe_reference_toolchain():
+    """can the reference's own Fortran / Trilinos path be built on THIS box?  Probed at run time."""
+    import shutil
+    have = {t: bool(shutil.which(t)) for t in ("gfortran", "mpirun", "mpicxx", "cmake")}
+    epetra = False
+    for root in ("/usr/include", "/usr/local/include", "/opt"):
+        if not os.path.isdir(root):
+            continue
+        for dp, dn, fn in os.walk(root):
+            if dp.count(os.sep) > 6:
+                dn[:] = []
+            if "Epetra_CrsMatrix.h" in fn:
+                epetra = True
                 break
-        res[t] = (cnt, time.perf_counter() - t0)
+        if epetra:
+            break
+    have["Epetra_CrsMatrix.h"] = epetra
+    if have["gfortran"] and have["mpirun"] and epetra:
+        return "reference CPU path: toolchain present (gfortran, MPI, Trilinos) -- not built by this harness", have
+    missing = [k for k in ("gfortran", "mpirun", "Epetra_CrsMatrix.h") if not have[k]]
+    return "reference CPU path: not buildable on this box (missing: %s)" % ", ".join(missing), have
 
-    th = [threading.Thread(target=work, args=(t,)) for t in range(threads)]
-    t0 = time.perf_counter()
-    for t in th:
-        t.start()
-    for t in th:
-        t.join()
-    wall = time.perf_counter() - t0
-    cells = sum(r[0] for r in res) * n * m * l
-    secs = max(r[1] for r in res)
-    return cells / secs, wall
+
+def host_threads():
+    try:
+        n = len(os.sched_getaffinity(0))
+    except AttributeError:
+        n = os.cpu_count() or 1
+    return max(1, min(n, 64))
+
+
+class CpuArm:
+    """The reference's CPU algorithm on the STATED grid: the n x m x l problem is cut into `threads` blocks by the reference's own
+    Decomp2D rule, every block is padded with the two ghost layers the reference uses (TRIOS_Domain.C:182-189), and one instance of
+    the CPU oracle (oracle/: slot-for-slot port of the Fortran, including the row copy into the static graph of THCM.C:1074-1155)
+    assembles Jacobian + residual of its block on its own thread.  One step = the whole grid, wall clock, no extrapolation.
+    This is the one place outside tests/ that executes oracle/ (the checker, timed as the CPU baseline)."""
+
+    GHOST = 2
+
+    def __init__(self, grid, mask_kind, threads):
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import oracle_lib as ol
+        from iemic_b200 import grids
+        self.ol, self.grids = ol, grids
+        n, m, l = grid
+        self.grid, self.threads = grid, threads
+        self.cfg = grids.global_config(n, m, l)
+        self.mask = grids.synthetic_mask(n, m, l, kind=mask_kind)
+        self.x = grids.synthetic_state(n, m, l, self.mask).reshape(l, m, n, 6)
+        self.npN, self.npM = grids.decomp2d(n, m, threads)
+        self.blocks = []
+        for pm in range(self.npM):
+            for pn in range(self.npN):
+                self.blocks.append(self._block(pn, pm))
+        self.cells_with_ghosts = sum(b[0]["n"] * b[0]["m"] * l for b in self.blocks)
+        self.oracles = None
+
+    @staticmethod
+    def _split(n, parts, p):
+        base, rem = divmod(n, parts)
+        lo = p * base + min(p, rem)
+        return lo, lo + base + (1 if p < rem else 0)
+
+    def _block(self, pn, pm):
+        n, m, l = self.grid
+        g = self.GHOST
+        i0, i1 = self._split(n, self.npN, pn)
+        j0, j1 = self._split(m, self.npM, pm)
+        perio = bool(self.cfg["periodic"])
+        gw = g if (self.npN > 1 and (perio or pn > 0)) else 0
+        ge = g if (self.npN > 1 and (perio or pn < self.npN - 1)) else 0
+        gs = g if pm > 0 else 0
+        gn = g if pm < self.npM - 1 else 0
+        ii = np.arange(i0 - gw, i1 + ge) % n                       # owned + ghost columns (wrapped)
+        jj = np.arange(j0 - gs, j1 + gn)
+        nb, mb = ii.size, jj.size
+        sub = np.ones((l + 2, mb + 2, nb + 2), np.int32)
+        ring_i = np.concatenate(([ii[0] - 1], ii, [ii[-1] + 1])) % n
+        ring_j = np.clip(np.concatenate(([jj[0] - 1], jj, [jj[-1] + 1])), -1, m)
+        full = self.mask
+        sub[:, :, :] = full[np.ix_(np.arange(l + 2), ring_j + 1, ring_i + 1)]
+        block_periodic = perio and self.npN == 1
+        if not block_periodic:                                       # a cut side is a wall for the sub-domain (usrc.F90:96-107)
+            sub[:, :, 0] = 1; sub[:, :, -1] = 1
+        sub[:, 0, :] = np.where(jj[0] == 0, sub[:, 0, :], 1); sub[:, -1, :] = np.where(jj[-1] == m - 1, sub[:, -1, :], 1)
+        cfg = dict(self.cfg)
+        dx = (self.cfg["xmax"] - self.cfg["xmin"]) / n
+        dy = (self.cfg["ymax"] - self.cfg["ymin"]) / m
+        cfg.update(n=nb, m=mb, xmin=self.cfg["xmin"] + (i0 - gw) * dx, xmax=self.cfg["xmin"] + (i1 + ge) * dx,
+                   ymin=self.cfg["ymin"] + (j0 - gs) * dy, ymax=self.cfg["ymin"] + (j1 + gn) * dy, periodic=int(block_periodic))
+        xs = np.ascontiguousarray(self.x[np.ix_(np.arange(l), jj, ii, np.arange(6))]).ravel()
+        return cfg, sub, xs
+
+    def bytes_needed(self):
+        return int(self.cells_with_ghosts * 21e3)                     # An + Al (2 x 972 doubles per cell) + CSR + fields
+
+    def setup(self):
+        """one oracle per block, created on its own thread (Al is built here: parameter-change cost, not assembly cost)"""
+        pars = self.grids.STARTING_PARS["global"]
+        self.oracles = [None] * len(self.blocks)
+
+        def mk(t):
+            cfg, sub, xs = self.blocks[t]
+            O = self.ol.Oracle(cfg, sub)
+            for k, v in pars.items():
+                O.set_par(k, v)
+            self.oracles[t] = O
+
+        self._run(mk)
+
+    def _run(self, fn):
+        th = [threading.Thread(target=fn, args=(t,)) for t in range(len(self.blocks))]
+        t0 = time.perf_counter()
+        for t in th:
+            t.start()
+        for t in th:
+            t.join()
+        return time.perf_counter() - t0
+
+    def step(self):
+        """one Jacobian + residual assembly of the whole grid; returns wall seconds"""
+        def work(t):
+            O, xs = self.oracles[t], self.blocks[t][2]
+            O.jac(xs)
+            O.rhs(xs)
+
+        return self._run(work)
+
+    def describe(self):
+        n, m, l = self.grid
+        return ("oracle port (kind=port), %dx%dx%d cut by Decomp2D into %dx%d blocks (+%d ghost layers: %d cells assembled for %d owned), one block per host "
+                "thread, %d threads; each step assembles the WHOLE grid (Jacobian incl. the row copy into the static graph + residual), wall clock"
+                % (n, m, l, self.npN, self.npM, self.GHOST, self.cells_with_ghosts, n * m * l, self.threads))
+
+
+def cpu_arm_for(grid, mask_kind, threads):
+    """CpuArm sized to the memory of this box: fewer threads (= fewer, larger blocks) never needs more memory, so only refuse when even
+    the bare grid does not fit"""
+    arm = CpuArm(grid, mask_kind, threads)
+    try:
+        import psutil
+        avail = psutil.virtual_memory().available
+    except Exception:
+        avail = None
+    if avail is not None and arm.bytes_needed() > 0.9 * avail:
+        raise MemoryError("CPU oracle needs about %.0f GB for this grid, %.0f GB available" % (arm.bytes_needed() / 1e9, avail / 1e9))
+    return arm
 
 
 def run_reference(args):
     """--impl reference: the reference's CPU algorithm for the path (oracle port; the Fortran/Trilinos original is not
-    buildable: no Fortran compiler, MPI or Trilinos in the image) on all usable host threads."""
+    buildable: no Fortran compiler, MPI or Trilinos in the image) on all usable host threads, on the stated grid."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     n, m, l = [int(v) for v in args.grid.split("x")]
     ncell = n * m * l
-    threads = max(1, min(os.cpu_count() or 1, 32))
-    per_step = max(2.0, min(10.0, 120.0 / max(1, args.steps + args.warmup)))
-    for _ in range(min(args.warmup, 1)):
-        cpu_sample(threads, min_seconds=1.0)
-    vals = []
+    threads = host_threads()
+    probe, _ = probe_reference_toolchain()
+    t_all = time.perf_counter()
+    arm = cpu_arm_for((n, m, l), args.mask, threads)
     t0 = time.perf_counter()
-    for _ in range(max(1, min(args.steps, 5))):
-        cps, _ = cpu_sample(threads, min_seconds=per_step)
-        vals.append(cps / ncell)
-    v = float(np.mean(vals))
-    sample = "each step: %d host threads x one 48x19x12-cell block (oracle port, Jacobian+RHS), extrapolated by cell count to %s" % (threads, args.grid)
+    arm.setup()
+    setup_s = time.perf_counter() - t0
+    budget = 170.0                                                     # seconds of timed + warm-up steps
+    first = arm.step()                                                 # warm-up step, also sizes the run
+    warm = max(0, min(args.warmup, int(0.25 * budget / max(first, 1e-3))) - 1)
+    for _ in range(warm):
+        arm.step()
+    steps = max(1, min(args.steps, int(0.75 * budget / max(first, 1e-3))))
+    secs = [arm.step() for _ in range(steps)]
+    v = steps / sum(secs)
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": 1000.0 / v, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "steps_run": steps, "warmup_run": warm + 1, "ms_per_step": 1000.0 / v, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
             "config": {"workload": "synthetic global 1-degree ocean %s (BASELINE config 4): Jacobian+RHS assembly per step" % args.grid,
                        "grid": args.grid, "unknowns": 6 * ncell, "mask": args.mask},
-            "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port", "sample": arm.describe()},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "gpu_launches": 0, "wall_s": time.perf_counter() - t0}
+            "same_config": True, "extrapolated": False, "step_seconds": {"min": min(secs), "median": float(np.median(secs)), "max": max(secs)},
+            "setup_seconds": setup_s, "reference_toolchain": probe,
+            "note": "the port omits nothing of THCM::evaluate's Jacobian branch except Epetra's FillComplete; ghost cells are assembled and discarded like the reference does",
+            "gpu_launches": 0, "wall_s": time.perf_counter() - t_all}
     print(json.dumps(line))
+
+
+PARITY_REF = os.path.join(ROOT, "tests", "golden", "bench_parity_ref.json")
+
+
+def check_parity(p, args, world):
+    """compares the run's decomposition-invariant numbers with the committed one-GPU values (tests/golden/bench_parity_ref.json:
+    F_norm2 there is the CPU ORACLE's value from tests/golden/global1deg_golden.npz; J1 and the GMRES history were taken on one B200)"""
+    try:
+        ref = json.load(open(PARITY_REF))["%s/%s/m%d" % (args.grid, args.mask, args.gmres_m)]
+    except Exception:
+        return {"status": "no reference for this workload", "tol": None}
+    out = {"status": "ok", "tol": {"norms": 1e-8, "gmres_hist": 1e-6}, "rel_dev": {}}
+    for k, tol in (("F_norm2", 1e-8), ("J1_norm2", 1e-8)):
+        d = abs(p[k] - ref[k]) / abs(ref[k])
+        out["rel_dev"][k] = d
+        if not d <= tol:
+            out["status"] = "FAILED"
+    if "gmres_hist" in p and "gmres_hist" in ref:
+        a, b = np.array(p["gmres_hist"]), np.array(ref["gmres_hist"])
+        d = float(np.max(np.abs(a - b) / np.abs(b))) if a.shape == b.shape else float("inf")
+        out["rel_dev"]["gmres_hist"] = d
+        if not d <= 1e-6:
+            out["status"] = "FAILED"
+    return out
 
 
 # ---------------------------------------------------------------------------------------------------------
@@ -254,12 +401,55 @@ def main():
     def step_e2e():
         G.assemble_host(x_pin_np, F_pin_np, jacobian=True)
 
+    # ---- parity gate (the reference's I5 idiom, src/tests/test_matrix.C:148-192): decomposition-invariant numbers of THIS run's
+    # distributed path, compared with the committed one-GPU values before anything is timed
+    def gsum(t):
+        if world > 1:
+            dist.all_reduce(t)
+        return float(t.item())
+
+    ones = torch.ones(G.nvec, dtype=torch.float64, device="cuda")
+    y = torch.zeros(G.nvec, dtype=torch.float64, device="cuda")
+    G.assemble(dx, dF, jacobian=True)
+    G.sync()
+    F_norm = gsum((dF[:G.nrows] ** 2).sum()) ** 0.5
+    G.applyMatrix(ones, y)
+    G.sync()
+    J1_norm = gsum((y[:G.nrows] ** 2).sum()) ** 0.5
+    parity = {"F_norm2": F_norm, "J1_norm2": J1_norm}
+    if not args.skip_gmres:
+        xs0 = torch.zeros(G.nvec, dtype=torch.float64, device="cuda")
+        rc_p, hist_p, it_p = G.solve(y.clone(), xs0, m=args.gmres_m, maxit=args.gmres_m - 1, tol=0.0, ortho=ib.CGS2F, check_every=0)
+        parity["gmres_hist"] = [float(v) for v in hist_p[:args.gmres_m][::5]] + [float(hist_p[args.gmres_m - 1])]
+        del xs0
+    if args.write_parity_ref and world == 1 and rank == 0:
+        key = "%s/%s/m%d" % (args.grid, args.mask, args.gmres_m)
+        ref_all = json.load(open(PARITY_REF)) if os.path.exists(PARITY_REF) else {}
+        entry = dict(parity, source="J1_norm2 and gmres_hist: bench.py --write-parity-ref on one B200")
+        gold = os.path.join(ROOT, "tests", "golden", "global1deg_golden.npz")
+        if args.grid == "360x160x32" and args.mask == "global" and os.path.exists(gold):
+            oracle_norm = float(np.load(gold)["norms"][0])
+            entry["F_norm2_this_run"] = entry["F_norm2"]
+            entry["F_norm2"] = oracle_norm
+            entry["source"] += "; F_norm2: CPU oracle (tests/golden/global1deg_golden.npz)"
+        ref_all[key] = entry
+        json.dump(ref_all, open(PARITY_REF, "w"), indent=1)
+    parity.update(check_parity(parity, args, world))
+    if parity["status"] == "FAILED":
+        if rank == 0:
+            print(json.dumps({"metric": METRIC, "value": None, "unit": UNIT, "n_gpus": world, "parity": parity,
+                              "error": "parity gate failed: the distributed path does not reproduce the committed one-GPU numbers"}))
+        if world > 1:
+            dist.destroy_process_group()
+        raise SystemExit(3)
+
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
     l0 = G.launch_count()
     ms_dev = timed(step_dev, args.steps, args.warmup)
     launches = (G.launch_count() - l0) * args.steps // (args.steps + args.warmup)
+    reps_ms = [ms_dev / args.steps] + [timed(step_dev, args.steps, 0) / args.steps for _ in range(4)]   # run-to-run noise of the same loop
     ms_e2e = timed(step_e2e, args.steps, max(1, args.warmup))
 
     # kernel-level durations (CUDA events on the launching stream, bracketing each kernel), same region re-run
@@ -272,11 +462,11 @@ def main():
     timed(step_seq, args.steps, 1)
     t_jac, c_jac = G.timing_get(1)
     t_rhs, c_rhs = G.timing_get(0)
+    timed(step_dev, args.steps, 1)        # the step's own kernel: Jacobian + residual fused in one launch
+    t_asm, c_asm = G.timing_get(4)
     G.timing(False)
 
     # SpMV alone
-    ones = torch.ones(G.nvec, dtype=torch.float64, device="cuda")
-    y = torch.zeros(G.nvec, dtype=torch.float64, device="cuda")
     ms_spmv = timed(lambda: G.applyMatrix(ones, y), max(args.steps, 20), args.warmup)
     nsp = max(args.steps, 20)
 
@@ -337,12 +527,16 @@ def main():
     value = 1000.0 / ms_step
     jac_ms = t_jac / max(c_jac, 1)
     rhs_ms = t_rhs / max(c_rhs, 1)
-    achieved = jac_b / world / (jac_ms * 1e-3) / 1e9  # per GPU (max-rank time approximated by rank 0's kernel time)
-    traffic = None  # DRAM bytes of one jac_kernel launch from the committed ncu capture, when it is this workload
+    asm_ms = t_asm / max(c_asm, 1)
+    # dominant kernel of the step: asm_kernel<JAC,RHS> (one launch per step): 1080 B per cell
+    achieved = (jac_b + rhs_b) / world / (asm_ms * 1e-3) / 1e9  # per GPU (max-rank time approximated by rank 0's kernel time)
+    traffic, traffic_src = None, None  # DRAM bytes of one launch from the committed ncu capture -- only if taken from THIS kernel source
     try:
-        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["jac_kernel"]
-        if tj["grid"] == args.grid and tj["n_gpus"] == world and args.mask == "global":
-            traffic = tj["dram_bytes_per_launch"]
+        import hashlib
+        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["asm_kernel"]
+        sha = hashlib.sha256(open(os.path.join(ROOT, "iemic_b200", "csrc", "thcm_kernels.cu"), "rb").read()).hexdigest()[:16]
+        if tj["grid"] == args.grid and tj["n_gpus"] == world and args.mask == "global" and tj.get("source_sha") == sha:
+            traffic, traffic_src = tj["dram_bytes_per_launch"], tj.get("capture")
     except Exception:
         pass
     line = {
@@ -353,10 +547,14 @@ def main():
                    "grid": args.grid, "unknowns": nrows_g, "nnz": nnz_g, "mask": args.mask, "decomposition": "%dx%d lon x lat" % G.block()[4:6],
                    "l2": "inputs larger than L2 (CSR %.2f GB), no flush" % (12 * nnz_g / 1e9), "gmres_m": args.gmres_m,
                        "exchange": {0: "none (one GPU)", 1: "NCCL send/recv + allreduce", 2: "peer memory over NVLink (CUDA IPC), NCCL bootstrap only"}[G.exchange_mode()]},
-        "roofline": {"bound": "hbm", "kernel": "jac_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": traffic, "peak_kind": peak_kind, "algorithmic_bytes_per_launch": jac_b // world, "kernel_ms": jac_ms,
-                     "rhs_kernel_ms": rhs_ms, "rhs_frac": rhs_b / world / (rhs_ms * 1e-3) / 1e9 / peak,
+        "roofline": {"bound": "hbm", "kernel": "asm_kernel<JAC,RHS> (Jacobian + residual, one launch per step)", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_kind": peak_kind,
+                     "algorithmic_bytes_per_launch": (jac_b + rhs_b) // world, "kernel_ms": asm_ms,
+                     "jacobian_alone_ms": jac_ms, "jacobian_alone_frac": jac_b / world / (jac_ms * 1e-3) / 1e9 / peak,
+                     "residual_alone_ms": rhs_ms, "residual_alone_frac": rhs_b / world / (rhs_ms * 1e-3) / 1e9 / peak,
                      "step_frac": (jac_b + rhs_b) / (ms_step * 1e-3) / 1e9 / peak_total},
+        "repeat": {"loops": len(reps_ms), "ms_per_step_min": min(reps_ms), "ms_per_step_median": float(np.median(reps_ms)), "ms_per_step_max": max(reps_ms)},
+        "parity": parity,
         "e2e": {"value": 1000.0 / (ms_e2e / args.steps), "unit": UNIT, "h2d_bytes_per_step": 8 * nrows_g,
                 "d2h_bytes_per_step": 8 * nrows_g, "api": "thcm_b200_assemble_host: state up from pinned host memory, residual back, Jacobian device-resident like Ocean::jac_"},
         "spmv": {"gbs": spmv_b / (ms_spmv / nsp * 1e-3) / 1e9, "ms": ms_spmv / nsp, "frac": spmv_b / (ms_spmv / nsp * 1e-3) / 1e9 / peak_total,
@@ -370,12 +568,16 @@ def main():
         line["gmres"] = {"iters_per_s": args.gmres_m / (ms_cycle * 1e-3), "ms_per_cycle": ms_cycle, "m": args.gmres_m, "ortho": "CGS2 (two reductions per step, fused normalisation)",
                          "frac": cycle_b / (ms_cycle * 1e-3) / 1e9 / peak_total, "algorithmic_bytes_per_cycle": cycle_b,
                          "orth_ms_per_step_avg": orth_ms, "spmv_ms": sp_ms}
-    if not args.no_cpu_baseline:
+    line["reference_toolchain"] = probe_reference_toolchain()[0]
+    if not args.no_cpu_baseline and world == 1:
         try:
-            cps, wall = cpu_sample(1, min_seconds=10.0)
-            line["cpu_baseline"] = {"value": cps / ncell_g, "unit": UNIT, "cores": 1, "kind": "port",
-                                    "sample": "oracle port, Jacobian+RHS on one 48x19x12-cell block for %.0f s on 1 core, extrapolated by cell count" % wall}
-        except Exception as e:  # the checker is missing: report, do not fake
+            threads = host_threads()
+            arm = cpu_arm_for((n, m, l), args.mask, threads)
+            arm.setup()
+            sec = arm.step()
+            line["cpu_baseline"] = {"value": 1.0 / sec, "unit": UNIT, "cores": threads, "kind": "port",
+                                    "sample": "ONE whole-grid assembly (%.1f s wall): %s" % (sec, arm.describe())}
+        except Exception as e:  # the checker is missing or does not fit: report, do not fake
             line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "port", "sample": "unavailable: %s" % e}
     print(json.dumps(line))
     if world > 1:

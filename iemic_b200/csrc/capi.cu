@@ -273,8 +273,19 @@ int spmv_impl(thcm_b200* h, double* d_x, double* d_y) {
     launch_spmv(p, h->d_rowptr, h->d_col, h->d_val, d_x, d_y, h->stream);
     h->launches++;
   }
-  // TODO(dist): dense integral row spans all ranks; handled by dist_intcond_row when SRES=0 and nranks>1
-  return check_launch(h, "spmv");
+  if (int rc = check_launch(h, "spmv")) return rc;
+  // Dense salinity-integral row on several GPUs (THCM.C:2494-2513): the owner's CSR row holds the columns it owns,
+  // every other rank contributes sum coef*x over its own S unknowns through one all-reduced double.
+  Host* H = h->host;
+  if (h->dist && H->cfg.sres == 0 && H->rowintcon >= 0) {
+    double* part = h->d_small + 1091;
+    if (H->owns_rowintcon) { CU(cudaMemsetAsync(part, 0, sizeof(double), h->stream)); }
+    else { launch_intcond_dot(h->d_coefS, d_x, h->nrows() / 6, part, h->stream); h->launches++; }
+    if (int rc = allreduce(h, part, 1)) return rc;
+    if (H->owns_rowintcon) { launch_intcond_add(part, (double)H->cfg.int_sign, d_y, H->rowintcon_local, h->stream); h->launches++; }
+    return check_launch(h, "spmv integral row");
+  }
+  return 0;
 }
 } // namespace
 

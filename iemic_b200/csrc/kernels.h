@@ -35,6 +35,7 @@ int asm_smem_bytes();
 // finished (after the optional allreduce) by intcond_finish.
 void launch_intcond_dot(const double* coefS, const double* x, long long ncell, double* partial /* 1 double */, cudaStream_t st);
 void launch_intcond_finish(const double* dotval, double sign, double corr, double* F, int row, int rowPfix1, int rowPfix2, cudaStream_t st);
+void launch_intcond_add(const double* dotval, double sign, double* y, int row, cudaStream_t st); // y[row] += sign * dotval (other ranks' share of the dense row)
 
 // ---- CSR SpMV (spmv.cu) ----
 // Most cells of the static THCM graph are "regular": all 27 neighbours stored, so the 104 columns of the cell's six rows

@@ -40,7 +40,6 @@ Host::Host(const Config& c, const int* landm_in, int rank_, int nranks_) : cfg(c
   ndim = 6 * ncell;
   decompose();
   if (105ull * (size_t)nloc * mloc * l > 0x7fffffffull) throw std::runtime_error("thcm_b200: sub-domain too large for 32-bit CSR offsets");
-  if (nranks > 1 && cfg.sres == 0 && cfg.intcond_i != -2) throw std::runtime_error("thcm_b200: the dense salinity-integral row (SRES=0) is only supported on a single GPU");
   version = 1; mask_version = 0; intCorrection = 0.0;
   make_grid();
   stpnt();
@@ -544,10 +543,16 @@ template <int A> static void graph_row(const Scalars& S, const Cell& c, std::vec
       cnt++;
     }
   }
-  if (row_has_seam(S, c)) { // single rank in x: stored index == global index order, sort like the global graph
-    std::sort(cols, cols + cnt);
+  if (row_has_seam(S, c)) { // single rank in x: order the row like the global graph (= the order the kernels' seam emit uses).
+    // Sorted by GLOBAL column: with several ranks in y the north / south neighbours of a block's edge rows sit in the halo ring,
+    // whose stored indices follow all owned cells.
+    int ord[Row<A>::NE];
+    for (int q = 0; q < cnt; q++) ord[q] = q;
+    std::sort(ord, ord + cnt, [&](int a, int b) { return gcols[a] < gcols[b]; });
+    int tmp[Row<A>::NE];
+    for (int q = 0; q < cnt; q++) tmp[q] = cols[ord[q]];
+    for (int q = 0; q < cnt; q++) cols[q] = tmp[q];
   }
-  (void)gcols;
   col.insert(col.end(), cols, cols + cnt);
 }
 void Host::build_graph() {

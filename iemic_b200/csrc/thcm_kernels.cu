@@ -499,6 +499,8 @@ __global__ void intcond_finish_kernel(const double* dotval, double sign, double 
   if (p2 >= 0) F[p2] = 0.0;
 }
 
+__global__ void intcond_add_kernel(const double* dotval, double sign, double* y, int row) { y[row] = y[row] + sign * (*dotval); }
+
 template <bool JAC, bool RHS> constexpr int asm_smem() {
   return ((RHS ? 9 : 5) * TCELLS + (JAC ? NWARP * 32 * STRIDE + 3 * CELL_NNZ : 0)) * (int)sizeof(double);
 }
@@ -530,6 +532,7 @@ void launch_asm(const AsmArgs& a, cudaStream_t st) { launch_asm_t<true, true>(a,
 void launch_intcond_dot(const double* coefS, const double* x, long long ncell, double* partial, cudaStream_t st) {
   intcond_dot_kernel<<<1, 1024, 0, st>>>(coefS, x, ncell, partial);
 }
+void launch_intcond_add(const double* dotval, double sign, double* y, int row, cudaStream_t st) { intcond_add_kernel<<<1, 1, 0, st>>>(dotval, sign, y, row); }
 void launch_intcond_finish(const double* dotval, double sign, double corr, double* F, int row, int p1, int p2, cudaStream_t st) {
   intcond_finish_kernel<<<1, 1, 0, st>>>(dotval, sign, corr, F, row, p1, p2);
 }

@@ -26,6 +26,12 @@ def case(name):
     if name == "2dmoc_run":    # run/2dmoc: 4x32x16
         cfg = g.moc2d_config(4, 32, 16)
         return cfg, g.no_land_mask(4, 32, 16, True), dict(g.STARTING_PARS["2dmoc"], COMB=0.5, SALT=0.2)
+    if name == "2dmoc_sres1":  # periodic in x inside ONE rank with the ranks stacked in y (seam rows next to halo rows)
+        cfg = g.moc2d_config(3, 6, 6, sres=1)
+        return cfg, g.no_land_mask(3, 6, 6, True), dict(g.STARTING_PARS["2dmoc"], COMB=0.5, SALT=0.2)
+    if name == "2dmoc_run_sres1":
+        cfg = g.moc2d_config(4, 32, 16, sres=1)
+        return cfg, g.no_land_mask(4, 32, 16, True), dict(g.STARTING_PARS["2dmoc"], COMB=0.5, SALT=0.2)
     if name == "rand_periodic":
         cfg = g.global_config(37, 11, 7, ymin=-60, ymax=60)
         return cfg, g.random_mask(37, 11, 7, True, 5), dict(g.STARTING_PARS["global"])

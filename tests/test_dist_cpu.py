@@ -51,7 +51,7 @@ def _assemble(name, nranks):
 
 
 @pytest.mark.parametrize("name,nranks", [("rand_periodic", 2), ("rand_periodic", 4), ("rand_periodic", 8), ("rand_box", 2), ("rand_box", 6),
-                                         ("global_half", 8), ("coupled4", 4), ("natl8_sres1", 4)])
+                                         ("global_half", 8), ("coupled4", 4), ("natl8_sres1", 4), ("2dmoc_sres1", 2), ("2dmoc_run_sres1", 4)])
 def test_rank_pieces_reproduce_the_global_problem(name, nranks):
     cfg, O, x, F, B, rows_g, cols_g, vals_g = _assemble(name, nranks)
     assert np.array_equal(F, O.rhs(x))
@@ -86,10 +86,56 @@ def test_decomposition_matches_reference_rule():
         assert cells == cfg["n"] * cfg["m"]
 
 
-def test_sres0_multirank_fails_loudly():
+def test_decomposition_literal_table():
+    """Decomp2D results worked out BY HAND from the reference's loop (src/trios/TRIOS_Domain.C:88-108: scan t1 = nprocs..1,
+    t2 = nprocs/t1, keep the LAST pair with t1*t2 == nprocs and |m/t1 - n/t2| <= r_min, r_min starting at 100), as npN x npM."""
+    from iemic_b200 import grids
+    table = {
+        (360, 160): {1: (1, 1), 2: (2, 1), 4: (4, 1), 6: (3, 2), 8: (4, 2)},
+        (96, 38): {1: (1, 1), 2: (2, 1), 4: (4, 1), 8: (4, 2)},
+        (48, 19): {2: (2, 1), 4: (4, 1), 8: (4, 2)},
+    }
+    for (n, m), rows in table.items():
+        for nranks, want in rows.items():
+            assert grids.decomp2d(n, m, nranks) == want, (n, m, nranks)
+    # the product's C++ side (thcm::Host) must give the same blocks
+    cfg, mask, pars = cases.case("global_half")
+    for nranks, (npN, npM) in table[(48, 19)].items():
+        H = hl.HostCheck(cfg, mask, rank=nranks - 1, nranks=nranks)
+        assert H.block()[4:6] == (npN, npM)
+    # offsets and sizes of the last block: remainders go to the first ranks (TRIOS_Domain.C:137-153); 48 = 4 x 12, 19 = 10 + 9
+    H = hl.HostCheck(cfg, mask, rank=7, nranks=8)
+    assert H.block()[:4] == (36, 10, 12, 9)
+
+
+def test_sres0_multirank_dense_row_is_split_by_owner():
+    """SRES = 0 on several ranks (THCM.C:2494-2513, the reference's partest_matrix idiom): the rank that owns the integral row keeps
+    it in its pattern with the S unknowns it owns; the other ranks' share reaches it through one all-reduced double (capi.cu
+    spmv_impl / rhs_epilogue), so no rank stores a column it does not hold."""
     cfg, mask, pars = cases.case("natl8")
-    with pytest.raises(RuntimeError):
-        hl.HostCheck(cfg, mask, rank=0, nranks=2)
+    O = ol.Oracle(cfg, mask)
+    rpo, colo = O.graph()
+    dense = int(np.argmax(np.diff(rpo)))
+    assert dense == O.rowintcon()
+    for nranks in (2, 4, 8):
+        owners = 0
+        for r in range(nranks):
+            H = hl.HostCheck(cfg, mask, rank=r, nranks=nranks)
+            gid = H.gid()
+            rp, col = H.graph()
+            assert np.all(gid[col] >= 0)
+            lens = np.diff(rp)
+            rows = gid[:H.ndim]
+            if dense in rows:
+                owners += 1
+                lr = int(np.flatnonzero(rows == dense)[0])
+                assert H.rowintcon() == dense                                                # the GLOBAL row index, on every rank
+                cols = gid[col[rp[lr]:rp[lr + 1]]]
+                assert np.array_equal(np.sort(cols), np.sort(rows[rows % 6 == 5]))          # exactly the S unknowns this rank owns
+                assert set(cols.tolist()) <= set(colo[rpo[dense]:rpo[dense + 1]].tolist())
+            else:
+                assert H.rowintcon() == dense and lens.max() <= 24
+        assert owners == 1
 
 
 def test_gloo_world2_halo_exchange():

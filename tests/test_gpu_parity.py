@@ -263,6 +263,51 @@ def test_full_size_properties():
     assert it == 10 and np.all(np.diff(hh) <= 1e-12) and hh[-1] < 1.0
 
 
+def test_full_size_against_oracle_golden():
+    """BASELINE config 4 itself (360x160x32, the bench's state and parameters) against the CPU oracle: the oracle's residual and
+    Jacobian were reduced to per-level SHA-256 digests of everything that must be bit-identical plus a strided sample of the
+    tanh-carrying values (tests/golden/make_1deg_golden.py -> global1deg_golden.npz).  Covers the tile / edge regimes the small
+    cases do not reach (12 i-tiles with an 8-wide remainder, land tiles that stage nothing, vector and bulk copy-out)."""
+    import os
+    import sys
+    import torch
+    import iemic_b200 as ib
+    from iemic_b200 import grids
+    gdir = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    gold = np.load(os.path.join(gdir, "global1deg_golden.npz"))
+    sys.path.insert(0, gdir)
+    import make_1deg_golden as mk
+    n, m, l = mk.N, mk.M, mk.L
+    cfg = grids.global_config(n, m, l)
+    mask = grids.synthetic_mask(n, m, l)
+    G = ib.Ocean(cfg, mask)
+    for k, v in grids.STARTING_PARS["global"].items():
+        G.setPar(k, v)
+    x = grids.synthetic_state(n, m, l, mask)
+    rp, col = G.graph()
+    for mode in ("separate", "fused"):
+        if mode == "separate":
+            F = G.computeRHS_host(x)
+            val, diagB = G.computeJacobian_host(x)
+        else:
+            G.set_values_host(np.full(G.nnz, 777.0))
+            dx = torch.from_numpy(x).cuda()
+            dF = torch.full((G.nvec,), 555.0, dtype=torch.float64, device="cuda")
+            G.assemble(dx, dF, jacobian=True)
+            G.sync()
+            F = dF[:G.nrows].cpu().numpy()
+            val, diagB = G.values_host()
+        d = mk.reduce_case(F, val, diagB, rp, col, n, m, l)
+        assert np.array_equal(d["graph_sha"], gold["graph_sha"]), mode
+        for key in ("F_exact_sha", "B_sha", "J_exact_sha"):
+            bad = np.flatnonzero(d[key] != gold[key])
+            assert bad.size == 0, (mode, key, "levels (0-based) that differ", bad.tolist())
+        assert np.array_equal(d["F_idx"], gold["F_idx"]) and np.array_equal(d["J_idx"], gold["J_idx"])
+        assert np.abs(d["F_val"] - gold["F_val"]).max() <= 1e-12 * gold["norms"][1], mode
+        assert (np.abs(d["J_val"] - gold["J_val"]) / np.maximum(gold["J_rowscale"], 1e-300)).max() <= 1e-6, mode
+        assert abs(d["norms"][0] - gold["norms"][0]) <= 1e-12 * gold["norms"][0]
+
+
 def test_assemble_host_equals_separate_calls():
     cfg, mask, O, G = cases.make_pair("global4")
     x = cases.state(cfg, mask, seed=10)
