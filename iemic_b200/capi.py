@@ -26,7 +26,8 @@ PAR = dict(AL_T=1, RAYL=2, EK_V=3, EK_H=4, ROSB=5, MIXP=6, RESC=7, SPL1=8, HMTP=
            IFRICB=22, CONT=23, ENER=24, ALPC=25, CMPR=26, FPER=27, SPER=28, MKAP=29, SPL2=30)
 
 MGS, CGS2, CGS2F = 0, 1, 2
-PREC_NONE, PREC_BLOCKJACOBI = 0, 1
+PREC_NONE, PREC_BLOCKJACOBI, PREC_CALLBACK = 0, 1, 2
+PRECOND_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p)
 
 
 class Config(C.Structure):
@@ -74,7 +75,8 @@ def lib():
             "thcm_b200_assemble_host": [vp, vp, vp, C.c_int], "thcm_b200_assemble": [vp, vp, vp, C.c_int], "thcm_b200_exchange_mode": [vp],
             "thcm_b200_spmv": [vp, vp, vp], "thcm_b200_spmv_host": [vp, vp, vp],
             "vec_b200_dot": [vp, vp, vp, dp], "vec_b200_norm2": [vp, vp, dp],
-            "vec_b200_dot_noalloc": [vp, vp, C.c_int64, vp, vp],
+            "vec_b200_dot_noalloc": [vp, vp, C.c_int64, vp, vp], "vec_b200_norminf": [vp, vp, dp],
+            "thcm_b200_upload": [vp, vp, vp, C.c_int64], "thcm_b200_download": [vp, vp, vp, C.c_int64],
             "vec_b200_update": [vp, C.c_double, vp, C.c_double, vp], "vec_b200_scale": [vp, C.c_double, vp],
             "vec_b200_putscalar": [vp, C.c_double, vp],
             "vec_b200_multiply": [vp, C.c_double, vp, vp, C.c_double, vp], "vec_b200_reciprocal": [vp, vp, vp],
@@ -82,6 +84,7 @@ def lib():
             "thcm_b200_left_scale": [vp, vp], "thcm_b200_block_jacobi": [vp, vp, ip],
             "gmres_b200_solve": [vp, vp, vp, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int, vp, C.c_int, dp, ip],
             "gmres_b200_solve_host": [vp, vp, vp, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int, vp, C.c_int, dp, ip],
+            "gmres_b200_set_precond": [vp, PRECOND_FN, vp], "vec_b200_block_jacobi_apply": [vp, vp, vp, vp],
             "thcm_b200_launch_count": [vp, i64p], "thcm_b200_timing_enable": [vp, C.c_int],
             "thcm_b200_timing_reset": [vp], "thcm_b200_timing_get": [vp, C.c_int, dp, i64p],
             "iemic_b200_malloc": [C.POINTER(vp), C.c_int64], "iemic_b200_free": [vp],
@@ -103,10 +106,10 @@ EXPORTED = ["iemic_b200_last_error", "iemic_b200_version", "iemic_b200_device_co
             "thcm_b200_rhs", "thcm_b200_jacobian", "thcm_b200_halo_exchange", "thcm_b200_csr", "thcm_b200_graph_host",
             "thcm_b200_values_host", "thcm_b200_set_values_host", "thcm_b200_forcing_host", "thcm_b200_intcond_host",
             "thcm_b200_rhs_host", "thcm_b200_jacobian_host", "thcm_b200_assemble_host", "thcm_b200_assemble", "thcm_b200_exchange_mode", "thcm_b200_spmv", "thcm_b200_spmv_host",
-            "vec_b200_dot", "vec_b200_dot_noalloc", "vec_b200_norm2", "vec_b200_update", "vec_b200_scale", "vec_b200_putscalar",
+            "vec_b200_dot", "vec_b200_dot_noalloc", "vec_b200_norm2", "vec_b200_norminf", "thcm_b200_upload", "thcm_b200_download", "vec_b200_update", "vec_b200_scale", "vec_b200_putscalar",
             "vec_b200_multiply", "vec_b200_reciprocal", "thcm_b200_average_block", "thcm_b200_scal", "thcm_b200_recompute_scaling",
             "thcm_b200_left_scale", "thcm_b200_block_jacobi",
-            "gmres_b200_solve", "gmres_b200_solve_host", "thcm_b200_launch_count", "thcm_b200_timing_enable",
+            "gmres_b200_solve", "gmres_b200_solve_host", "gmres_b200_set_precond", "vec_b200_block_jacobi_apply", "thcm_b200_launch_count", "thcm_b200_timing_enable",
             "thcm_b200_timing_reset", "thcm_b200_timing_get", "iemic_b200_malloc", "iemic_b200_free",
             "iemic_b200_memcpy_h2d", "iemic_b200_memcpy_d2h"]
 
@@ -297,6 +300,11 @@ class Ocean:
         rc = check(lib().gmres_b200_solve(self.h, _ptr(d_b), _ptr(d_x), m, maxit, tol, ortho, prec, _ptr(d_blockinv), check_every,
                                           hist.ctypes.data_as(C.POINTER(C.c_double)), C.byref(it)))
         return rc, hist, it.value
+
+    def set_precond(self, fn):
+        """fn(d_v_ptr, d_z_ptr, n, stream_ptr) -> int: the right preconditioner z = M^-1 v used with prec=PREC_CALLBACK (None: remove)"""
+        self._precond_cb = PRECOND_FN(lambda user, v, z, n, st: int(fn(v, z, n, st) or 0)) if fn is not None else C.cast(None, PRECOND_FN)
+        check(lib().gmres_b200_set_precond(self.h, self._precond_cb, None))
 
     def dot(self, d_a, d_b):
         r = C.c_double()

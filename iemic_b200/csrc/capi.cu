@@ -67,6 +67,7 @@ struct thcm_b200 {
   double* d_small = nullptr; // [0,512) h1, [512,1024) h2, 1024 nrm2, 1025 hnext, 1026 bnorm, 1027 beta, 1028 dot, 1029 intcond,
                              // [1030,1067) average block + count, [1070,1088) Fortran-level centre entries of the special rows, 1090 int counter
   GmresWs g;
+  gmres_b200_precond_fn precond = nullptr; void* precond_user = nullptr; // right preconditioner supplied by the caller (GMRES_B200_PREC_CALLBACK)
   long long launches = 0;
   bool timing = false;
   std::vector<TimedEv> evs;
@@ -346,7 +347,12 @@ int thcm_b200_destroy(thcm_b200_t* h) {
   return 0;
 }
 int thcm_b200_set_stream(thcm_b200_t* h, void* s) { CHECK_H(h); h->stream = (cudaStream_t)s; return 0; }
-int thcm_b200_sync(thcm_b200_t* h) { CHECK_H(h); CU(cudaStreamSynchronize(h->stream)); return 0; }
+int thcm_b200_sync(thcm_b200_t* h) {
+  CHECK_H(h);
+  CU(cudaStreamSynchronize(h->stream));
+  if (dist_peer_error(h->dist) != 0) return fail(IEMIC_B200_ENCCL, dist_last_error());
+  return 0;
+}
 
 int thcm_b200_set_par(thcm_b200_t* h, int idx1, double value) {
   CHECK_H(h);
@@ -775,6 +781,40 @@ int vec_b200_dot(thcm_b200_t* h, const double* a, const double* b, double* resul
   if (int rc = allreduce(h, h->d_small + 1028, 1, pr)) return rc;
   CU(cudaMemcpyAsync(result, h->d_small + 1028, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
   CU(cudaStreamSynchronize(h->stream));
+  if (dist_peer_error(h->dist) != 0) return fail(IEMIC_B200_ENCCL, dist_last_error());
+  return 0;
+}
+// Epetra_Vector::NormInf: max over the owned parts of all ranks (slot [rank] of a zeroed array, summed across ranks)
+int vec_b200_norminf(thcm_b200_t* h, const double* d_a, double* result) {
+  CHECK_H(h);
+  const int nr = h->host->nranks, me = h->host->rank;
+  if (nr > 8) return fail(IEMIC_B200_ENOTSUP, "vec_b200_norminf: more than 8 ranks");
+  double* slots = h->d_small + 1092; // 8 doubles
+  CU(cudaMemsetAsync(slots, 0, 8 * sizeof(double), h->stream));
+  launch_absmax(d_a, h->nrows(), slots + me, h->stream);
+  h->launches++;
+  if (int rc = check_launch(h, "absmax")) return rc;
+  if (int rc = allreduce(h, slots, nr)) return rc;
+  double v[8];
+  CU(cudaMemcpyAsync(v, slots, nr * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  double m = 0.0;
+  for (int q = 0; q < nr; q++) m = std::fmax(m, v[q]);
+  *result = m;
+  return 0;
+}
+// host <-> device copies of vector data ordered on the handle's stream (a user stream set with thcm_b200_set_stream does not
+// synchronise with the legacy stream plain cudaMemcpy runs on)
+int thcm_b200_upload(thcm_b200_t* h, double* d_dst, const double* src, int64_t n) {
+  CHECK_H(h);
+  CU(cudaMemcpyAsync(d_dst, src, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  return 0;
+}
+int thcm_b200_download(thcm_b200_t* h, double* dst, const double* d_src, int64_t n) {
+  CHECK_H(h);
+  CU(cudaMemcpyAsync(dst, d_src, (size_t)n * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
   return 0;
 }
 int vec_b200_dot_noalloc(const double* d_a, const double* d_b, int64_t n, double* d_out, void* stream) {
@@ -812,7 +852,8 @@ int gmres_b200_solve(thcm_b200_t* h, const double* d_b, double* d_x, int m, int 
   if (m < 1 || m > 500) return fail(IEMIC_B200_EINVAL, "GMRES restart length must be in 1..500");
   if (ortho != GMRES_B200_MGS && ortho != GMRES_B200_CGS2 && ortho != GMRES_B200_CGS2F) return fail(IEMIC_B200_EINVAL, "unknown orthogonalisation");
   if (prec == GMRES_B200_PREC_BLOCKJACOBI && !d_blockinv) return fail(IEMIC_B200_EINVAL, "block Jacobi needs d_blockinv");
-  if (prec != GMRES_B200_PREC_NONE && prec != GMRES_B200_PREC_BLOCKJACOBI) return fail(IEMIC_B200_EINVAL, "unknown preconditioner");
+  if (prec != GMRES_B200_PREC_NONE && prec != GMRES_B200_PREC_BLOCKJACOBI && prec != GMRES_B200_PREC_CALLBACK) return fail(IEMIC_B200_EINVAL, "unknown preconditioner");
+  if (prec == GMRES_B200_PREC_CALLBACK && !h->precond) return fail(IEMIC_B200_EINVAL, "GMRES_B200_PREC_CALLBACK without gmres_b200_set_precond");
   if (int rc = refresh_device(h)) return rc;
   const bool flex = prec != GMRES_B200_PREC_NONE;
   if (int rc = gmres_alloc(h, m, flex)) return rc;
@@ -845,6 +886,8 @@ int gmres_b200_solve(thcm_b200_t* h, const double* d_b, double* d_x, int m, int 
   if (resid <= tol) { if (iters_out) *iters_out = 0; return 0; }
 
   std::vector<double> hbuf(m + 2);
+  int guard_trips = 0;
+  double cycle_start_resid = resid;
   static const bool guard_on = !(getenv("IEMIC_GMRES_GUARD") && getenv("IEMIC_GMRES_GUARD")[0] == '0');
   while (iter <= maxit) {
     // beta = ||r|| ; V0 = r / beta ; s = beta e1   (nrm2 holds ||r||^2)
@@ -858,7 +901,11 @@ int gmres_b200_solve(thcm_b200_t* h, const double* d_b, double* d_x, int m, int 
       double* w = fused ? g.V + (size_t)(i + 1) * ld : g.w; // fused mode builds v_{i+1} in place
       if (flex) {
         double* zi = g.Z + (size_t)i * ld;
-        launch_block_jacobi(d_blockinv, vi, zi, n / 6, st); L();
+        if (prec == GMRES_B200_PREC_CALLBACK) { // model_.applyPrecon(v, z) of GMRESSolver.H:153-172, on the solver's stream
+          if (int rc = check_launch(h, "gmres (before the preconditioner callback)")) return rc;
+          const int prc = h->precond(h->precond_user, vi, zi, (int64_t)n, (void*)st);
+          if (prc != 0) return fail(IEMIC_B200_ECALLBACK, "preconditioner callback returned " + std::to_string(prc));
+        } else { launch_block_jacobi(d_blockinv, vi, zi, n / 6, st); L(); }
         if (int rc = spmv_impl(h, zi, w)) return rc;
       } else if (int rc = spmv_impl(h, vi, w)) return rc;
       {
@@ -936,29 +983,67 @@ int gmres_b200_solve(thcm_b200_t* h, const double* d_b, double* d_x, int m, int 
     };
     launch_backsolve(g.H, m + 1, g.s, space, g.y, st); L();
     if (int rc = candidate(space + 1)) return rc;
-    if (guard_on && ortho != GMRES_B200_MGS && done_in_cycle > 0 && gmres_lost_accuracy(resid, std::sqrt(r2) / normb, tol)) {
-      // the least-squares coefficients outgrew what double precision carries (singular Jacobian, b outside its range):
-      // keep the leading columns the estimate of gmres_guard.h still trusts, return that iterate and stop
-      std::vector<double> hH((size_t)(m + 1) * done_in_cycle), hs(m + 1), ytr;
+    const double expl_full = std::sqrt(r2) / normb;
+    bool lost = guard_on && ortho != GMRES_B200_MGS && done_in_cycle > 0 && gmres_lost_accuracy(resid, expl_full, tol, 0.0);
+    std::vector<double> hH, hs;
+    if (lost) {
+      // the recurrence and the explicit residual disagree: is it more than the rounding of this least-squares problem,
+      // eps ||R||_F ||y|| / ||b||, explains?  (a constant floor would cut legitimate solves with tol below it short)
+      hH.resize((size_t)(m + 1) * done_in_cycle); hs.resize(m + 1);
       CU(cudaMemcpyAsync(hH.data(), g.H, hH.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
       CU(cudaMemcpyAsync(hs.data(), g.s, hs.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
       CU(cudaStreamSynchronize(st));
+      lost = gmres_lost_accuracy(resid, expl_full, tol, gmres_rounding_floor(hH.data(), m + 1, hs.data(), done_in_cycle, normb));
+    }
+    if (lost) {
+      // the least-squares coefficients outgrew what double precision carries (singular Jacobian, b outside its range):
+      // candidate two keeps the leading columns the estimate of gmres_guard.h still trusts; the better of the two is taken
+      std::vector<double> ytr;
       const int keep = gmres_truncate(hH.data(), m + 1, hs.data(), hbuf.data(), done_in_cycle, normb, ytr);
       CU(cudaMemcpyAsync(g.y, ytr.data(), keep * sizeof(double), cudaMemcpyHostToDevice, st));
       if (int rc = candidate(keep)) return rc;
+      const double expl_trunc = std::sqrt(r2) / normb;
+      if (!(expl_trunc <= expl_full)) { // the full update is the better one after all: rebuild it (and its residual vector)
+        launch_backsolve(g.H, m + 1, g.s, space, g.y, st); L();
+        if (int rc = candidate(space + 1)) return rc;
+      }
+      const double expl_best = std::sqrt(r2) / normb;
       CU(cudaMemcpyAsync(d_x, g.tmp, n * sizeof(double), cudaMemcpyDeviceToDevice, st));
-      ret = 2;
-      break;
+      // GMRESSolver.H:213-246 restarts from the explicit residual, which repairs ordinary recurrence drift: do that once.
+      // Two trips in a row, or a cycle that did not reduce the explicit residual, is the breakdown: stop with code 2.
+      const bool progress = expl_best < 0.999 * cycle_start_resid;
+      if (expl_best <= tol) { ret = 0; break; }
+      if (guard_trips >= 1 || !progress || iter > maxit) { ret = 2; break; }
+      guard_trips++;
+      cycle_start_resid = expl_best;
+      continue; // g.r and nrm2 hold the residual of the iterate just stored
     }
+    guard_trips = 0;
+    cycle_start_resid = expl_full;
     CU(cudaMemcpyAsync(d_x, g.tmp, n * sizeof(double), cudaMemcpyDeviceToDevice, st));
     if (conv) { ret = 0; break; }
   }
   CU(cudaMemcpyAsync(&r2, nrm2, sizeof(double), cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
+  if (dist_peer_error(h->dist) != 0) return fail(IEMIC_B200_ENCCL, dist_last_error());
   if (hist_out) hist_out[nh] = std::sqrt(r2) / normb; // explicit residual after the last cycle (:241-242)
   if (iters_out) *iters_out = iter;
   if (int rc = check_launch(h, "gmres")) return rc;
   return ret;
+}
+
+int vec_b200_block_jacobi_apply(thcm_b200_t* h, const double* d_blockinv, const double* d_v, double* d_z) {
+  CHECK_H(h);
+  if (!d_blockinv || !d_v || !d_z) return fail(IEMIC_B200_EINVAL, "block_jacobi_apply: null pointer");
+  launch_block_jacobi(d_blockinv, d_v, d_z, h->nrows() / 6, h->stream);
+  h->launches++;
+  return check_launch(h, "block_jacobi_apply");
+}
+
+int gmres_b200_set_precond(thcm_b200_t* h, gmres_b200_precond_fn fn, void* user) {
+  CHECK_H(h);
+  h->precond = fn; h->precond_user = user;
+  return 0;
 }
 
 int gmres_b200_solve_host(thcm_b200_t* h, const double* b, double* x, int m, int maxit, double tol, int ortho, int prec,

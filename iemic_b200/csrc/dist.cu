@@ -99,7 +99,7 @@ __global__ void __launch_bounds__(256) halo_push_kernel(const double* __restrict
 }
 __global__ void __launch_bounds__(256) halo_pull_kernel(double* __restrict__ x, const int* __restrict__ cells, int ncells, const double* rbuf,
                                                         const PeerHalo p) {
-  if (threadIdx.x < p.npeers) peer_wait(p.wait[threadIdx.x], p.epoch);
+  if (threadIdx.x < p.npeers) peer_wait(p.wait[threadIdx.x], p.epoch, p.me);
   __syncthreads();
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t < 6 * ncells) x[(size_t)6 * cells[t / 6] + (t % 6)] = peer_ld_f64(rbuf + t);
@@ -177,6 +177,12 @@ void p2p_setup(Dist* d) {
       N.AllReduce(d_agree, d_agree, 1, NCCL_FLOAT64, NCCL_SUM, d->comm, nullptr) == 0 && cudaStreamSynchronize(nullptr) == cudaSuccess &&
       cudaMemcpy(&agree, d_agree, sizeof(double), cudaMemcpyDeviceToHost) == cudaSuccess)
     d->p2p = ok && agree == (double)d->nranks;
+  if (d->p2p) { // time-out of a wait on a peer's flag (nanoseconds), kept in the rank's own box
+    const char* ts = getenv("IEMIC_PEER_TIMEOUT_S");
+    const double sec = ts && atof(ts) > 0.0 ? atof(ts) : 120.0;
+    const unsigned long long ns = (unsigned long long)(sec * 1.0e9);
+    cudaMemcpy(&((PeerBox*)d->box_local)->pad[PEER_PAD_TIMEOUT_NS], &ns, sizeof(ns), cudaMemcpyHostToDevice);
+  }
   if (d_mine) cudaFree(d_mine);
   if (d_all) cudaFree(d_all);
   cudaGetLastError();
@@ -194,6 +200,7 @@ PeerHalo peer_halo_args(Dist* d) {
   a.epoch = ++d->halo_epoch;
   const int b = (int)(a.epoch & 1ull);
   PeerBox* me = (PeerBox*)d->box_local;
+  a.me = me;
   int i = 0;
   for (const auto& p : d->peers) {
     PeerBox* rb = (PeerBox*)d->box_remote[p.rank];
@@ -348,6 +355,14 @@ PeerRed dist_next_red(Dist* d) {
   for (int q = 0; q < d->nranks; q++) r.box[q] = (PeerBox*)d->box_remote[q];
   r.rank = d->rank; r.nranks = d->nranks; r.epoch = ++d->ar_epoch;
   return r;
+}
+// Did a wait on a peer's flag give up (peer.cuh)?  Call after a synchronisation of the stream the kernels ran on.
+int dist_peer_error(Dist* d) {
+  if (!d || !d->p2p) return 0;
+  unsigned long long w = 0;
+  if (cudaMemcpy(&w, &((PeerBox*)d->box_local)->pad[PEER_PAD_ERROR], sizeof(w), cudaMemcpyDeviceToHost) != cudaSuccess) { g_derr = "reading the peer error word failed"; return -1; }
+  if (w) { g_derr = "a wait on a peer GPU's flag timed out (IEMIC_PEER_TIMEOUT_S): a rank died or fell more than the time-out behind; this handle is out of step with its peers, recreate it"; return -1; }
+  return 0;
 }
 const char* dist_last_error() { return g_derr.c_str(); }
 

@@ -23,5 +23,6 @@ int dist_halo_end(Dist*, cudaStream_t st);
 // dist_allreduce_sum after the kernel).  Every rank must request them in the same order.
 bool dist_p2p(const Dist*);
 PeerRed dist_next_red(Dist*);
+int dist_peer_error(Dist*); // 0, or -1 when a peer wait timed out since the handle was created (message in dist_last_error)
 const char* dist_last_error();
 } // namespace thcm

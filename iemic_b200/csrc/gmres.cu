@@ -338,10 +338,13 @@ __device__ void givens_step(const GivensArgs& g) { // one thread
   if (g.pyth) { // ||w - V h2||^2 = ||w||^2 - |h2|^2 for orthonormal V: h2[j+1] carries <w,w> from the same reduction
     double hh = 0.0;
     for (int k = 0; k <= j; k++) hh = fma(g.h2[k], g.h2[k], hh);
-    nrm = sqrt(fmax(g.h2[j + 1] - hh, 0.0));
+    const double ww = g.h2[j + 1], d2 = ww - hh;
+    // (happy) breakdown: the new direction lies in span(V) to working precision.  The difference is then pure cancellation
+    // noise; H[j+1][j] = 0 ends the Krylov space here and the normalisation that rides on the next kernel divides by 1, not 0.
+    nrm = (d2 > 1.0e-28 * ww) ? sqrt(d2) : 0.0;
   } else nrm = g.sq ? sqrt(*g.nrm2) : *g.nrm2;
   Hc[j + 1] = nrm;
-  *g.hnext = nrm;
+  *g.hnext = (nrm > 0.0) ? nrm : 1.0;
   for (int k = 0; k < j; k++) app_rot(Hc[k], Hc[k + 1], g.cs[k], g.sn[k]);
   gen_rot(Hc[j], Hc[j + 1], g.cs[j], g.sn[j]);
   app_rot(Hc[j], Hc[j + 1], g.cs[j], g.sn[j]);
@@ -370,6 +373,21 @@ __global__ void sqrt_store_kernel(const double* nrm2, double* out) {
   if (threadIdx.x == 0) *out = sqrt(*nrm2);
 }
 
+// max |a_i| over the owned part; one block (used for log lines and divergence tests, never inside the solver loop)
+__global__ void __launch_bounds__(1024, 1) absmax_kernel(const double* __restrict__ a, long long n, double* out) {
+  __shared__ double red[32];
+  double m = 0.0;
+  for (long long i = threadIdx.x; i < n; i += blockDim.x) m = fmax(m, fabs(a[i]));
+  for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_down_sync(0xffffffffu, m, o));
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = m;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    m = red[threadIdx.x];
+    for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_down_sync(0xffffffffu, m, o));
+    if (threadIdx.x == 0) *out = m;
+  }
+}
+
 // ---- dot product without any allocation (vec_b200_dot_noalloc; no counterpart in the reference) ----
 // Block partials and the arrival ticket live in a file-scope device array that every GPU loading the library holds until
 // exit (NOALLOC_SLOTS * 8 bytes = 16.6 KB).  Every call shares it: calls that overlap on one GPU race.
@@ -393,7 +411,7 @@ __global__ void __launch_bounds__(RT) dot_noalloc_kernel(const double* __restric
   if (last_block(ticket)) final_sum(partial, 1, 1, out);
 }
 
-int g_red_blocks = 0;
+int g_red_blocks[64] = {0}; // per device
 int grid_for(long long n) {
   long long need = ((n >> 1) + RT - 1) / RT;
   int cap = red_blocks();
@@ -402,15 +420,17 @@ int grid_for(long long n) {
 } // namespace
 
 int red_blocks() {
-  if (g_red_blocks == 0) {
-    int dev = 0, sms = 148;
-    cudaGetDevice(&dev);
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  int& cached = g_red_blocks[dev & 63];
+  if (cached == 0) {
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    g_red_blocks = sms * 8; // 8 resident blocks of 256 threads per SM: one full wave
+    cached = sms * 8; // 8 resident blocks of 256 threads per SM: one full wave
   }
-  return g_red_blocks;
+  return cached;
 }
 
+void launch_absmax(const double* a, long long n, double* out, cudaStream_t st) { absmax_kernel<<<1, 1024, 0, st>>>(a, n, out); }
 long long dot_noalloc_max_n() { return 1ll << 30; }
 // Returns 0, or a cudaError_t.  In host code the array's name is only a stand-in: the device address comes from
 // cudaGetSymbolAddress, asked once per device with that device current.
@@ -451,10 +471,13 @@ template <int FT, int NB, int MINB, int FK = 8>
 static void launch_mad(const double* V, long long ldv, int nv, const double* h, double* w, long long n, double* out, RedBuf rb, cudaStream_t st,
                        const PeerRed& pr, const GivensArgs& g) {
   const int smem = NB * (nv + 1) * FT * (int)sizeof(double);
-  static bool attr = false;
-  if (!attr) { cudaFuncSetAttribute(multi_axpy_dot_kernel<FT, NB, MINB, FK>, cudaFuncAttributeMaxDynamicSharedMemorySize, NB * (FUSE_MAXNV + 1) * FT * (int)sizeof(double)); attr = true; }
+  static unsigned long long attr_done = 0; // one bit per device: a function attribute belongs to the device's copy of the kernel
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
+  if (!(attr_done >> (dev & 63) & 1ull)) {
+    cudaFuncSetAttribute(multi_axpy_dot_kernel<FT, NB, MINB, FK>, cudaFuncAttributeMaxDynamicSharedMemorySize, NB * (FUSE_MAXNV + 1) * FT * (int)sizeof(double));
+    attr_done |= 1ull << (dev & 63);
+  }
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   const int per_sm = std::max(1, std::min(MINB, (220 * 1024) / (smem + 1024)));
   const long long need = (n + FT - 1) / FT, cap = std::min<long long>((long long)sms * per_sm, rb.nblk_max);

@@ -15,11 +15,30 @@
 
 namespace thcm {
 
-// explicit residual that contradicts the recurrence residual (both relative to ||b||)
-inline bool gmres_lost_accuracy(double recurrence, double explicit_resid, double tol) {
-  // 1e-8: a disagreement at rounding level (tol = 0 runs, histories taken to machine precision) is not a breakdown
-  const double lim = std::fmax(std::fmax(10.0 * tol, 100.0 * recurrence), 1.0e-8);
+// explicit residual that contradicts the recurrence residual (both relative to ||b||); `floor`: what rounding alone explains
+inline bool gmres_lost_accuracy(double recurrence, double explicit_resid, double tol, double floor) {
+  const double lim = std::fmax(std::fmax(10.0 * tol, 100.0 * recurrence), floor);
   return !(explicit_resid <= lim); // NaN counts as lost
+}
+
+// min(100 eps ||R||_F ||y|| / ||b||, 1e-6) of the full least-squares problem of this cycle (k columns): the size of the
+// disagreement between recurrence and explicit residual that ordinary rounding produces
+inline double gmres_rounding_floor(const double* R, int ldr, const double* s, int k, double normb) {
+  const double eps = 2.220446049250313e-16;
+  std::vector<double> y((size_t)k);
+  for (int i = 0; i < k; i++) y[i] = s[i];
+  double fro2 = 0.0;
+  for (int i = k - 1; i >= 0; i--) {
+    const double* col = R + (size_t)i * ldr;
+    y[i] /= col[i];
+    for (int q = 0; q < i; q++) y[q] -= col[q] * y[i];
+    for (int q = 0; q <= i; q++) fro2 += col[q] * col[q];
+  }
+  double y2 = 0.0;
+  for (int i = 0; i < k; i++) y2 += y[i] * y[i];
+  const double f = 100.0 * eps * std::sqrt(fro2) * std::sqrt(y2) / normb;
+  // capped: in the breakdown this guard exists for, ||y|| itself has exploded (1e13 ||b||) and would "explain" any residual
+  return f >= 0.0 ? std::fmin(f, 1.0e-6) : 0.0; // NaN (zero pivot): no floor, the guard decides on the residuals alone
 }
 
 // R: rotated Hessenberg matrix, column j at R + j * ldr (upper triangular); s: rotated right-hand side; hist[j]: recurrence

@@ -116,6 +116,7 @@ void launch_dot(const double* a, const double* b, long long n, double* out, RedB
 // same product with the reduction scratch in a static device array (no allocation anywhere); returns 0 or a cudaError_t
 int launch_dot_noalloc(const double* a, const double* b, long long n, double* out, cudaStream_t st);
 long long dot_noalloc_max_n();
+void launch_absmax(const double* a, long long n, double* out /* 1 double */, cudaStream_t st);
 // y = alpha * x with alpha = (inv ? 1/s[0] : s[0]) read on the device ; s may be sqrt'ed first (sq: s[0] holds a squared norm)
 void launch_scale_copy(const double* x, double* y, long long n, const double* s, int inv, int sq, cudaStream_t st);
 void launch_update(double a, const double* A, double b, double* y, long long n, cudaStream_t st); // y = a*A + b*y

@@ -12,7 +12,10 @@
 //
 // Flags carry a monotonically increasing epoch; slots and buffers are double-buffered by epoch parity, which is enough
 // because a rank can only complete exchange e+1 after every peer has finished reading exchange e (stream order).
-// A wait that lasts longer than PEER_TIMEOUT_NS traps: a dead peer must not hang the GPU.
+// A wait that lasts longer than the time-out (box word pad[1], nanoseconds; IEMIC_PEER_TIMEOUT_S, default 120 s) gives up: it
+// raises the error word pad[0] of the rank's own box and lets the kernel finish with meaningless numbers; the host turns the
+// word into IEMIC_B200_ENCCL at its next synchronisation (dist_peer_error).  No __trap(): the CUDA context survives, so a caller
+// like Continuation::reset() keeps working; the handle itself is out of step with its peers from then on and must be recreated.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -21,7 +24,7 @@ namespace thcm {
 
 constexpr int PEER_MAX = 8;          // ranks of one NVSwitch domain handled here
 constexpr int PEER_ARMAX = 512;      // doubles per fused allreduce (= MAXV of gmres.cu)
-constexpr unsigned long long PEER_TIMEOUT_NS = 4000000000ull;
+enum { PEER_PAD_ERROR = 0, PEER_PAD_TIMEOUT_NS = 1 }; // words of PeerBox::pad
 
 struct PeerBox {
   unsigned long long ar_flag[2][PEER_MAX];
@@ -44,6 +47,7 @@ struct PeerHalo {
   unsigned long long* flag[PEER_MAX];     // per neighbour q: q's halo_flag[parity][my rank]
   int send_end[PEER_MAX];                 // prefix ends (cells) of the per-neighbour segments of the send list
   const unsigned long long* wait[PEER_MAX]; // my own halo_flag[parity][q's rank]
+  PeerBox* me;                            // my own box (error word, time-out)
   int npeers;
   unsigned long long epoch;
 };
@@ -67,11 +71,11 @@ __device__ __forceinline__ unsigned long long peer_now() {
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
   return t;
 }
-__device__ __forceinline__ void peer_wait(const unsigned long long* flag, unsigned long long epoch) {
+__device__ __forceinline__ void peer_wait(const unsigned long long* flag, unsigned long long epoch, PeerBox* me) {
   if (peer_ld_acquire(flag) >= epoch) return;
-  const unsigned long long t0 = peer_now();
+  const unsigned long long t0 = peer_now(), limit = me->pad[PEER_PAD_TIMEOUT_NS];
   while (peer_ld_acquire(flag) < epoch)
-    if (peer_now() - t0 > PEER_TIMEOUT_NS) __trap();
+    if (peer_now() - t0 > limit) { atomicExch(&me->pad[PEER_PAD_ERROR], 1ull); __threadfence_system(); return; }
 }
 
 // Called by every thread of ONE block after out[0..nv) holds this rank's sums; on return out[] holds the global sums.
@@ -86,7 +90,7 @@ __device__ __forceinline__ void peer_allreduce_block(const PeerRed& p, double* o
   __syncthreads();
   if (tid < p.nranks) {
     peer_st_release(&p.box[tid]->ar_flag[b][p.rank], p.epoch);
-    peer_wait(&p.box[p.rank]->ar_flag[b][tid], p.epoch);
+    peer_wait(&p.box[p.rank]->ar_flag[b][tid], p.epoch, p.box[p.rank]);
   }
   __syncthreads();
   const PeerBox* me = p.box[p.rank];

@@ -57,9 +57,9 @@ typedef struct {
   int fix_pressure_points;
 } thcm_b200_config;
 
-enum { IEMIC_B200_OK = 0, IEMIC_B200_EINVAL = -1, IEMIC_B200_ECUDA = -2, IEMIC_B200_ENOTSUP = -3, IEMIC_B200_ENCCL = -4 };
+enum { IEMIC_B200_OK = 0, IEMIC_B200_EINVAL = -1, IEMIC_B200_ECUDA = -2, IEMIC_B200_ENOTSUP = -3, IEMIC_B200_ENCCL = -4, IEMIC_B200_ECALLBACK = -5 };
 enum { GMRES_B200_MGS = 0, GMRES_B200_CGS2 = 1, GMRES_B200_CGS2F = 2 };
-enum { GMRES_B200_PREC_NONE = 0, GMRES_B200_PREC_BLOCKJACOBI = 1 };
+enum { GMRES_B200_PREC_NONE = 0, GMRES_B200_PREC_BLOCKJACOBI = 1, GMRES_B200_PREC_CALLBACK = 2 };
 
 const char* iemic_b200_last_error(void);
 const char* iemic_b200_version(void);
@@ -129,6 +129,10 @@ int vec_b200_dot(thcm_b200_t* h, const double* d_a, const double* d_b, double* r
  * threads or processes' contexts apart) race; order them on one stream. */
 int vec_b200_dot_noalloc(const double* d_a, const double* d_b, int64_t n, double* d_out, void* stream);
 int vec_b200_norm2(thcm_b200_t* h, const double* d_a, double* result);
+int vec_b200_norminf(thcm_b200_t* h, const double* d_a, double* result); /* Epetra_Vector::NormInf, global over the ranks */
+/* owned part of a vector between host memory and the device, ordered on the handle's stream (synchronous for the caller) */
+int thcm_b200_upload(thcm_b200_t* h, double* d_dst, const double* src, int64_t n);
+int thcm_b200_download(thcm_b200_t* h, double* dst, const double* d_src, int64_t n);
 int vec_b200_update(thcm_b200_t* h, double a, const double* d_A, double b, double* d_this); /* this = a*A + b*this */
 int vec_b200_scale(thcm_b200_t* h, double a, double* d_this);
 int vec_b200_putscalar(thcm_b200_t* h, double a, double* d_this);
@@ -160,23 +164,34 @@ int thcm_b200_scal(const double* db36, double* dr6, double* dc6);
 int thcm_b200_recompute_scaling(thcm_b200_t* h, double* d_rowscal, double* d_colscal, double* rs6, double* cs6);
 int thcm_b200_left_scale(thcm_b200_t* h, const double* d_scal);
 int thcm_b200_block_jacobi(thcm_b200_t* h, double* d_blockinv, int* nsingular);
+/* z = blockdiag(d_blockinv) v on the handle's stream: the apply of that preconditioner alone (Model::applyPrecon, src/utils/Model.H:52-118) */
+int vec_b200_block_jacobi_apply(thcm_b200_t* h, const double* d_blockinv, const double* d_v, double* d_z);
 
 /* ---- GMRES(m) on the handle's Jacobian (GMRESSolver.H:81-255) ----
  * ortho: GMRES_B200_MGS reproduces the reference's modified Gram-Schmidt loop (:177-181); GMRES_B200_CGS2 is the
  * fused two-pass classical Gram-Schmidt (three reductions per step: h1, h2, norm); GMRES_B200_CGS2F is the same
  * projection with two reductions per step (the second also returns <w,w>, the new norm follows from Pythagoras and
  * the normalisation is fused into the second update: 6 kernels and 2 allreduces per Arnoldi step).  prec: right (flexible) preconditioner; BLOCKJACOBI takes nrows_local/6
- * inverted 6x6 blocks, row-major, in d_blockinv.  hist[it] receives resid_ after inner iteration it
- * (length >= maxit+1).  check_every: 1 tests convergence every iteration like the reference; 0 never leaves the
+ * inverted 6x6 blocks, row-major, in d_blockinv; CALLBACK applies the function registered with gmres_b200_set_precond.
+ * hist[it] receives resid_ after inner iteration it, and the entry behind the last one the explicit residual after the last
+ * cycle: the array must hold maxit + 2 doubles.  check_every: 1 tests convergence every iteration like the reference; 0 never leaves the
  * device until the cycle ends (fixed iteration count).  Return value: 0 converged, 1 not converged (like solve()),
  * 2 accuracy limit: in the CGS2 modes the explicit residual at the end of a cycle (GMRESSolver.H:228-242) is compared
- * with the recurrence residual the reference accepts on; when it is more than max(10 tol, 100 x recurrence, 1e-8) -- a singular
- * Jacobian with a right-hand side at the rounding floor of F -- the update keeps only the leading Krylov columns whose
- * estimated residual is still attainable (iemic_b200/csrc/gmres_guard.h), d_x holds that iterate and the solve stops.
+ * with the recurrence residual the reference accepts on; when it is more than max(10 tol, 100 x recurrence, min(100 eps |R||y|/|b|, 1e-6))
+ * the better of the full update and the one that keeps only the leading Krylov columns whose estimated residual is still
+ * attainable (iemic_b200/csrc/gmres_guard.h) is taken and, like GMRESSolver.H:213-246, the solve restarts from the explicit
+ * residual; a second trip in a row, or a cycle without progress -- a singular Jacobian with a right-hand side at the rounding
+ * floor of F -- ends the solve with that iterate in d_x.
  * The MGS mode keeps the reference's behaviour to the letter.  IEMIC_GMRES_GUARD=0 in the environment switches it off. */
 int gmres_b200_solve(thcm_b200_t* h, const double* d_b, double* d_x, int m, int maxit, double tol,
                      int ortho, int prec, const double* d_blockinv, int check_every,
                      double* hist, int* iters);
+/* Right (flexible) preconditioner supplied by the caller: z = M^-1 v, both device vectors of n = nrows_local doubles, enqueued on
+ * `stream` (the solver's cudaStream_t) -- the hook Ocean::solve uses through setRightPrec (src/ocean/Ocean.C:972-975) and
+ * GMRESSolver through model_.applyPrecon (GMRESSolver.H:153-172); a TRIOS / MRILU apply living on the host or on another device
+ * synchronises inside.  Return 0, anything else aborts the solve with IEMIC_B200_ECALLBACK.  Used when prec = GMRES_B200_PREC_CALLBACK. */
+typedef int (*gmres_b200_precond_fn)(void* user, const double* d_v, double* d_z, int64_t n, void* stream);
+int gmres_b200_set_precond(thcm_b200_t* h, gmres_b200_precond_fn fn, void* user);
 int gmres_b200_solve_host(thcm_b200_t* h, const double* b, double* x, int m, int maxit, double tol,
                           int ortho, int prec, const double* blockinv, int check_every,
                           double* hist, int* iters);

@@ -152,7 +152,8 @@ class OracleModel {
     std::vector<double> r(n), w(n), tmp(n), V((size_t)(m + 1) * n), Z((size_t)m * n), H((size_t)ldh * m), cs(m), sn(m), s(m + 1), hist(m), y;
     auto residual = [&](const std::vector<double>& xx) { amul(xx.data(), r.data()); for (size_t i = 0; i < n; i++) r[i] = b[i] - r[i]; return std::sqrt(dot(r.data(), r.data())); };
     double beta = residual(x), resid = beta / normb;
-    int iter = 0, rc = 1;
+    int iter = 0, rc = 1, trips = 0;
+    double cycle_start = resid;
     if (resid <= tol) rc = 0;
     while (rc == 1 && iter <= maxit) {
       for (size_t i = 0; i < n; i++) V[i] = r[i] / beta;
@@ -180,13 +181,23 @@ class OracleModel {
       y.assign(s.begin(), s.begin() + done);
       for (int a = done - 1; a >= 0; a--) { y[a] /= H[(size_t)a * ldh + a]; for (int q = 0; q < a; q++) y[q] -= H[(size_t)a * ldh + q] * y[a]; }
       double expl = candidate(y);
-      if (guard && thcm::gmres_lost_accuracy(resid, expl, tol)) {
+      if (guard && thcm::gmres_lost_accuracy(resid, expl, tol, 0.0) &&
+          thcm::gmres_lost_accuracy(resid, expl, tol, thcm::gmres_rounding_floor(H.data(), ldh, s.data(), done, normb))) {
+        // same walk as gmres_b200_solve: better of the full and the truncated update, one restart, then stop with code 2
+        const std::vector<double> yfull = y;
+        const double expl_full = expl;
         const int keep = thcm::gmres_truncate(H.data(), ldh, s.data(), hist.data(), done, normb, y);
         expl = candidate(y);
-        x = tmp; rc = 2;
+        if (!(expl <= expl_full)) expl = candidate(yfull);
+        x = tmp;
         if (std::getenv("IEMIC_COMPAT_VERBOSE")) std::printf("OracleModel: accuracy guard kept %d of %d columns, explicit residual %.3e\n", keep, done, expl);
-        break;
+        const bool progress = expl < 0.999 * cycle_start;
+        if (expl <= tol) { rc = 0; break; }
+        if (trips >= 1 || !progress || iter > maxit) { rc = 2; break; }
+        trips++; cycle_start = expl; beta = expl * normb;
+        continue;
       }
+      trips = 0; cycle_start = expl;
       x = tmp; beta = expl * normb;
       if (conv) rc = 0;
     }
