@@ -1003,11 +1003,15 @@ int gmres_b200_solve(thcm_b200_t* h, const double* d_b, double* d_x, int m, int 
       CU(cudaMemcpyAsync(g.y, ytr.data(), keep * sizeof(double), cudaMemcpyHostToDevice, st));
       if (int rc = candidate(keep)) return rc;
       const double expl_trunc = std::sqrt(r2) / normb;
-      if (!(expl_trunc <= expl_full)) { // the full update is the better one after all: rebuild it (and its residual vector)
-        launch_backsolve(g.H, m + 1, g.s, space, g.y, st); L();
-        if (int rc = candidate(space + 1)) return rc;
+      // The truncated update is the trustworthy one (the full one carries the exploded coefficients: on a singular Jacobian a
+      // multiple of the null vector, whatever its residual says).  It must not be worse than where the cycle started, though:
+      // then the full update is taken if IT improved on the start, else the iterate stays where it was.
+      double expl_best = expl_trunc;
+      if (!(expl_trunc <= cycle_start_resid)) {
+        if (expl_full <= cycle_start_resid) { launch_backsolve(g.H, m + 1, g.s, space, g.y, st); L(); if (int rc = candidate(space + 1)) return rc; }
+        else if (int rc = candidate(0)) return rc; // zero columns: x itself, with its residual vector rebuilt for the restart
+        expl_best = std::sqrt(r2) / normb;
       }
-      const double expl_best = std::sqrt(r2) / normb;
       CU(cudaMemcpyAsync(d_x, g.tmp, n * sizeof(double), cudaMemcpyDeviceToDevice, st));
       // GMRESSolver.H:213-246 restarts from the explicit residual, which repairs ordinary recurrence drift: do that once.
       // Two trips in a row, or a cycle that did not reduce the explicit residual, is the breakdown: stop with code 2.

@@ -21,7 +21,7 @@ inline bool gmres_lost_accuracy(double recurrence, double explicit_resid, double
   return !(explicit_resid <= lim); // NaN counts as lost
 }
 
-// min(100 eps ||R||_F ||y|| / ||b||, 1e-6) of the full least-squares problem of this cycle (k columns): the size of the
+// min(100 eps ||R||_F ||y|| / ||b||, 1e-8) of the full least-squares problem of this cycle (k columns): the size of the
 // disagreement between recurrence and explicit residual that ordinary rounding produces
 inline double gmres_rounding_floor(const double* R, int ldr, const double* s, int k, double normb) {
   const double eps = 2.220446049250313e-16;
@@ -38,7 +38,7 @@ inline double gmres_rounding_floor(const double* R, int ldr, const double* s, in
   for (int i = 0; i < k; i++) y2 += y[i] * y[i];
   const double f = 100.0 * eps * std::sqrt(fro2) * std::sqrt(y2) / normb;
   // capped: in the breakdown this guard exists for, ||y|| itself has exploded (1e13 ||b||) and would "explain" any residual
-  return f >= 0.0 ? std::fmin(f, 1.0e-6) : 0.0; // NaN (zero pivot): no floor, the guard decides on the residuals alone
+  return f >= 0.0 ? std::fmin(f, 1.0e-8) : 0.0; // NaN (zero pivot): no floor, the guard decides on the residuals alone
 }
 
 // R: rotated Hessenberg matrix, column j at R + j * ldr (upper triangular); s: rotated right-hand side; hist[j]: recurrence

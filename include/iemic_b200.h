@@ -177,7 +177,7 @@ int vec_b200_block_jacobi_apply(thcm_b200_t* h, const double* d_blockinv, const 
  * cycle: the array must hold maxit + 2 doubles.  check_every: 1 tests convergence every iteration like the reference; 0 never leaves the
  * device until the cycle ends (fixed iteration count).  Return value: 0 converged, 1 not converged (like solve()),
  * 2 accuracy limit: in the CGS2 modes the explicit residual at the end of a cycle (GMRESSolver.H:228-242) is compared
- * with the recurrence residual the reference accepts on; when it is more than max(10 tol, 100 x recurrence, min(100 eps |R||y|/|b|, 1e-6))
+ * with the recurrence residual the reference accepts on; when it is more than max(10 tol, 100 x recurrence, min(100 eps |R||y|/|b|, 1e-8))
  * the better of the full update and the one that keeps only the leading Krylov columns whose estimated residual is still
  * attainable (iemic_b200/csrc/gmres_guard.h) is taken and, like GMRESSolver.H:213-246, the solve restarts from the explicit
  * residual; a second trip in a row, or a cycle without progress -- a singular Jacobian with a right-hand side at the rounding

@@ -187,8 +187,8 @@ class OracleModel {
         const std::vector<double> yfull = y;
         const double expl_full = expl;
         const int keep = thcm::gmres_truncate(H.data(), ldh, s.data(), hist.data(), done, normb, y);
-        expl = candidate(y);
-        if (!(expl <= expl_full)) expl = candidate(yfull);
+        expl = candidate(y);                       // the truncated update is the trustworthy one, unless it is worse than the cycle's start
+        if (!(expl <= cycle_start)) expl = (expl_full <= cycle_start) ? candidate(yfull) : candidate(std::vector<double>());
         x = tmp;
         if (std::getenv("IEMIC_COMPAT_VERBOSE")) std::printf("OracleModel: accuracy guard kept %d of %d columns, explicit residual %.3e\n", keep, done, expl);
         const bool progress = expl < 0.999 * cycle_start;
