@@ -513,6 +513,18 @@ def main():
         prec_leg = {"block_jacobi_build_ms": ms_bj, "recompute_scaling_ms": ms_sc, "left_scale_ms": ms_ls,
                     "gmres_block_jacobi_iters_per_s": mm / (ms_gp * 1e-3), "gmres_block_jacobi_ms_per_cycle": ms_gp}
         del d_binv, d_rs, d_ri
+    # row N1: what a parameter change costs on top of the next assembly (Continuation::computeDFDPar changes one twice per Newton step)
+    kk = [0]
+
+    def step_setpar():
+        kk[0] += 1
+        G.setPar("COMB", 0.1 + 1.0e-9 * kk[0])
+        G.assemble(dx, dF, jacobian=True)
+
+    ms_sp = timed(step_setpar, args.steps, 2) / args.steps
+    ms_plain = timed(step_dev, args.steps, 1) / args.steps
+    G.setPar("COMB", grids.STARTING_PARS["global"]["COMB"])
+    set_par_ms = ms_sp - ms_plain
     clocks = sampler.stop() if rank == 0 else None
 
     if rank != 0:
@@ -559,6 +571,7 @@ def main():
                 "d2h_bytes_per_step": 8 * nrows_g, "api": "thcm_b200_assemble_host: state up from pinned host memory, residual back, Jacobian device-resident like Ocean::jac_"},
         "spmv": {"gbs": spmv_b / (ms_spmv / nsp * 1e-3) / 1e9, "ms": ms_spmv / nsp, "frac": spmv_b / (ms_spmv / nsp * 1e-3) / 1e9 / peak_total,
                  "algorithmic_bytes": spmv_b},
+        "set_par_ms": set_par_ms,
         "gpu_launches": int(launches),
         "clocks": clocks,
     }

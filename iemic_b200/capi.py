@@ -72,7 +72,7 @@ def lib():
             "thcm_b200_set_values_host": [vp, dp], "thcm_b200_forcing_host": [vp, dp],
             "thcm_b200_intcond_host": [vp, dp, ip],
             "thcm_b200_rhs_host": [vp, vp, vp], "thcm_b200_jacobian_host": [vp, vp, vp, vp],
-            "thcm_b200_assemble_host": [vp, vp, vp, C.c_int], "thcm_b200_assemble": [vp, vp, vp, C.c_int], "thcm_b200_exchange_mode": [vp],
+            "thcm_b200_assemble_host": [vp, vp, vp, C.c_int], "thcm_b200_assemble": [vp, vp, vp, C.c_int], "thcm_b200_exchange_mode": [vp], "thcm_b200_evaluate_b": [vp, vp],
             "thcm_b200_spmv": [vp, vp, vp], "thcm_b200_spmv_host": [vp, vp, vp],
             "vec_b200_dot": [vp, vp, vp, dp], "vec_b200_norm2": [vp, vp, dp],
             "vec_b200_dot_noalloc": [vp, vp, C.c_int64, vp, vp], "vec_b200_norminf": [vp, vp, dp],
@@ -105,7 +105,7 @@ EXPORTED = ["iemic_b200_last_error", "iemic_b200_version", "iemic_b200_device_co
             "thcm_b200_set_intcond_correction", "thcm_b200_sizes", "thcm_b200_block", "thcm_b200_global_ids",
             "thcm_b200_rhs", "thcm_b200_jacobian", "thcm_b200_halo_exchange", "thcm_b200_csr", "thcm_b200_graph_host",
             "thcm_b200_values_host", "thcm_b200_set_values_host", "thcm_b200_forcing_host", "thcm_b200_intcond_host",
-            "thcm_b200_rhs_host", "thcm_b200_jacobian_host", "thcm_b200_assemble_host", "thcm_b200_assemble", "thcm_b200_exchange_mode", "thcm_b200_spmv", "thcm_b200_spmv_host",
+            "thcm_b200_rhs_host", "thcm_b200_jacobian_host", "thcm_b200_assemble_host", "thcm_b200_assemble", "thcm_b200_exchange_mode", "thcm_b200_evaluate_b", "thcm_b200_spmv", "thcm_b200_spmv_host",
             "vec_b200_dot", "vec_b200_dot_noalloc", "vec_b200_norm2", "vec_b200_norminf", "thcm_b200_upload", "thcm_b200_download", "vec_b200_update", "vec_b200_scale", "vec_b200_putscalar",
             "vec_b200_multiply", "vec_b200_reciprocal", "thcm_b200_average_block", "thcm_b200_scal", "thcm_b200_recompute_scaling",
             "thcm_b200_left_scale", "thcm_b200_block_jacobi",
@@ -279,6 +279,9 @@ class Ocean:
 
     def computeJacobian(self, d_x):
         check(lib().thcm_b200_jacobian(self.h, _ptr(d_x)))
+
+    def evaluateB(self, d_diagB=None):
+        check(lib().thcm_b200_evaluate_b(self.h, _ptr(d_diagB)))
 
     def exchange_mode(self):
         """0 single GPU, 1 NCCL, 2 peer memory over NVLink"""

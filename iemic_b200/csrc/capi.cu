@@ -56,7 +56,7 @@ struct thcm_b200 {
   // static / per-parameter device data
   double* d_tab = nullptr; uint64_t* d_sig = nullptr; int* d_rowptr = nullptr; int* d_col = nullptr;
   double* d_val = nullptr; double* d_diagB = nullptr; double* d_frc = nullptr; double* d_coefS = nullptr;
-  int* d_blkrow = nullptr; int nblk = 0; size_t d_frc_len = 0;
+  int* d_blkrow = nullptr; int nblk = 0; size_t d_frc_len = 0, d_tab_len = 0;
   int* d_blkp0 = nullptr; unsigned char* d_blkreg = nullptr; SpmvTab spmv_tab; size_t spmv_regular_cells = 0;
   uint64_t dev_version = 0, dev_mask_version = 0;
   unsigned int* d_dinfo = nullptr; uint64_t dinfo_mask_version = 0; // diagonal-block positions (scaling.cu), built on first use
@@ -154,6 +154,7 @@ SpmvHostPlan spmv_plan(const Host& H) {
   return P;
 }
 
+int check_launch(thcm_b200* h, const char* what);
 int refresh_device(thcm_b200* h) {
   Host* H = h->host;
   if (h->dev_mask_version != H->mask_version) {
@@ -194,16 +195,35 @@ int refresh_device(thcm_b200* h) {
     h->dev_version = 0;
   }
   if (h->dev_version != H->version) {
-    if (int rc = dev_upload(&h->d_tab, H->tab)) return rc;
-    if (h->d_frc && h->d_frc_len == H->frc.size() && H->frc_dirty_from > 0) { // only the rows a parameter change rewrote
-      const size_t a = std::min(H->frc_dirty_from, H->frc.size());
-      if (a < H->frc.size()) CU(cudaMemcpy(h->d_frc + a, H->frc.data() + a, (H->frc.size() - a) * sizeof(double), cudaMemcpyHostToDevice));
-    } else {
-      if (int rc = dev_upload(&h->d_frc, H->frc)) return rc;
-      h->d_frc_len = H->frc.size();
+    // coefficient tables and per-latitude forcing profiles: one small buffer, reused (no allocation on a parameter change),
+    // copied on the handle's stream so that kernels still reading the old values finish first
+    const size_t ntab = H->tab.size(), nprof = H->fprof.size(), need = ntab + nprof + 8;
+    if (!h->d_tab || h->d_tab_len < need) {
+      if (h->d_tab) cudaFree(h->d_tab);
+      CU(cudaMalloc((void**)&h->d_tab, need * sizeof(double)));
+      h->d_tab_len = need;
     }
-    H->frc_dirty_from = H->frc.size();
+    CU(cudaMemcpyAsync(h->d_tab, H->tab.data(), ntab * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    if (nprof) CU(cudaMemcpyAsync(h->d_tab + ntab, H->fprof.data(), nprof * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    if (H->frc_host_valid && !(h->d_frc && h->d_frc_len == H->frc.size() && H->frc_dirty_from >= H->frc.size())) {
+      // the host copy is current (creation, new land mask): upload what changed
+      if (h->d_frc && h->d_frc_len == H->frc.size() && H->frc_dirty_from > 0) {
+        const size_t a = std::min(H->frc_dirty_from, H->frc.size());
+        if (a < H->frc.size()) CU(cudaMemcpyAsync(h->d_frc + a, H->frc.data() + a, (H->frc.size() - a) * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+      } else {
+        CU(cudaStreamSynchronize(h->stream));
+        if (int rc = dev_upload(&h->d_frc, H->frc)) return rc;
+        h->d_frc_len = H->frc.size();
+      }
+      H->frc_dirty_from = H->frc.size();
+    } else if (!H->frc_host_valid) {
+      // a parameter changed: only the surface rows depend on it; a kernel rebuilds them from the profiles (row N1)
+      launch_forcing_surface(H->S, h->d_sig, h->d_tab + ntab, h->d_frc, h->stream);
+      h->launches++;
+      if (int rc = check_launch(h, "forcing_surface")) return rc;
+    }
     h->dev_version = H->version;
+    H->forcing_on_device = true; // from now on set_par leaves the rows to the kernel
   }
   return 0;
 }
@@ -476,6 +496,16 @@ int thcm_b200_jacobian(thcm_b200_t* h, const double* d_x) {
   return jac_part(h, d_x, 0);
 }
 
+// THCM::evaluateB (THCM.C:1195-1235): the mass-matrix diagonal alone (time steppers ask for it without a Jacobian)
+int thcm_b200_evaluate_b(thcm_b200_t* h, double* d_diagB) {
+  CHECK_H(h);
+  if (int rc = refresh_device(h)) return rc;
+  AsmArgs a = asm_args(h, nullptr);
+  launch_diagb(a.S, h->d_sig, a.sp, d_diagB ? d_diagB : h->d_diagB, h->stream);
+  h->launches++;
+  return check_launch(h, "diagb");
+}
+
 int thcm_b200_exchange_mode(thcm_b200_t* h) {
   if (!h) return -1;
   return !h->dist ? 0 : (dist_p2p(h->dist) ? 2 : 1);
@@ -562,6 +592,7 @@ int thcm_b200_set_values_host(thcm_b200_t* h, const double* val) {
 }
 int thcm_b200_forcing_host(thcm_b200_t* h, double* frc) {
   CHECK_H(h);
+  h->host->refresh_host_forcing(); // after a parameter change only the device copy is current: rebuild the host one on demand
   std::memcpy(frc, h->host->frc.data(), h->host->frc.size() * sizeof(double));
   return 0;
 }

@@ -24,6 +24,9 @@ struct AsmArgs {
   int kz0, nkz;           // restrict the launch to nkz tile layers starting at layer kz0 (nkz = 0: all layers)
 };
 int asm_tile_levels();    // model levels per tile layer
+void launch_diagb(const Scalars& S, const uint64_t* sig, const SpecialRows& sp, double* diagB, cudaStream_t st); // THCM::evaluateB
+// surface rows of Frc from the per-latitude profiles (device copy of Host::fprof) after a parameter change
+void launch_forcing_surface(const Scalars& S, const uint64_t* sig, const double* fprof, double* frc, cudaStream_t st);
 void launch_jac(const AsmArgs& a, cudaStream_t st);
 void launch_rhs(const AsmArgs& a, cudaStream_t st);
 void launch_asm(const AsmArgs& a, cudaStream_t st); // Jacobian and residual of the same state in one pass over the staged tiles

@@ -210,7 +210,10 @@ void Host::set_par(int idx1, double value) {
   if (cfg.vmix != 0 && (par[P_MIXP] * par[P_PE_H] != 0.0 || par[P_MKAP] * par[P_PE_H] != 0.0 || (1.0 - par[P_ALPC]) * par[P_ENER] * par[P_PE_V] != 0.0))
     throw std::runtime_error("thcm_b200: MIXP/MKAP/ALPC settings enable neutral-physics or consistent mixing, which the B200 path does not implement");
   build_tables();
-  build_forcing(true); // forcing.F90 depends on the parameters through the surface terms only (the body term is an exact zero)
+  // forcing.F90 depends on the parameters through the surface terms only (the body term is an exact zero).  With a device
+  // attached only the per-latitude profiles are rebuilt here; the rows are filled by a kernel and the host copy goes stale.
+  if (forcing_on_device) { forcing_profiles(); frc_host_valid = false; }
+  else build_forcing(true);
   version++;
 }
 
@@ -451,7 +454,58 @@ double wfun(double yy, int v1) {
 }
 } // namespace
 
-// forcing.F90:4-218 (idealized, uncoupled salinity) followed by the Frc zeroing of boundary.F90
+// forcing.F90:4-218 (idealized, uncoupled salinity): the surface forcing of an OCEAN cell depends on its latitude only, so it is
+// evaluated once per latitude -- fprof = [fu | fv | ft | fs], each (m + 2) doubles indexed by the global Fortran j -- with the
+// reference's expressions and summation order.  The host fill below and the device kernel (forcing_surface_kernel, capi.cu /
+// thcm_kernels.cu) both only copy these numbers into the rows, so they cannot disagree.
+void Host::forcing_profiles() {
+  const int TRES = cfg.tres, SRES = cfg.sres;
+  const double gymin = cfg.ymin, gymax = cfg.ymax;
+  auto temfun = [&](double yy) {
+    if (cfg.forcing_type == 2) return std::cos(pi * (yy - gymin) / (gymax - gymin));
+    return std::cos(pi * yy / gymax) + par[P_CMPR] * std::sin(pi * yy / gymax);
+  };
+  auto salfun = [&](double yy) {
+    if (cfg.forcing_type == 2) return std::cos(pi * (yy - gymin) / (gymax - gymin));
+    if (cfg.forcing_type == 1) return (std::cos(pi * yy / gymax) + par[P_FPER] * yy / gymax) / std::cos(yy);
+    return std::cos(pi * yy / gymax) + par[P_FPER] * yy / gymax;
+  };
+  // thcm_forcing_integral_ (THCM.C:2704-2740): a GLOBAL surface integral; every rank holds the global mask, so it is
+  // evaluated redundantly in the reference's summation order instead of through an allreduce.  Only the flux-forced
+  // configurations (TRES = 0 / SRES = 0) need it.
+  std::vector<double> tj(m + 2, 0.0), sj(m + 2, 0.0), cosy(m + 2, 0.0);
+  for (int j = 1; j <= m; j++) { cosy[j] = std::cos(y[j]); tj[j] = temfun(y[j]); sj[j] = salfun(y[j]); }
+  auto qint = [&](const std::vector<double>* prof, bool times_ocean) { // prof == nullptr: the zero field
+    double lf = 0.0, ls = 0.0;
+    for (int j = 1; j <= m; j++) for (int i = 1; i <= n; i++) {
+      const int ocean = 1 - lm(i, j, l);
+      const double field = prof ? (times_ocean ? (*prof)[j] * ocean : (*prof)[j]) : 0.0;
+      lf = field * cosy[j] * ocean + lf;
+      ls = cosy[j] * ocean + ls;
+    }
+    return lf / ls;
+  };
+  fprof.assign(4 * (size_t)(m + 2), 0.0);
+  double *fu = fprof.data(), *fv = fu + (m + 2), *ft = fv + (m + 2), *fs = ft + (m + 2);
+  const double sigma = par[P_COMB] * par[P_WIND] * par[P_AL_T];
+  for (int j = 1; j <= m - 1; j++) { fu[j] = sigma * wfun(yv[j], 1); fv[j] = sigma * wfun(yv[j], 2); }
+  const double etabi = par[P_COMB] * par[P_TEMP] * (1 - TRES + TRES * par[P_BIOT]);
+  double temcor = 0.0;
+  if (cfg.coupled_T == 0) {
+    if (TRES == 0) temcor = qint(&tj, false);
+    for (int j = 1; j <= m; j++) ft[j] = etabi * (tj[j] - temcor);
+  }
+  // coupled_T == 1 with no atmosphere attached: tatm = qatm = albe = msi = 0, lvsc = 0 => Frc(TT) = par(COMB)*par(SUNP)*suno(j)*(1-albe0)
+  // with the unset albe0 = 0; only meaningful once set_atmos_parameters exists (SURVEY.md row N2), kept at 0 here.
+  const double gamma = par[P_COMB] * par[P_SALT] * (1 - SRES + SRES * par[P_BIOT]);
+  double salcor = 0.0, adapted_salcor = 0.0, spertcor = 0.0;
+  if (SRES == 0) { salcor = qint(&sj, true); adapted_salcor = qint(nullptr, false); spertcor = qint(nullptr, false); }
+  for (int j = 1; j <= m; j++) // emip = salfun * (1 - landm) = salfun on an ocean cell
+    fs[j] = gamma * (1 - par[P_HMTP]) * (sj[j] * 1 - salcor) + gamma * par[P_HMTP] * (0.0 - adapted_salcor) +
+            par[P_SPER] * (1 - SRES + SRES * par[P_BIOT]) * (0.0 - spertcor);
+}
+
+// Frc on the host: the surface rows from fprof, the body rows (an exact zero), then the Frc zeroing of boundary.F90
 void Host::build_forcing(bool surface_only) {
   const size_t nrows = 6 * (size_t)S.nown;
   const size_t top = 6 * (size_t)nloc * mloc * (l - 1); // first row of the surface level (levels are the slowest index)
@@ -463,56 +517,15 @@ void Host::build_forcing(bool surface_only) {
     frc.assign(nrows, 0.0);
     frc_dirty_from = 0;
   }
-  const int TRES = cfg.tres, SRES = cfg.sres;
-  const double gymin = cfg.ymin, gymax = cfg.ymax;
+  forcing_profiles();
+  frc_host_valid = true;
   const int i1 = io0, i2 = io0 + nloc - 1, j1 = jo0, j2 = jo0 + mloc - 1; // owned block, global Fortran indices
   auto row = [&](int i, int j, int k, int X) { return 6 * cell_index(S, i, j, k) + X - 1; };
-  auto temfun = [&](double yy) {
-    if (cfg.forcing_type == 2) return std::cos(pi * (yy - gymin) / (gymax - gymin));
-    return std::cos(pi * yy / gymax) + par[P_CMPR] * std::sin(pi * yy / gymax);
-  };
-  auto salfun = [&](double yy) {
-    if (cfg.forcing_type == 2) return std::cos(pi * (yy - gymin) / (gymax - gymin));
-    if (cfg.forcing_type == 1) return (std::cos(pi * yy / gymax) + par[P_FPER] * yy / gymax) / std::cos(yy);
-    return std::cos(pi * yy / gymax) + par[P_FPER] * yy / gymax;
-  };
-  // thcm_forcing_integral_ (THCM.C:2704-2740): a GLOBAL surface integral; every rank holds the global mask, so it is
-  // evaluated redundantly in the reference's summation order instead of through an allreduce
-  // Same operations and summation order as the reference; cos(y_j) and the profiles are evaluated once per latitude
-  // instead of once per cell (a parameter change runs this twice per Newton step, Continuation.H:405-410).
-  std::vector<double> cosy(m + 2, 0.0);
-  for (int j = 1; j <= m; j++) cosy[j] = std::cos(y[j]);
-  auto qint = [&](const std::vector<double>& field) {
-    double lf = 0.0, ls = 0.0;
-    for (int j = 1; j <= m; j++) for (int i = 1; i <= n; i++) {
-      const int ocean = 1 - lm(i, j, l);
-      lf = field[(size_t)(i - 1) + (size_t)n * (j - 1)] * cosy[j] * ocean + lf;
-      ls = cosy[j] * ocean + ls;
-    }
-    return lf / ls;
-  };
-  const double sigma = par[P_COMB] * par[P_WIND] * par[P_AL_T];
-  for (int j = j1; j <= std::min(j2, m - 1); j++) {
-    const double fu = sigma * wfun(yv[j], 1), fv = sigma * wfun(yv[j], 2);
-    for (int i = i1; i <= i2; i++) { frc[row(i, j, l, UU)] = fu; frc[row(i, j, l, VV)] = fv; }
+  const double *fu = fprof.data(), *fv = fu + (m + 2), *ft = fv + (m + 2), *fs = ft + (m + 2);
+  for (int j = j1; j <= j2; j++) for (int i = i1; i <= i2; i++) {
+    frc[row(i, j, l, UU)] = fu[j]; frc[row(i, j, l, VV)] = fv[j];
+    frc[row(i, j, l, TT)] = ft[j]; frc[row(i, j, l, SS)] = fs[j];
   }
-  std::vector<double> tatm((size_t)n * m, 0.0), emip((size_t)n * m, 0.0), zero2((size_t)n * m, 0.0);
-  const double etabi = par[P_COMB] * par[P_TEMP] * (1 - TRES + TRES * par[P_BIOT]);
-  double temcor = 0.0;
-  if (cfg.coupled_T == 0) {
-    for (int j = 1; j <= m; j++) { const double tj = temfun(y[j]); for (int i = 1; i <= n; i++) tatm[(size_t)(i - 1) + (size_t)n * (j - 1)] = tj; }
-    if (TRES == 0) temcor = qint(tatm);
-    for (int j = j1; j <= j2; j++) for (int i = i1; i <= i2; i++) frc[row(i, j, l, TT)] = etabi * (tatm[(size_t)(i - 1) + (size_t)n * (j - 1)] - temcor);
-  }
-  // coupled_T == 1 with no atmosphere attached: tatm = qatm = albe = msi = 0, lvsc = 0 => Frc(TT) = par(COMB)*par(SUNP)*suno(j)*(1-albe0)
-  // with the unset albe0 = 0; only meaningful once set_atmos_parameters exists (SURVEY.md row N2), kept at 0 here.
-  const double gamma = par[P_COMB] * par[P_SALT] * (1 - SRES + SRES * par[P_BIOT]);
-  double salcor = 0.0, adapted_salcor = 0.0, spertcor = 0.0;
-  for (int j = 1; j <= m; j++) { const double sj = salfun(y[j]); for (int i = 1; i <= n; i++) emip[(size_t)(i - 1) + (size_t)n * (j - 1)] = sj * (1 - lm(i, j, l)); }
-  if (SRES == 0) { salcor = qint(emip); adapted_salcor = qint(zero2); spertcor = qint(zero2); }
-  for (int j = j1; j <= j2; j++) for (int i = i1; i <= i2; i++)
-    frc[row(i, j, l, SS)] = gamma * (1 - par[P_HMTP]) * (emip[(size_t)(i - 1) + (size_t)n * (j - 1)] - salcor) +
-                            gamma * par[P_HMTP] * (0.0 - adapted_salcor) + par[P_SPER] * (1 - SRES + SRES * par[P_BIOT]) * (0.0 - spertcor);
   if (!surface_only)
   for (int k = 1; k <= l - 1; k++) for (int j = j1; j <= j2; j++) for (int i = i1; i <= i2; i++) // internal T/S forcing is zero (THCM.C:540-544)
     frc[row(i, j, k, WW)] = -par[P_COMB] * (1 - lm(i, j, k)) * par[P_RAYL] * (par[P_LAMB] * (0.0 + 0.0) / 2. - (0.0 + 0.0) / 2.);

@@ -77,6 +77,9 @@ class Host {
 
   std::vector<unsigned> diag_info() const; // per row: where its own cell's 6x6 block entries sit (scaling.cu)
 
+  std::vector<double> fprof;    // surface forcing of an ocean cell per latitude: fu | fv | ft | fs, (m + 2) doubles each (forcing_profiles)
+  bool forcing_on_device = false, frc_host_valid = true; // set_par leaves `frc` stale when a kernel fills the device copy
+  void refresh_host_forcing() { if (!frc_host_valid) build_forcing(true); }
   size_t frc_dirty_from = 0; // first row of `frc` a device copy made before the last change does not have yet
   Tables tables(const double* base) const; // pointers into a (host or device) copy of `tab`
   inline int lm(int i, int j, int k) const { return landm[(size_t)i + (size_t)(n + 2) * (j + (size_t)(m + 2) * k)]; }
@@ -89,6 +92,7 @@ class Host {
   void build_tables();
   // surface_only: a parameter change touches the top level only (wind stress, surface T/S forcing); the body rows stay zero
   void build_forcing(bool surface_only = false);
+  void forcing_profiles();
   void build_graph();
   void check_supported() const;
 };

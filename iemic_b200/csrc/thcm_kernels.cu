@@ -499,6 +499,39 @@ __global__ void intcond_finish_kernel(const double* dotval, double sign, double 
   if (p2 >= 0) F[p2] = 0.0;
 }
 
+// Surface rows of the forcing vector after a parameter change (forcing.F90:4-218 through Host::forcing_profiles): one thread
+// per owned surface cell copies the per-latitude values of an ocean cell into its six rows and applies the Frc zeroing of
+// `boundaries` -- the same selection Host::build_forcing makes, no arithmetic, hence the same bits.
+__global__ void __launch_bounds__(256) forcing_surface_kernel(const Scalars S, const uint64_t* __restrict__ sig, const double* __restrict__ fprof,
+                                                              double* __restrict__ frc) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= S.nloc * S.mloc) return;
+  const int li = t % S.nloc, lj = t / S.nloc, j = S.jo0 + lj;
+  const size_t c = ((size_t)(S.l - 1) * S.mloc + lj) * S.nloc + li;
+  const uint64_t g = __ldg(sig + c);
+  const int stride = S.m + 2;
+  double v[6];
+  v[0] = frc_masked<UU>(g) ? 0.0 : __ldg(fprof + j);
+  v[1] = frc_masked<VV>(g) ? 0.0 : __ldg(fprof + stride + j);
+  v[2] = 0.0;
+  v[3] = 0.0;
+  v[4] = frc_masked<TT>(g) ? 0.0 : __ldg(fprof + 2 * stride + j);
+  v[5] = frc_masked<SS>(g) ? 0.0 : __ldg(fprof + 3 * stride + j);
+  store6(frc + 6 * c, v);
+}
+
+// THCM::evaluateB (THCM.C:1195-1235): diag(B) alone, from the signatures -- fillcolB plus the zeroed P-fix / integral rows
+__global__ void __launch_bounds__(256) diagb_kernel(const Scalars S, const uint64_t* __restrict__ sig, const SpecialRows sp, double* __restrict__ diagB) {
+  const long long c = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= S.nown) return;
+  const uint64_t g = __ldg(sig + c);
+  const int row0 = (int)(6 * c);
+  double b[6];
+  b[0] = diagb_entry<UU>(S, g, sp, row0); b[1] = diagb_entry<VV>(S, g, sp, row0 + 1); b[2] = diagb_entry<WW>(S, g, sp, row0 + 2);
+  b[3] = diagb_entry<PP>(S, g, sp, row0 + 3); b[4] = diagb_entry<TT>(S, g, sp, row0 + 4); b[5] = diagb_entry<SS>(S, g, sp, row0 + 5);
+  store6(diagB + row0, b);
+}
+
 __global__ void intcond_add_kernel(const double* dotval, double sign, double* y, int row) { y[row] = y[row] + sign * (*dotval); }
 
 template <bool JAC, bool RHS> constexpr int asm_smem() {
@@ -531,6 +564,13 @@ void launch_rhs(const AsmArgs& a, cudaStream_t st) { launch_asm_t<false, true>(a
 void launch_asm(const AsmArgs& a, cudaStream_t st) { launch_asm_t<true, true>(a, st); }
 void launch_intcond_dot(const double* coefS, const double* x, long long ncell, double* partial, cudaStream_t st) {
   intcond_dot_kernel<<<1, 1024, 0, st>>>(coefS, x, ncell, partial);
+}
+void launch_forcing_surface(const Scalars& S, const uint64_t* sig, const double* fprof, double* frc, cudaStream_t st) {
+  const int cells = S.nloc * S.mloc;
+  forcing_surface_kernel<<<(cells + 255) / 256, 256, 0, st>>>(S, sig, fprof, frc);
+}
+void launch_diagb(const Scalars& S, const uint64_t* sig, const SpecialRows& sp, double* diagB, cudaStream_t st) {
+  diagb_kernel<<<(int)((S.nown + 255) / 256), 256, 0, st>>>(S, sig, sp, diagB);
 }
 void launch_intcond_add(const double* dotval, double sign, double* y, int row, cudaStream_t st) { intcond_add_kernel<<<1, 1, 0, st>>>(dotval, sign, y, row); }
 void launch_intcond_finish(const double* dotval, double sign, double corr, double* F, int row, int p1, int p2, cudaStream_t st) {

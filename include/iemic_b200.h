@@ -96,6 +96,9 @@ int thcm_b200_halo_exchange(thcm_b200_t* h, double* d_x);
 /* how the exchange steps travel: 0 one GPU (nothing to exchange), 1 NCCL send/recv + allreduce, 2 peer memory over
  * NVLink (CUDA IPC; halo push/pull kernels, reductions finished inside the reducing kernels).  Mode 2 is chosen when
  * every rank can map every other rank's buffers; IEMIC_P2P=0 in the environment forces mode 1. */
+/* THCM::evaluateB (src/ocean/THCM.C:1195-1235): diag(B) alone into d_diagB (nrows_local doubles; NULL: the handle's own array
+ * that thcm_b200_csr returns) -- fillcolB (assemble.F90:18-54) with the fixed-pressure and integral rows zeroed. */
+int thcm_b200_evaluate_b(thcm_b200_t* h, double* d_diagB);
 int thcm_b200_exchange_mode(thcm_b200_t* h);             /* fills the halo part of a stored vector (no-op on 1 GPU) */
 /* residual (d_F may be NULL) and/or Jacobian on one state; on several GPUs the halo exchange of d_x runs concurrently with
  * the tiles that read no halo cell (NCCL on a second stream), the rim tiles follow.  Replaces the sequence

@@ -354,3 +354,28 @@ def test_parameter_change_after_first_evaluation(name):
     rows = np.repeat(np.arange(rp.size - 1), np.diff(rp))
     tracer = (rows % 6 >= 4) & (col % 6 >= 4)
     assert np.array_equal(vo[~tracer], vg[~tracer]) and np.array_equal(bo, bg)
+
+
+@pytest.mark.parametrize("name", ["natl8", "2dmoc", "rand_periodic", "global4"])
+def test_parameter_change_on_the_device(name):
+    """Row N1: after the first evaluation set_par only rebuilds per-latitude profiles on the host; a kernel refills the surface rows
+    of Frc on the device.  Residual after a chain of parameter changes == oracle with the same parameters (bit level outside the
+    tanh rows), the host copy of the forcing (rebuilt on demand) == oracle, and diag(B) alone == the Jacobian pass's."""
+    import torch
+    cfg, mask, O, G = cases.make_pair(name)
+    x = cases.state(cfg, mask, seed=12)
+    G.computeRHS_host(x)
+    for pname, val in (("COMB", 0.37), ("WIND", 0.8), ("TEMP", 7.5), ("SALT", 0.4), ("CMPR", 0.2), ("FPER", 0.1), ("COMB", 0.371)):
+        O.set_par(pname, val)
+        G.setPar(pname, val)
+        Fo = O.rhs(x)
+        Fg = G.computeRHS_host(x)
+        ts = _mix_rows(cfg, Fo.size)
+        assert np.array_equal(Fo[~ts], Fg[~ts]), pname
+        assert np.abs(Fo - Fg).max() <= 1e-12 * max(np.abs(Fo).max(), 1e-300), pname
+    assert np.array_equal(G.forcing_host(), O.frc())
+    vg, bg = G.computeJacobian_host(x)
+    d = torch.full((G.nrows,), 9.0, dtype=torch.float64, device="cuda")
+    G.evaluateB(d)
+    G.sync()
+    assert np.array_equal(d.cpu().numpy(), bg)
