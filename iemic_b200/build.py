@@ -19,6 +19,7 @@ COMMON = ["-O3", "-std=c++17", "-lineinfo", "--expt-relaxed-constexpr", "-Xcompi
 UNITS = [
     ("thcm_kernels.cu", ["-fmad=false"]),
     ("spmv.cu", []),
+    ("spmv_tile.cu", ["-fmad=false"]),
     ("gmres.cu", []),
     ("scaling.cu", ["-fmad=false"]),
     ("dist.cu", []),

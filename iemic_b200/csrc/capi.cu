@@ -290,9 +290,19 @@ int spmv_impl(thcm_b200* h, double* d_x, double* d_y) {
   }
   {
     Timed t(h, 2);
-    SpmvPlan p{h->nblk, h->d_blkrow, spmv_nnz_cap(), h->d_blkp0, h->d_blkreg, h->spmv_tab};
-    launch_spmv(p, h->d_rowptr, h->d_col, h->d_val, d_x, d_y, h->stream);
-    h->launches++;
+    static const bool tile = !(getenv("IEMIC_SPMV_TILE") && getenv("IEMIC_SPMV_TILE")[0] == '0');
+    if (tile) { // the handle's matrix always has the static THCM pattern: structured product (spmv_tile.cu)
+      Host* H = h->host;
+      int long_row = -1;
+      if (H->owns_rowintcon && H->rowintcon_local >= 0 &&
+          H->rowptr[H->rowintcon_local + 1] - H->rowptr[H->rowintcon_local] > spmv_tile_long_row()) long_row = H->rowintcon_local;
+      launch_spmv_tile(H->S, h->d_rowptr, h->d_col, h->d_val, d_x, d_y, long_row, h->stream);
+      h->launches += long_row >= 0 ? 2 : 1;
+    } else {
+      SpmvPlan p{h->nblk, h->d_blkrow, spmv_nnz_cap(), h->d_blkp0, h->d_blkreg, h->spmv_tab};
+      launch_spmv(p, h->d_rowptr, h->d_col, h->d_val, d_x, d_y, h->stream);
+      h->launches++;
+    }
   }
   if (int rc = check_launch(h, "spmv")) return rc;
   // Dense salinity-integral row on several GPUs (THCM.C:2494-2513): the owner's CSR row holds the columns it owns,

@@ -56,6 +56,9 @@ struct SpmvPlan {
   SpmvTab tab;                   // column offsets of a regular cell, relative to 6 * cell
 };
 void launch_spmv(const SpmvPlan& p, const int* rowptr, const int* col, const double* val, const double* x, double* y, cudaStream_t st);
+// structured product over the static THCM graph (spmv_tile.cu): columns of complete cells are compile-time tile offsets
+void launch_spmv_tile(const Scalars& S, const int* rowptr, const int* col, const double* val, const double* x, double* y, int long_row, cudaStream_t st);
+int spmv_tile_long_row();
 int spmv_nnz_cap();
 int spmv_rows_cap();
 int spmv_regular_cells(); // regular cells per block

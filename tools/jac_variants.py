@@ -19,5 +19,7 @@ def t(fn, reps=20):
     for _ in range(reps): fn()
     e1.record(); torch.cuda.synchronize()
     return e0.elapsed_time(e1) / reps
-print(os.path.basename(os.environ.get("IEMIC_B200_LIB", "default")), "vmix", vm, "mask", kind, "state", os.environ.get("STATE", "random"),
+y = torch.empty_like(x)
+sp = t(lambda: G.applyMatrix(x, y))
+print(os.path.basename(os.environ.get("IEMIC_B200_LIB", "default")), "spmv ms %.4f" % sp, "vmix", vm, "mask", kind, "state", os.environ.get("STATE", "random"),
       "jac ms %.4f rhs ms %.4f fused ms %.4f" % (t(lambda: G.computeJacobian(x)), t(lambda: G.computeRHS(x, F)), t(lambda: G.assemble(x, F, jacobian=True))))
