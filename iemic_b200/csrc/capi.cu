@@ -997,9 +997,14 @@ int gmres_b200_solve(thcm_b200_t* h, const double* d_b, double* d_x, int m, int 
       }
       space = i; done_in_cycle = i + 1;
       if (check_every > 0 && ((i + 1) % check_every == 0)) {
-        CU(cudaMemcpyAsync(&resid, g.hist + i, sizeof(double), cudaMemcpyDeviceToHost, st));
+        // look at the residuals of the last check_every iterations in order: the FIRST one below the tolerance is where the
+        // reference (which tests every iteration) stops; columns computed beyond it are simply not used
+        const int q0 = i + 1 - check_every;
+        CU(cudaMemcpyAsync(hbuf.data() + q0, g.hist + q0, check_every * sizeof(double), cudaMemcpyDeviceToHost, st));
         CU(cudaStreamSynchronize(st));
-        if (resid < tol) { conv = true; break; }
+        for (int q = q0; q <= i; q++)
+          if (hbuf[q] < tol) { conv = true; iter -= i - q; space = q; done_in_cycle = q + 1; break; }
+        if (conv) break;
       }
     }
     if (int rc = check_launch(h, "gmres cycle")) return rc;

@@ -180,7 +180,9 @@ template <int A> __device__ __forceinline__ double complete_row_side(const doubl
 __global__ void __launch_bounds__(NTHREADS, 2) spmv_tile_kernel(const Scalars S, const int* __restrict__ rowptr, const int* __restrict__ col,
                                                                 const double* __restrict__ val, const double* __restrict__ x, double* __restrict__ y) {
   extern __shared__ __align__(16) double sm[];
-  const int gi0 = S.io0 + blockIdx.x * TI, gj0 = S.jo0 + blockIdx.y * TJ, gk0 = 1 + blockIdx.z * TK;
+  // the bottom and the top layer of tiles hold the clipped rows (slower path): they are scheduled first, not in the tail
+  const int ntz = gridDim.z, bz = blockIdx.z == 0 ? 0 : (blockIdx.z == 1 ? ntz - 1 : (int)blockIdx.z - 1);
+  const int gi0 = S.io0 + blockIdx.x * TI, gj0 = S.jo0 + blockIdx.y * TJ, gk0 = 1 + bz * TK;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int lj = warp % TJ, lk = warp / TJ;
   const int i = gi0 + lane, j = gj0 + lj, k = gk0 + lk;
