@@ -23,7 +23,20 @@ def test_multi_gpu_parity(nproc, p2p):
     env = dict(os.environ, IEMIC_P2P="1" if p2p == "peer" else "0", IEMIC_DEBUG="1")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(nproc), "--master-addr", "127.0.0.1",
            "--master-port", str(29600 + nproc + (10 if p2p == "nccl" else 0)), os.path.join(here, "dist_gpu_worker.py")]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=env)
+    # own process group + hard kill: a rank that fails while its peers wait in a collective must not leave workers spinning on the GPUs
+    p = subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, env=env, start_new_session=True)
+    try:
+        out, err = p.communicate(timeout=300)
+    except subprocess.TimeoutExpired:
+        import signal
+        os.killpg(p.pid, signal.SIGKILL)
+        out, err = p.communicate()
+        raise AssertionError("multi-GPU worker timed out\n" + out[-2000:] + err[-3000:])
+    log = os.path.join(os.path.dirname(here), "gpurun_out")
+    if os.path.isdir(log):
+        with open(os.path.join(log, "dist_worker_%d_%s.log" % (nproc, p2p)), "w") as f:
+            f.write(out + "\n---- stderr ----\n" + err)
+    r = subprocess.CompletedProcess(cmd, p.returncode, out, err)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     for k in range(nproc):
         assert "rank %d ok" % k in r.stdout
