@@ -16,6 +16,8 @@ namespace {
 
 struct Global { // what m_global::initialize keeps (global.F90:66-170)
   bool set = false;
+  int N = 0, M = 0, L = 0;
+  std::vector<int> landm; // the global mask, when the host program hands one over with m_global::set_landm
   double hdim = 0, qz = 0;
   int tres = 1, sres = 1, iza = 2, ite = 1, its = 1, coupled_T = 0, coupled_S = 0, forcing_type = 0;
 } G;
@@ -90,11 +92,11 @@ void run_matrix(const double* un) {
 extern "C" {
 #define EXPORT __attribute__((visibility("default")))
 
-EXPORT void __m_global_MOD_initialize(int*, int*, int*, double*, double*, double*, double*, double* hdim, double* qz, int*,
+EXPORT void __m_global_MOD_initialize(int* N, int* M, int* L, double*, double*, double*, double*, double* hdim, double* qz, int*,
                                       int*, int*, int* rd_mask, int* TRES, int* SRES, int* iza, int* ite, int* its, int*,
                                       int* coupled_T, int* coupled_S, int* forcing_type, const char*, const char*, const char*,
                                       const char*, const char*) {
-  G.set = true; G.hdim = *hdim; G.qz = *qz; G.tres = *TRES; G.sres = *SRES; G.iza = *iza; G.ite = *ite; G.its = *its;
+  G.set = true; G.N = *N; G.M = *M; G.L = *L; G.hdim = *hdim; G.qz = *qz; G.tres = *TRES; G.sres = *SRES; G.iza = *iza; G.ite = *ite; G.its = *its;
   G.coupled_T = *coupled_T; G.coupled_S = *coupled_S; G.forcing_type = *forcing_type;
   (void)rd_mask; // mask files are not read here: the mask arrives through init_ / set_landmask_
 }
@@ -240,4 +242,77 @@ EXPORT void __m_scaling_MOD_compute(double* db, double* row_scaling, double* col
   }
 }
 
+} // extern "C"
+
+// ---- the rest of the symbol surface THCM.C:47-174 binds ----
+// Served where the hot path has an answer (global mask hand-over, idealised forcing fields = none, parameter print-out);
+// everything that belongs to data-file forcing, time-dependent forcing or the coupled model (SURVEY rows out of scope / N2)
+// refuses loudly through the same route as every other error here: message, thcm_throw_error_ if the host has it, abort.
+namespace {
+[[noreturn]] void refuse(const char* sym, const char* why) {
+  std::fprintf(stderr, "thcm_b200 (Fortran ABI) %s: not served by the B200 path (%s)\n", sym, why);
+  typedef void (*throw_fn)(const char*);
+  if (throw_fn f = (throw_fn)dlsym(RTLD_DEFAULT, "thcm_throw_error_")) f(sym);
+  std::abort();
+}
+size_t global_mask_len() { return (size_t)(G.N + 2) * (G.M + 2) * (G.L + 2); }
+void need_global(const char* where) {
+  if (!G.set) { std::fprintf(stderr, "thcm_b200 (Fortran ABI) %s called before m_global::initialize\n", where); std::abort(); }
+}
+void zero_surface(double* a) { if (a) std::fill(a, a + (size_t)G.N * G.M, 0.0); }
+} // namespace
+
+extern "C" {
+// usrc.F90
+EXPORT void writeparams_(void) { // usrc.F90:199-234: the parameter table
+  need_model("writeparams_");
+  for (int q = 1; q <= 30; q++) { double v = 0.0; thcm_b200_get_par(M.h, q, &v); std::printf(" par(%2d) = %.15e\n", q, v); }
+}
+EXPORT void stochastic_forcing_(void) { refuse("stochastic_forcing_", "stochastic forcing is not on the hot path"); }
+EXPORT void write_levitus_(const char*) { refuse("write_levitus_", "Levitus data files are not read"); }
+// global.F90: the global land mask.  Mask FILES are not read here; a host program that has the mask hands it over with set_landm
+EXPORT void __m_global_MOD_set_maskfile(const char*) { refuse("m_global::set_maskfile", "mask files are not read; pass the mask through m_global::set_landm / init_"); }
+EXPORT void __m_global_MOD_set_landm(int* landm) { need_global("m_global::set_landm"); G.landm.assign(landm, landm + global_mask_len()); }
+EXPORT void __m_global_MOD_get_landm(int* landm) {
+  need_global("m_global::get_landm");
+  if (G.landm.size() != global_mask_len()) refuse("m_global::get_landm", "no global mask has been set: mask files are not read, call m_global::set_landm first");
+  std::copy(G.landm.begin(), G.landm.end(), landm);
+}
+EXPORT void __m_global_MOD_get_current_landm(int* landm) { __m_global_MOD_get_landm(landm); }
+EXPORT void __m_thcm_utils_MOD_get_landm(int* landm) { // the SUB-DOMAIN mask the Fortran layer works with (thcm_utils.F90)
+  need_model("m_thcm_utils::get_landm");
+  std::copy(M.landm.begin(), M.landm.end(), landm);
+}
+// idealised forcing (iza = 2, ite = its = 1): there are no data fields; the arrays THCM's constructor fetches and hands back to
+// init_ (which ignores them) are zero
+EXPORT void __m_global_MOD_get_windfield(double* taux, double* tauy) { need_global("m_global::get_windfield"); zero_surface(taux); zero_surface(tauy); }
+EXPORT void __m_global_MOD_get_temforcing(double* tatm) { need_global("m_global::get_temforcing"); zero_surface(tatm); }
+EXPORT void __m_global_MOD_get_salforcing(double* emip) { need_global("m_global::get_salforcing"); zero_surface(emip); }
+EXPORT void __m_global_MOD_get_spert(double* spert) { need_global("m_global::get_spert"); zero_surface(spert); }
+EXPORT void __m_global_MOD_get_internal_temforcing(double*) { refuse("m_global::get_internal_temforcing", "internal (data) forcing"); }
+EXPORT void __m_global_MOD_get_internal_salforcing(double*) { refuse("m_global::get_internal_salforcing", "internal (data) forcing"); }
+EXPORT void __m_global_MOD_get_monthly_forcing(double*, double*, double*, double*, int*) { refuse("m_global::get_monthly_forcing", "time-dependent forcing"); }
+EXPORT void __m_global_MOD_get_monthly_internal_forcing(double*, double*, int*) { refuse("m_global::get_monthly_internal_forcing", "time-dependent forcing"); }
+EXPORT void __m_global_MOD_get_land_temp(double*) { refuse("m_global::get_land_temp", "coupled model (SURVEY row N2)"); }
+EXPORT void __m_monthly_MOD_set_forcing(double*, double*, double*, double*, int*) { refuse("m_monthly::set_forcing", "time-dependent forcing"); }
+EXPORT void __m_monthly_MOD_set_internal_forcing(double*, double*, int*) { refuse("m_monthly::set_internal_forcing", "time-dependent forcing"); }
+EXPORT void __m_monthly_MOD_update_forcing(double*, double*, double*, double*) { refuse("m_monthly::update_forcing", "time-dependent forcing"); }
+EXPORT void __m_monthly_MOD_update_internal_forcing(double*, double*, double*) { refuse("m_monthly::update_internal_forcing", "time-dependent forcing"); }
+EXPORT void __m_usr_MOD_set_internal_forcing(double*, double*) { refuse("m_usr::set_internal_forcing", "internal (data) forcing"); }
+EXPORT void __m_thcm_utils_MOD_loadbal_weights(double*, double*, double*, double*) { refuse("m_thcm_utils::loadbal_weights", "load balancing is disabled in the reference too (TRIOS_Domain.H:271)"); }
+// I-EMIC couplings (m_inserts / m_probe / m_integrals): the coupled model's surface fields, SURVEY row N2
+#define REFUSE_N2_1(name) EXPORT void name(double*) { refuse(#name, "coupled model (SURVEY row N2)"); }
+REFUSE_N2_1(__m_inserts_MOD_insert_atmosphere_t) REFUSE_N2_1(__m_inserts_MOD_insert_atmosphere_q) REFUSE_N2_1(__m_inserts_MOD_insert_atmosphere_a)
+REFUSE_N2_1(__m_inserts_MOD_insert_atmosphere_p) REFUSE_N2_1(__m_inserts_MOD_insert_seaice_q) REFUSE_N2_1(__m_inserts_MOD_insert_seaice_m)
+REFUSE_N2_1(__m_inserts_MOD_insert_seaice_g) REFUSE_N2_1(__m_inserts_MOD_insert_emip) REFUSE_N2_1(__m_inserts_MOD_insert_adapted_emip)
+REFUSE_N2_1(__m_inserts_MOD_insert_emip_pert) REFUSE_N2_1(__m_inserts_MOD_insert_tatm)
+REFUSE_N2_1(__m_probe_MOD_get_emip) REFUSE_N2_1(__m_probe_MOD_get_suno) REFUSE_N2_1(__m_probe_MOD_get_adapted_emip) REFUSE_N2_1(__m_probe_MOD_get_emip_pert)
+REFUSE_N2_1(__m_probe_MOD_get_atmosphere_t) REFUSE_N2_1(__m_probe_MOD_get_atmosphere_q) REFUSE_N2_1(__m_probe_MOD_get_atmosphere_p)
+#undef REFUSE_N2_1
+EXPORT void __m_integrals_MOD_salt_advection(double*, double*) { refuse("m_integrals::salt_advection", "diagnostic integrals are not on the hot path"); }
+EXPORT void __m_integrals_MOD_salt_diffusion(double*, double*) { refuse("m_integrals::salt_diffusion", "diagnostic integrals are not on the hot path"); }
+EXPORT void __m_probe_MOD_get_derivatives(double*, double*, double*, double*, double*) { refuse("m_probe::get_derivatives", "coupled model (SURVEY row N2)"); }
+EXPORT void __m_probe_MOD_get_salflux(double*, double*, double*, double*, double*) { refuse("m_probe::get_salflux", "coupled model (SURVEY row N2)"); }
+EXPORT void __m_probe_MOD_get_temflux(double*, double*, double*, double*, double*, double*, double*) { refuse("m_probe::get_temflux", "coupled model (SURVEY row N2)"); }
+EXPORT void __m_probe_MOD_compute_evap(double*, double*) { refuse("m_probe::compute_evap", "coupled model (SURVEY row N2)"); }
 } // extern "C"

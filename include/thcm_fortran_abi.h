@@ -2,8 +2,9 @@
  *
  * The reference's C++ layer (src/ocean/THCM.C:47-174) binds the Fortran routines below as extern "C" symbols with GNU
  * name mangling (src/utils/my_f2c.H:15-42: `name_`, `__module_MOD_name`), every argument by pointer.
- * libthcm_b200_fortran.so exports the subset that lies on the hot path, so that THCM.C can link against it instead of the
- * Fortran objects: same argument lists, same array conventions (interleaved unknowns 6*cell+var, cells i fastest,
+ * libthcm_b200_fortran.so exports ALL 64 of them, so that THCM.C links against it instead of the Fortran objects
+ * (tests/test_fortran_link.py compiles that extern block and links it with -Wl,--no-undefined); the routines on the hot path
+ * are served by the device path, the others are listed at the end of this header with what they do: same argument lists, same array conventions (interleaved unknowns 6*cell+var, cells i fastest,
  * land mask (n+2)(m+2)(l+2) with its border ring, CSR arrays 1-based and owned by the caller).  It is a host-buffer
  * adaptor over the native device API (iemic_b200.h): one process-global model, like the Fortran module state.
  *
@@ -68,6 +69,46 @@ void fillcolb_(void);
 void __m_thcm_utils_MOD_intcond_scaling(double* values, int* indices, int* len);
 void __m_scaling_MOD_average_block(double* db);
 void __m_scaling_MOD_compute(double* db, double* row_scaling, double* col_scaling);
+
+/* ---- the rest of the surface (src/ocean/THCM.C:47-174) ----
+ * served: */
+void writeparams_(void);                                  /* usrc.F90:199-234: prints par(1..30) */
+void __m_global_MOD_set_landm(int* landm);               /* global.F90: keeps the GLOBAL (N+2)(M+2)(L+2) mask the host hands over */
+void __m_global_MOD_get_landm(int* landm);               /* ... and returns it (mask FILES are not read: loud error if none was set) */
+void __m_global_MOD_get_current_landm(int* landm);
+void __m_thcm_utils_MOD_get_landm(int* landm);           /* the sub-domain mask init_ / set_landmask_ received */
+void __m_global_MOD_get_windfield(double* taux, double* tauy); /* idealised forcing has no data fields: N x M zeros */
+void __m_global_MOD_get_temforcing(double* tatm);
+void __m_global_MOD_get_salforcing(double* emip);
+void __m_global_MOD_get_spert(double* spert);
+/* refused loudly (message, thcm_throw_error_ when the host program has it, abort): data-file / time-dependent forcing and the
+ * coupled model's inserts and probes (SURVEY.md rows out of scope / N2) */
+void stochastic_forcing_(void);
+void write_levitus_(const char* file);
+void __m_global_MOD_set_maskfile(const char* maskfile);
+void __m_global_MOD_get_internal_temforcing(double* temp);
+void __m_global_MOD_get_internal_salforcing(double* salt);
+void __m_global_MOD_get_monthly_forcing(double* tatm, double* emip, double* taux, double* tauy, int* month);
+void __m_global_MOD_get_monthly_internal_forcing(double* temp, double* salt, int* month);
+void __m_global_MOD_get_land_temp(double* land);
+void __m_monthly_MOD_set_forcing(double* tatm, double* emip, double* taux, double* tauy, int* month);
+void __m_monthly_MOD_set_internal_forcing(double* temp, double* salt, int* month);
+void __m_monthly_MOD_update_forcing(double* t, double* gammaw, double* gammat, double* gammas);
+void __m_monthly_MOD_update_internal_forcing(double* t, double* gammat, double* gammas);
+void __m_usr_MOD_set_internal_forcing(double* temp, double* salt);
+void __m_thcm_utils_MOD_loadbal_weights(double* weights, double* a, double* b, double* c);
+void __m_inserts_MOD_insert_atmosphere_t(double* f); void __m_inserts_MOD_insert_atmosphere_q(double* f);
+void __m_inserts_MOD_insert_atmosphere_a(double* f); void __m_inserts_MOD_insert_atmosphere_p(double* f);
+void __m_inserts_MOD_insert_seaice_q(double* f); void __m_inserts_MOD_insert_seaice_m(double* f); void __m_inserts_MOD_insert_seaice_g(double* f);
+void __m_inserts_MOD_insert_emip(double* f); void __m_inserts_MOD_insert_adapted_emip(double* f);
+void __m_inserts_MOD_insert_emip_pert(double* f); void __m_inserts_MOD_insert_tatm(double* f);
+void __m_integrals_MOD_salt_advection(double* un, double* check); void __m_integrals_MOD_salt_diffusion(double* un, double* check);
+void __m_probe_MOD_get_emip(double* f); void __m_probe_MOD_get_suno(double* f); void __m_probe_MOD_get_adapted_emip(double* f);
+void __m_probe_MOD_get_emip_pert(double* f); void __m_probe_MOD_get_atmosphere_t(double* f); void __m_probe_MOD_get_atmosphere_q(double* f);
+void __m_probe_MOD_get_atmosphere_p(double* f); void __m_probe_MOD_compute_evap(double* oceanE, double* x);
+void __m_probe_MOD_get_derivatives(double* sol, double* dftdm, double* dfsdq, double* dfsdm, double* dfsdg);
+void __m_probe_MOD_get_salflux(double* sol, double* salflux, double* scorr, double* qsoaflux, double* qsosflux);
+void __m_probe_MOD_get_temflux(double* sol, double* totflux, double* swflux, double* shflux, double* lhflux, double* siflux, double* simask);
 
 #ifdef __cplusplus
 }
