@@ -33,7 +33,7 @@ def build_continuation_dropin():
         return EXE
     cmd = ["g++", "-std=c++17", "-O1", "-Wall", "-I", os.path.join(ROOT, "tests", "compat"), "-I", REF_CONT,
            "-I", os.path.join(ROOT, "include"), "-I", host, os.path.join(ROOT, "tests", "continuation_dropin.cpp"),
-           "-L", os.path.join(ROOT, "iemic_b200", "lib"), "-liemic_b200", "-Wl,-rpath,$ORIGIN/../../iemic_b200/lib", "-o", EXE]
+           "-L", os.path.join(ROOT, "iemic_b200", "lib"), "-liemic_b200", "-ldl", "-Wl,-rpath,$ORIGIN/../../iemic_b200/lib", "-o", EXE]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("continuation_dropin.cpp does not compile against the reference's Continuation.H:\n" + r.stderr[-4000:])
