@@ -23,6 +23,7 @@ y = torch.empty_like(x)
 for _ in range(reps):
     G.computeJacobian(x)
     G.computeRHS(x, F)
+    G.assemble(x, F, jacobian=True)   # the step's own kernel: Jacobian + residual fused
     G.applyMatrix(x, y)
 G.sync()
 # row N3: scaling and the point-block-Jacobi builder on the current Jacobian
