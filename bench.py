@@ -191,11 +191,14 @@ class CpuArm:
         jj = np.arange(j0 - gs, j1 + gn)
         nb, mb = ii.size, jj.size
         sub = np.ones((l + 2, mb + 2, nb + 2), np.int32)
-        ring_i = np.concatenate(([ii[0] - 1], ii, [ii[-1] + 1])) % n
-        ring_j = np.clip(np.concatenate(([jj[0] - 1], jj, [jj[-1] + 1])), -1, m)
-        full = self.mask
-        sub[:, :, :] = full[np.ix_(np.arange(l + 2), ring_j + 1, ring_i + 1)]
         block_periodic = perio and self.npN == 1
+        ring_j = np.clip(np.concatenate(([jj[0] - 1], jj, [jj[-1] + 1])), -1, m) + 1      # indices into the (m + 2) mask
+        if block_periodic:
+            ring_i = np.arange(n + 2)                                                      # the global mask's own ring (PERIO markers)
+        else:
+            ring_i = np.concatenate(([ii[0] - 1], ii, [ii[-1] + 1])) % n + 1
+        full = self.mask
+        sub[:, :, :] = full[np.ix_(np.arange(l + 2), ring_j, ring_i)]
         if not block_periodic:                                       # a cut side is a wall for the sub-domain (usrc.F90:96-107)
             sub[:, :, 0] = 1; sub[:, :, -1] = 1
         sub[:, 0, :] = np.where(jj[0] == 0, sub[:, 0, :], 1); sub[:, -1, :] = np.where(jj[-1] == m - 1, sub[:, -1, :], 1)

@@ -99,6 +99,37 @@ def test_I4_jacobian_vs_finite_differences(name):
         assert np.all(np.abs(fd - ref)[ocean] <= tol[ocean]), (j, np.abs(fd - ref)[ocean].max())
 
 
+def test_I4_global4_sampled_columns():
+    """I4 on BASELINE config 2 (global 4 degree, 96x38x12: Coriolis, stretched levels qz = 2.25, half of the cells land): the
+    analytic Jacobian against forward differences of F on sampled columns, sparse (262 656 unknowns)."""
+    cfg, mask, O = _oracle("global4")
+    x = cases.state(cfg, mask, seed=3)
+    n, m, l = cfg["n"], cfg["m"], cfg["l"]
+    ocean = np.repeat((mask[1:l + 1, 1:m + 1, 1:n + 1] == 0).ravel(), 6)
+    wall = np.zeros((l, m, n, 6), bool)
+    wall[:, m - 1, :, 0:2] = True
+    x.reshape(l, m, n, 6)[wall] = 0.0
+    val, _ = O.jac(x)
+    rp, col = O.graph()
+    Jc = sp.csr_matrix((val, col, rp), shape=(O.ndim, O.ndim)).tocsc()
+    F0 = O.rhs(x)
+    h = 1e-6
+    rng = np.random.default_rng(0)
+    cand = np.nonzero(ocean & ~wall.ravel())[0]
+    scale = max(np.abs(val).max(), 1.0)
+    worst = 0.0
+    for j in rng.choice(cand, size=48, replace=False):
+        xp = x.copy()
+        xp[j] += h
+        fd = (O.rhs(xp) - F0) / h
+        ref = np.asarray(Jc[:, j].todense()).ravel()
+        tol = np.maximum(1e-2 * np.abs(ref), 5e-3 * max(np.abs(ref).max(), 1.0))
+        err = np.abs(fd - ref)[ocean]
+        assert np.all(err <= tol[ocean]), (j, err.max())
+        worst = max(worst, err.max() / scale)
+    assert worst < 1e-2
+
+
 def test_fortran_level_csr_matches_static_graph_values():
     """The Fortran-level value-dependent CSR (assemble.F90) and the static-graph copy (THCM.C:1074-1155) hold the same matrix."""
     cfg, mask, O = _oracle("rand_box")
