@@ -339,7 +339,9 @@ __global__ void __launch_bounds__(NTHREADS, JAC ? JAC_MINB : RHS_MINB) asm_kerne
   constexpr int NF = RHS ? 9 : 5;                     // staged field arrays
   constexpr int SCRW = JAC ? 32 * STRIDE : 0;         // scratch doubles per warp
   const Scalars& S = a.S;
-  const int bx = blockIdx.x, by = blockIdx.y, bz = blockIdx.z + a.kz0;
+  // surface layers (ocean: the expensive tiles) are scheduled first, deep layers (mostly land: bulk copies) last, so that the tail
+  // of the grid is cheap (-1 % at 1 degree, -2.5 % on the 90x80x32 block a rank owns on 8 GPUs)
+  const int bx = blockIdx.x, by = blockIdx.y, bz = (int)(gridDim.z - 1 - blockIdx.z) + a.kz0;
   if (a.part) { // overlap with the halo exchange: rim tiles wait for it, the others do not (block-uniform exit)
     const bool rim = bx == 0 || bx == a.ntx - 1 || by == 0 || by == a.nty - 1;
     if (rim != (a.part == 2)) return;

@@ -4,7 +4,7 @@ import numpy as np, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import iemic_b200 as ib
 from iemic_b200 import grids
-n, m, l = 360, 160, 32
+n, m, l = [int(v) for v in os.environ.get('GRID', '360x160x32').split('x')]
 vm = int(os.environ.get("VMIX", "1")); kind = os.environ.get("MASK", "global")
 cfg = grids.global_config(n, m, l, vmix=vm); mask = grids.synthetic_mask(n, m, l, kind=kind)
 G = ib.Ocean(cfg, mask)
