@@ -452,7 +452,7 @@ int rhs_part(thcm_b200* h, const double* d_x, double* d_F, int part, cudaStream_
     launch_rhs(a, st);
     h->launches++;
   }
-  return check_launch(h, "rhs_kernel");
+  return check_launch(h, "asm_kernel<false,true> (residual)");
 }
 int rhs_epilogue(thcm_b200* h, const double* d_x, double* d_F) { // THCM.C:1006-1033
   Host* H = h->host;
@@ -477,7 +477,7 @@ int jac_part(thcm_b200* h, const double* d_x, int part, int kz0 = 0, int nkz = 0
     launch_jac(a, h->stream);
     h->launches++;
   }
-  return check_launch(h, "jac_kernel");
+  return check_launch(h, "asm_kernel<true,false> (Jacobian)");
 }
 // Jacobian and residual of one state in ONE kernel: the residual operator is built from the tile the Jacobian pass staged.
 int asm_part(thcm_b200* h, const double* d_x, double* d_F, int part, int kz0 = 0, int nkz = 0) {

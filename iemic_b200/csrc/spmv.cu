@@ -12,7 +12,7 @@
 // reference's serial loop and independent of the launch configuration.
 // A row longer than NNZ_CAP (the dense salinity-integral row, src/ocean/THCM.C:2494-2513) gets a block to itself
 // and a block-wide tree reduction.
-// The default kernel (spmv_kernel_r) additionally knows the graph's "regular" cells (kernels.h): blocks of whole regular
+// The kernel used when IEMIC_SPMV_TILE=0 (spmv_kernel_r; the default is spmv_tile.cu) additionally knows the graph's "regular" cells (kernels.h): blocks of whole regular
 // cells compute their columns and row boundaries instead of loading them and keep their products transposed in shared
 // memory.  Measured at 1 degree: 0.586 ms generic -> 0.509 ms (4.9 TB/s of the 12 B/nnz model; real DRAM traffic is lower).
 // HBM traffic: 12 B per non-zero (8 B where the columns are computed) + 4 B rowptr + 8 B y per row + x once.
