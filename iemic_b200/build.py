@@ -21,6 +21,8 @@ UNITS = [
     ("spmv.cu", []),
     ("spmv_tile.cu", ["-fmad=false"]),
     ("gmres.cu", []),
+    ("gmres_cycle.cu", []),
+    ("gmres_cluster.cu", []),
     ("scaling.cu", ["-fmad=false"]),
     ("dist.cu", []),
     ("capi.cu", ["-Xcompiler", "-fvisibility=default"]),

@@ -43,6 +43,8 @@ struct GmresWs {
   int m = 0; long long n = 0, ld = 0; bool haveZ = false;
   double *V = nullptr, *Z = nullptr, *w = nullptr, *r = nullptr, *tmp = nullptr;
   double *H = nullptr, *cs = nullptr, *sn = nullptr, *s = nullptr, *y = nullptr, *hist = nullptr;
+  double* cyc_part = nullptr;  // block partials of the cooperative one-launch cycle (gmres_cycle.cu)
+  double* cyc_flags = nullptr; // two ints: columns built, stopped on the tolerance (gmres_cycle.cu, gmres_cluster.cu)
 };
 
 struct TimedEv { int which; cudaEvent_t a, b; };
@@ -251,7 +253,7 @@ int gmres_alloc(thcm_b200* h, int m, bool needZ) {
   const long long n = h->nrows();
   const long long ld = (h->nvec() + 31) / 32 * 32; // basis vectors double as SpMV inputs: room for the halo
   if (g.m >= m && g.n == n && (!needZ || g.haveZ)) return 0;
-  double** ptrs[] = {&g.V, &g.Z, &g.w, &g.r, &g.tmp, &g.H, &g.cs, &g.sn, &g.s, &g.y, &g.hist};
+  double** ptrs[] = {&g.V, &g.Z, &g.w, &g.r, &g.tmp, &g.H, &g.cs, &g.sn, &g.s, &g.y, &g.hist, &g.cyc_part, &g.cyc_flags};
   for (auto p : ptrs) if (*p) { cudaFree(*p); *p = nullptr; }
   g.m = m; g.n = n; g.ld = ld; g.haveZ = needZ;
   CU(cudaMalloc((void**)&g.V, (size_t)(m + 1) * ld * sizeof(double)));
@@ -267,10 +269,12 @@ int gmres_alloc(thcm_b200* h, int m, bool needZ) {
   CU(cudaMalloc((void**)&g.s, (m + 2) * sizeof(double)));
   CU(cudaMalloc((void**)&g.y, (m + 2) * sizeof(double)));
   CU(cudaMalloc((void**)&g.hist, (m + 2) * sizeof(double)));
+  if (!h->dist && n <= gmres_cycle_max_rows()) CU(cudaMalloc((void**)&g.cyc_part, (size_t)gmres_cycle_partials(m) * sizeof(double)));
+  CU(cudaMalloc((void**)&g.cyc_flags, 2 * sizeof(double)));
   return 0;
 }
 void gmres_free(GmresWs& g) {
-  double** ptrs[] = {&g.V, &g.Z, &g.w, &g.r, &g.tmp, &g.H, &g.cs, &g.sn, &g.s, &g.y, &g.hist};
+  double** ptrs[] = {&g.V, &g.Z, &g.w, &g.r, &g.tmp, &g.H, &g.cs, &g.sn, &g.s, &g.y, &g.hist, &g.cyc_part, &g.cyc_flags};
   for (auto p : ptrs) if (*p) { cudaFree(*p); *p = nullptr; }
   g.m = 0;
 }
@@ -936,6 +940,55 @@ int gmres_b200_solve(thcm_b200_t* h, const double* d_b, double* d_x, int m, int 
     launch_scale_copy(g.r, g.V, n, beta, 1, 0, st); L();
     int i, space = 0, done_in_cycle = 0;
     bool conv = false;
+    // Small single-GPU problems: the whole cycle is ONE launch -- same algorithm, no launch and no host round trip per
+    // iteration.  Tiny ones (the basis fits the shared memory of one cluster: 2-D MOC, the 8x8x4 box) run in gmres_cluster.cu,
+    // L2-resident ones in the cooperative kernel of gmres_cycle.cu.  IEMIC_GMRES_CYCLE=0 keeps the kernel-per-operation path
+    // below, =coop skips the cluster kernel, =cluster skips the cooperative one.
+    const char* cyc_env = getenv("IEMIC_GMRES_CYCLE");
+    const bool cyc_any = !(cyc_env && cyc_env[0] == '0') && !h->dist && prec != GMRES_B200_PREC_CALLBACK && iter <= maxit;
+    const bool use_cluster = cyc_any && !(cyc_env && !strcmp(cyc_env, "coop")) && ortho != GMRES_B200_MGS && gmres_cluster_fits(n, m);
+    const bool use_coop = cyc_any && !use_cluster && !(cyc_env && !strcmp(cyc_env, "cluster")) && g.cyc_part && ortho == GMRES_B200_CGS2F &&
+                          n <= gmres_cycle_max_rows();
+    if (use_cluster || use_coop) {
+      Host* HH = h->host;
+      int* flags = reinterpret_cast<int*>(g.cyc_flags);
+      const int maxcols = std::min(m, maxit + 1 - iter); // the loop below runs while i < m && iter <= maxit
+      CU(cudaMemsetAsync(flags, 0, 2 * sizeof(int), st));
+      if (use_cluster) {
+        ClusterArgs ca;
+        ca.rowptr = h->d_rowptr; ca.col = h->d_col; ca.val = h->d_val; ca.binv = flex ? d_blockinv : nullptr;
+        ca.V = g.V; ca.Z = g.Z; ca.ld = ld; ca.n = n; ca.m = m; ca.maxcols = maxcols; ca.fused = ortho == GMRES_B200_CGS2F ? 1 : 0;
+        ca.tol = tol; ca.check = check_every > 0 ? 1 : 0; ca.out_cols = flags; ca.stop = flags + 1;
+        ca.H = g.H; ca.ldh = m + 1; ca.cs = g.cs; ca.sn = g.sn; ca.s = g.s; ca.hist = g.hist; ca.bnorm = bnorm;
+        ca.R = ca.RP = ca.KG = ca.npad = 0;
+        Timed t(h, 3);
+        if (int e = launch_gmres_cluster(ca, st)) return fail(IEMIC_B200_ECUDA, std::string("gmres cluster kernel: ") + (e > 0 ? cudaGetErrorString((cudaError_t)e) : "does not fit"));
+      } else {
+        CycleArgs ca;
+        ca.rowptr = h->d_rowptr; ca.col = h->d_col; ca.val = h->d_val; ca.binv = flex ? d_blockinv : nullptr;
+        ca.V = g.V; ca.Z = g.Z; ca.ld = ld; ca.n = n;
+        ca.long_row = (HH->owns_rowintcon && HH->rowintcon_local >= 0 &&
+                       HH->rowptr[HH->rowintcon_local + 1] - HH->rowptr[HH->rowintcon_local] > 256) ? HH->rowintcon_local : -1;
+        ca.part = g.cyc_part; ca.ldp = 0; ca.m = m; ca.maxcols = maxcols;
+        ca.tol = tol; ca.check = check_every > 0 ? 1 : 0;
+        ca.out_cols = flags; ca.stop = flags + 1;
+        ca.h1 = h1; ca.h2 = h2;
+        GivensArgs& gc = ca.gv;
+        gc.H = g.H; gc.ldh = m + 1; gc.cs = g.cs; gc.sn = g.sn; gc.s = g.s; gc.h1 = h1; gc.h2 = h2; gc.nrm2 = nrm2; gc.sq = 1; gc.pyth = 1;
+        gc.bnorm = bnorm; gc.hist = g.hist; gc.hnext = hnext; gc.j = 0;
+        Timed t(h, 3);
+        if (int e = launch_gmres_cycle(ca, st)) return fail(IEMIC_B200_ECUDA, std::string("gmres cycle kernel: ") + cudaGetErrorString((cudaError_t)e));
+      }
+      L();
+      int fl[2] = {0, 0}; // columns built, stopped on the tolerance
+      CU(cudaMemcpyAsync(fl, flags, 2 * sizeof(int), cudaMemcpyDeviceToHost, st));
+      CU(cudaStreamSynchronize(st));
+      const int cols = fl[0];
+      if (cols < 1 || cols > maxcols) return fail(IEMIC_B200_ECUDA, "gmres cycle kernel returned no column");
+      conv = fl[1] != 0;
+      // GMRESSolver.H:142-213 leaves its loop BEFORE counting the converged iteration
+      i = cols; iter += conv ? cols - 1 : cols; done_in_cycle = cols; space = cols - 1;
+    } else
     for (i = 0; i < m && iter <= maxit; i++, iter++) {
       double* vi = g.V + (size_t)i * ld;
       const bool fused = ortho == GMRES_B200_CGS2F;

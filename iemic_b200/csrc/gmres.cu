@@ -16,6 +16,7 @@
 #include <algorithm>
 #include <cstdlib>
 #include "kernels.h"
+#include "gmres_givens.cuh"
 
 namespace thcm {
 namespace {
@@ -72,7 +73,6 @@ __device__ __forceinline__ void final_sum(const double* partial, int stride, int
   }
 }
 
-__device__ void givens_step(const GivensArgs& g);
 // With gv.H set, the finishing block also performs the Arnoldi bookkeeping of this step (fused CGS2: the second
 // multi-dot is the last reduction of the step), which saves the launch of the single-thread givens kernel.
 __global__ void __launch_bounds__(RT) multi_dot_kernel(const double* __restrict__ V, long long ldv, int nv, const double* __restrict__ w,
@@ -319,38 +319,6 @@ __global__ void __launch_bounds__(RT) residual_kernel(const double* __restrict__
   for (long long i = (long long)blockIdx.x * RT + threadIdx.x; i < n; i += (long long)gridDim.x * RT) r[i] = 1.0 * b[i] + -1.0 * r[i];
 }
 
-// GMRESSolver.H:258-289
-__device__ void gen_rot(double& dx, double& dy, double& cs, double& sn) {
-  if (dy == 0.0) { cs = 1.0; sn = 0.0; }
-  else if (fabs(dy) > fabs(dx)) { double temp = dx / dy; sn = 1.0 / sqrt(1.0 + temp * temp); cs = temp * sn; }
-  else { double temp = dy / dx; cs = 1.0 / sqrt(1.0 + temp * temp); sn = temp * cs; }
-}
-__device__ void app_rot(double& dx, double& dy, double cs, double sn) {
-  double temp = cs * dx + sn * dy;
-  dy = -sn * dx + cs * dy;
-  dx = temp;
-}
-__device__ void givens_step(const GivensArgs& g) { // one thread
-  const int j = g.j;
-  double* Hc = g.H + (size_t)j * g.ldh;
-  for (int k = 0; k <= j; k++) Hc[k] = g.h1[k] + (g.h2 ? g.h2[k] : 0.0);
-  double nrm;
-  if (g.pyth) { // ||w - V h2||^2 = ||w||^2 - |h2|^2 for orthonormal V: h2[j+1] carries <w,w> from the same reduction
-    double hh = 0.0;
-    for (int k = 0; k <= j; k++) hh = fma(g.h2[k], g.h2[k], hh);
-    const double ww = g.h2[j + 1], d2 = ww - hh;
-    // (happy) breakdown: the new direction lies in span(V) to working precision.  The difference is then pure cancellation
-    // noise; H[j+1][j] = 0 ends the Krylov space here and the normalisation that rides on the next kernel divides by 1, not 0.
-    nrm = (d2 > 1.0e-28 * ww) ? sqrt(d2) : 0.0;
-  } else nrm = g.sq ? sqrt(*g.nrm2) : *g.nrm2;
-  Hc[j + 1] = nrm;
-  *g.hnext = (nrm > 0.0) ? nrm : 1.0;
-  for (int k = 0; k < j; k++) app_rot(Hc[k], Hc[k + 1], g.cs[k], g.sn[k]);
-  gen_rot(Hc[j], Hc[j + 1], g.cs[j], g.sn[j]);
-  app_rot(Hc[j], Hc[j + 1], g.cs[j], g.sn[j]);
-  app_rot(g.s[j], g.s[j + 1], g.cs[j], g.sn[j]);
-  g.hist[j] = fabs(g.s[j + 1]) / *g.bnorm;
-}
 __global__ void givens_kernel(const GivensArgs g) {
   if (threadIdx.x == 0) givens_step(g);
 }

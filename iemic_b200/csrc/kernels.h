@@ -135,6 +135,42 @@ void launch_block_jacobi(const double* binv, const double* v, double* z, long lo
 void launch_residual(const double* b, double* r, long long n, cudaStream_t st);
 
 void launch_givens(const GivensArgs& g, cudaStream_t st);
+
+// One GMRES(m) cycle in one cooperative launch (gmres_cycle.cu): single GPU, fused CGS2, no or block-Jacobi preconditioner.
+// The basis starts with v_0 in V; the kernel builds up to maxcols further columns and stops early once hist[i] < tol (check).
+struct CycleArgs {
+  const int* rowptr; const int* col; const double* val;
+  const double* binv;          // 6x6 inverse diagonal blocks or null
+  double* V; double* Z;        // basis (m+1 vectors of ld) ; preconditioned basis (with binv)
+  long long ld, n;
+  int long_row;                // row summed by a whole block (dense salinity-integral row) or -1
+  double* part; int ldp;       // gmres_cycle_partials(m) doubles ; ldp is set by the launcher
+  int m, maxcols;
+  double tol; int check;
+  int* out_cols; int* stop;    // device ints: columns built ; *stop must be 0 at launch
+  double* h1; double* h2;      // the buffers gv.h1 / gv.h2 point at
+  GivensArgs gv;
+};
+// The same cycle for a tiny problem inside one thread-block cluster, basis in distributed shared memory (gmres_cluster.cu);
+// plain CGS2 (explicit norm) or the fused variant.  R, RP, KG, npad are filled in by the launcher.
+struct ClusterArgs {
+  const int* rowptr; const int* col; const double* val;
+  const double* binv;
+  double* V; double* Z;
+  long long ld, n;
+  int m, maxcols, fused;
+  double tol; int check;
+  int* out_cols; int* stop;
+  double* H; int ldh;
+  double* cs; double* sn; double* s; double* hist;
+  const double* bnorm;
+  int R, RP, KG, npad;
+};
+int gmres_cluster_fits(long long n, int m);
+int launch_gmres_cluster(ClusterArgs a, cudaStream_t st); // 0, a cudaError_t, or -1: does not fit
+long long gmres_cycle_max_rows();
+int gmres_cycle_partials(int m);
+int launch_gmres_cycle(CycleArgs a, cudaStream_t st); // 0 or a cudaError_t
 // y = H(0:k,0:k)^-1 s(0:k)   (GMRESSolver::backSolve, :258-289)
 void launch_backsolve(const double* H, int ldh, const double* s, int k, double* y, cudaStream_t st);
 // beta = sqrt(nrm2) ; s[0] = beta ; s[1..m] = 0 ; bnorm keeps ||b|| (set separately)
