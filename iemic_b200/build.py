@@ -24,12 +24,13 @@ UNITS = [
     ("gmres_cycle.cu", []),
     ("gmres_cluster.cu", []),
     ("scaling.cu", ["-fmad=false"]),
+    ("coupled.cu", ["-fmad=false"]),
     ("dist.cu", []),
     ("capi.cu", ["-Xcompiler", "-fvisibility=default"]),
     # host-side table construction: host compiler must not contract a*b+c either
     ("thcm_host.cpp", ["-Xcompiler", "-ffp-contract=off"]),
 ]
-HEADERS = ["thcm_rows.cuh", "thcm_stage.cuh", "thcm_cell.cuh", "thcm_host.h", "kernels.h", "dist.h", "peer.cuh",
+HEADERS = ["thcm_rows.cuh", "thcm_stage.cuh", "thcm_cell.cuh", "thcm_host.h", "kernels.h", "dist.h", "peer.cuh", "gmres_givens.cuh", "gmres_guard.h",
            os.path.join("..", "..", "include", "iemic_b200.h")]
 
 

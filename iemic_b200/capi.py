@@ -90,11 +90,18 @@ def lib():
             "iemic_b200_malloc": [C.POINTER(vp), C.c_int64], "iemic_b200_free": [vp],
             "iemic_b200_memcpy_h2d": [vp, vp, C.c_int64], "iemic_b200_memcpy_d2h": [vp, vp, C.c_int64],
             "iemic_b200_device_count": [],
+            # row N2: coupling to an atmosphere / sea-ice model
+            "thcm_b200_insert_field": [vp, C.c_int, dp], "thcm_b200_set_atmos_parameters": [vp, dp], "thcm_b200_set_seaice_parameters": [vp, dp],
+            "thcm_b200_getdeps": [vp, dp], "thcm_b200_get_suno": [vp, dp], "thcm_b200_get_dftdm": [vp, vp, dp],
+            "thcm_b200_atmos_block": [vp, ip, ip, ip, dp, ip], "thcm_b200_seaice_block": [vp, vp, ip, ip, ip, dp, ip],
+            "coupling_b200_create": [vp, C.c_int, ip, ip, ip, dp, C.c_int64, C.POINTER(vp)], "coupling_b200_apply": [vp, vp, vp, C.c_int],
         }
         for name, args in sig.items():
             f = getattr(L, name)
             f.argtypes = args
             f.restype = C.c_int
+        L.coupling_b200_destroy.argtypes = [vp]
+        L.coupling_b200_destroy.restype = None
         _LIB = L
     return _LIB
 
@@ -111,7 +118,9 @@ EXPORTED = ["iemic_b200_last_error", "iemic_b200_version", "iemic_b200_device_co
             "thcm_b200_left_scale", "thcm_b200_block_jacobi",
             "gmres_b200_solve", "gmres_b200_solve_host", "gmres_b200_set_precond", "vec_b200_block_jacobi_apply", "thcm_b200_launch_count", "thcm_b200_timing_enable",
             "thcm_b200_timing_reset", "thcm_b200_timing_get", "iemic_b200_malloc", "iemic_b200_free",
-            "iemic_b200_memcpy_h2d", "iemic_b200_memcpy_d2h"]
+            "iemic_b200_memcpy_h2d", "iemic_b200_memcpy_d2h",
+            "thcm_b200_insert_field", "thcm_b200_set_atmos_parameters", "thcm_b200_set_seaice_parameters", "thcm_b200_getdeps", "thcm_b200_get_suno",
+            "thcm_b200_get_dftdm", "thcm_b200_atmos_block", "thcm_b200_seaice_block", "coupling_b200_create", "coupling_b200_apply", "coupling_b200_destroy"]
 
 
 def check(rc):
@@ -189,6 +198,59 @@ class Ocean:
         v = C.c_double()
         check(lib().thcm_b200_get_par(self.h, idx, C.byref(v)))
         return v.value
+
+    # ---- row N2: Ocean::synchronize(atmos / seaice), Ocean::getBlock, THCM::getDerivatives ----
+    FIELDS = dict(tatm=0, qatm=1, albe=2, patm=3, qsa=4, msi=5, gsi=6)
+    ATMOS_PARS = ("tdim", "qdim", "nuq", "eta", "dqso", "dqsi", "dqdt", "Eo0", "Ei0", "Cs", "t0o", "t0i", "a0", "da", "tauf", "tauc", "comb", "albf")
+    SEAICE_PARS = ("zeta", "a0", "Lf", "s0", "rhoo", "qvar", "q0")
+
+    def insert(self, which, field):
+        f = np.ascontiguousarray(field, np.float64).ravel()
+        assert f.size == self.cfg["n"] * self.cfg["m"]
+        check(lib().thcm_b200_insert_field(self.h, self.FIELDS[which], f.ctypes.data_as(C.POINTER(C.c_double))))
+
+    def set_atmos_parameters(self, pars):
+        a = np.array([float(pars[k]) for k in self.ATMOS_PARS])
+        check(lib().thcm_b200_set_atmos_parameters(self.h, a.ctypes.data_as(C.POINTER(C.c_double))))
+
+    def set_seaice_parameters(self, pars):
+        a = np.array([float(pars[k]) for k in self.SEAICE_PARS])
+        check(lib().thcm_b200_set_seaice_parameters(self.h, a.ctypes.data_as(C.POINTER(C.c_double))))
+
+    def getdeps(self):
+        out = np.zeros(7)
+        check(lib().thcm_b200_getdeps(self.h, out.ctypes.data_as(C.POINTER(C.c_double))))
+        return dict(zip(("Ooa", "Os", "nus", "eta", "lvsc", "qdim", "pQSnd"), out))
+
+    def suno(self):
+        out = np.zeros(self.cfg["n"] * self.cfg["m"])
+        check(lib().thcm_b200_get_suno(self.h, out.ctypes.data_as(C.POINTER(C.c_double))))
+        return out
+
+    def dftdm(self, d_x):
+        i0, j0, nloc, mloc, _, _ = self.block()
+        out = np.zeros(nloc * mloc)
+        check(lib().thcm_b200_get_dftdm(self.h, _ptr(d_x), out.ctypes.data_as(C.POINTER(C.c_double))))
+        return out
+
+    def _block(self, fn, *lead):
+        nm = self.cfg["n"] * self.cfg["m"]
+        rows, beg, jco, co = np.zeros(nm, np.int32), np.zeros(nm + 1, np.int32), np.zeros(3 * nm, np.int32), np.zeros(3 * nm)
+        nr = C.c_int(0)
+        ip, dp = C.POINTER(C.c_int), C.POINTER(C.c_double)
+        check(fn(self.h, *lead, rows.ctypes.data_as(ip), beg.ctypes.data_as(ip), jco.ctypes.data_as(ip), co.ctypes.data_as(dp), C.byref(nr)))
+        k = nr.value
+        return rows[:k].copy(), beg[:k + 1].copy(), jco[:beg[k]].copy(), co[:beg[k]].copy()
+
+    def atmos_block(self):
+        """Ocean::getBlock(Atmosphere), compact: (rows, beg, jco, co)"""
+        return self._block(lib().thcm_b200_atmos_block)
+
+    def seaice_block(self, d_x):
+        return self._block(lib().thcm_b200_seaice_block, _ptr(d_x))
+
+    def coupling_block(self, rows, beg, jco, co, ncols):
+        return CouplingBlock(self, rows, beg, jco, co, ncols)
 
     def set_landmask(self, landm):
         lm = np.ascontiguousarray(landm, dtype=np.int32).ravel()
@@ -371,3 +433,24 @@ class Ocean:
         t, c = C.c_double(), C.c_int64()
         check(lib().thcm_b200_timing_get(self.h, which, C.byref(t), C.byref(c)))
         return t.value, c.value
+
+
+class CouplingBlock:
+    """CouplingBlock<Ocean, Model> on the device (src/coupledmodel/CouplingBlock.H)"""
+
+    def __init__(self, ocean, rows, beg, jco, co, ncols):
+        self.ocean = ocean  # keeps the handle alive
+        rows, beg, jco = (np.ascontiguousarray(a, np.int32) for a in (rows, beg, jco))
+        co = np.ascontiguousarray(co, np.float64)
+        ip, dp = C.POINTER(C.c_int), C.POINTER(C.c_double)
+        self.b = C.c_void_p()
+        check(lib().coupling_b200_create(ocean.h, int(rows.size), rows.ctypes.data_as(ip), beg.ctypes.data_as(ip), jco.ctypes.data_as(ip),
+                                         co.ctypes.data_as(dp), int(ncols), C.byref(self.b)))
+
+    def apply(self, d_in, d_out, accumulate=False):
+        check(lib().coupling_b200_apply(self.b, _ptr(d_in), _ptr(d_out), 1 if accumulate else 0))
+
+    def __del__(self):
+        if getattr(self, "b", None):
+            lib().coupling_b200_destroy(self.b)
+            self.b = None

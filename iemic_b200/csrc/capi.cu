@@ -13,6 +13,7 @@
 #include "../../include/iemic_b200.h"
 #include "thcm_host.h"
 #include "kernels.h"
+#include "thcm_stage.cuh"
 #include "gmres_guard.h"
 #include "dist.h"
 
@@ -61,6 +62,8 @@ struct thcm_b200 {
   int* d_blkrow = nullptr; int nblk = 0; size_t d_frc_len = 0, d_tab_len = 0;
   int* d_blkp0 = nullptr; unsigned char* d_blkreg = nullptr; SpmvTab spmv_tab; size_t spmv_regular_cells = 0;
   uint64_t dev_version = 0, dev_mask_version = 0;
+  // row N2: device copies of the coupling fields (whole surface) and of the per-cell surface T forcing
+  double *d_msi = nullptr, *d_ftcell = nullptr, *d_cplf = nullptr; uint64_t dev_msi_version = 0;
   unsigned int* d_dinfo = nullptr; uint64_t dinfo_mask_version = 0; // diagonal-block positions (scaling.cu), built on first use
   // scratch vectors for the host-buffer entry points
   double *d_xs = nullptr, *d_ys = nullptr;
@@ -222,7 +225,20 @@ int refresh_device(thcm_b200* h) {
       // a parameter changed: only the surface rows depend on it; a kernel rebuilds them from the profiles (row N1)
       launch_forcing_surface(H->S, h->d_sig, h->d_tab + ntab, h->d_frc, h->stream);
       h->launches++;
+      if (H->cfg.coupled_T == 1) { // coupled to an atmosphere: the T rows are per-cell values (forcing.F90:73-96), row N2
+        const size_t nc = H->ftcell.size();
+        if (!h->d_ftcell) CU(cudaMalloc((void**)&h->d_ftcell, nc * sizeof(double)));
+        CU(cudaMemcpyAsync(h->d_ftcell, H->ftcell.data(), nc * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+        launch_forcing_cells(H->S, h->d_sig, h->d_ftcell, h->d_frc, h->stream);
+        h->launches++;
+      }
       if (int rc = check_launch(h, "forcing_surface")) return rc;
+    }
+    if (H->cfg.coupled_T == 1 && h->dev_msi_version != H->cpl.msi_version) { // sea-ice mask the coefficients were built with
+      const size_t nm = (size_t)H->n * H->m;
+      if (!h->d_msi) CU(cudaMalloc((void**)&h->d_msi, nm * sizeof(double)));
+      if (H->cpl.msi_lin.size() == nm) CU(cudaMemcpyAsync(h->d_msi, H->cpl.msi_lin.data(), nm * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+      h->dev_msi_version = H->cpl.msi_version;
     }
     h->dev_version = H->version;
     H->forcing_on_device = true; // from now on set_par leaves the rows to the kernel
@@ -236,6 +252,7 @@ AsmArgs asm_args(thcm_b200* h, const double* d_x) {
   Host* H = h->host;
   a.S = H->S;
   a.T = H->tables(h->d_tab);
+  a.T.msi = (H->cfg.coupled_T == 1 && H->cpl.have_msi) ? h->d_msi : nullptr;
   a.x = d_x; a.sig = h->d_sig; a.rowptr = h->d_rowptr; a.frc = h->d_frc; a.val = h->d_val; a.diagB = h->d_diagB;
   a.sp.rowintcon = H->owns_rowintcon ? H->rowintcon_local : -1;
   a.sp.rowPfix1 = H->rowPfix1_local; a.sp.rowPfix2 = H->rowPfix2_local;
@@ -369,7 +386,7 @@ int thcm_b200_destroy(thcm_b200_t* h) {
   cudaStreamSynchronize(h->stream);
   flush_timing(h);
   void* ptrs[] = {h->d_tab, h->d_sig, h->d_rowptr, h->d_col, h->d_val, h->d_diagB, h->d_frc, h->d_coefS, h->d_blkrow, h->d_blkp0, h->d_blkreg, h->d_xs, h->d_ys, h->d_dinfo,
-                  h->rb.partial, h->rb.ticket, h->d_small};
+                  h->d_msi, h->d_ftcell, h->d_cplf, h->rb.partial, h->rb.ticket, h->d_small};
   for (void* p : ptrs) if (p) cudaFree(p);
   gmres_free(h->g);
   if (h->copy_stream) { cudaStreamDestroy(h->copy_stream); cudaEventDestroy(h->ev_rhs); cudaEventDestroy(h->ev_copy); }
@@ -393,6 +410,143 @@ int thcm_b200_set_par(thcm_b200_t* h, int idx1, double value) {
   if (idx1 < 1 || idx1 > NPAR) return fail(IEMIC_B200_EINVAL, "parameter index out of range");
   try { h->host->set_par(idx1, value); } catch (const std::exception& e) { return fail(IEMIC_B200_ENOTSUP, e.what()); }
   return 0;
+}
+// ---- row N2: coupling to an atmosphere / sea-ice model (Coupled Temperature = 1) ----
+int thcm_b200_insert_field(thcm_b200_t* h, int which, const double* field) {
+  CHECK_H(h);
+  if (!field) return fail(IEMIC_B200_EINVAL, "insert_field: null field");
+  if (which < 0 || which > THCM_B200_FIELD_SEAICE_G) return fail(IEMIC_B200_EINVAL, "insert_field: unknown field");
+  try { h->host->insert_field(which, field); } catch (const std::exception& e) { return fail(IEMIC_B200_ENOTSUP, e.what()); }
+  return 0;
+}
+int thcm_b200_set_atmos_parameters(thcm_b200_t* h, const thcm_b200_atmos_pars* pars) {
+  CHECK_H(h);
+  if (!pars) return fail(IEMIC_B200_EINVAL, "set_atmos_parameters: null argument");
+  static_assert(sizeof(thcm_b200_atmos_pars) == 18 * sizeof(double), "atmos_pars must stay 18 doubles (usrc.F90:250-269)");
+  try { h->host->set_atmos_parameters(reinterpret_cast<const double*>(pars)); } catch (const std::exception& e) { return fail(IEMIC_B200_ENOTSUP, e.what()); }
+  return 0;
+}
+int thcm_b200_set_seaice_parameters(thcm_b200_t* h, const thcm_b200_seaice_pars* pars) {
+  CHECK_H(h);
+  if (!pars) return fail(IEMIC_B200_EINVAL, "set_seaice_parameters: null argument");
+  static_assert(sizeof(thcm_b200_seaice_pars) == 7 * sizeof(double), "seaice_pars must stay 7 doubles (usrc.F90:303-311)");
+  try { h->host->set_seaice_parameters(reinterpret_cast<const double*>(pars)); } catch (const std::exception& e) { return fail(IEMIC_B200_ENOTSUP, e.what()); }
+  return 0;
+}
+int thcm_b200_getdeps(thcm_b200_t* h, double* out7) {
+  CHECK_H(h);
+  if (!out7) return fail(IEMIC_B200_EINVAL, "getdeps: null argument");
+  h->host->getdeps(out7);
+  return 0;
+}
+int thcm_b200_get_suno(thcm_b200_t* h, double* suno) { // THCM::getSunO: the shortwave profile on every surface point
+  CHECK_H(h);
+  if (!suno) return fail(IEMIC_B200_EINVAL, "get_suno: null argument");
+  Host* H = h->host;
+  for (int j = 1; j <= H->m; j++) for (int i = 1; i <= H->n; i++) suno[(size_t)(j - 1) * H->n + (i - 1)] = H->cpl.suno[j];
+  return 0;
+}
+int thcm_b200_get_dftdm(thcm_b200_t* h, const double* d_x, double* dftdm) {
+  CHECK_H(h);
+  if (!d_x || !dftdm) return fail(IEMIC_B200_EINVAL, "get_dftdm: null argument");
+  Host* H = h->host;
+  const size_t nc = (size_t)H->nloc * H->mloc, nm = (size_t)H->n * H->m;
+  if (H->cfg.coupled_T != 1) { std::fill(dftdm, dftdm + nc, 0.0); return 0; } // probe.F90:429
+  if (int rc = refresh_device(h)) return rc;
+  // tatm | albe | qatm | suno | out
+  const size_t need = 3 * nm + (size_t)H->m + 2 + nc;
+  if (!h->d_cplf) CU(cudaMalloc((void**)&h->d_cplf, need * sizeof(double)));
+  const Host::Coupling& c = H->cpl;
+  const std::vector<double>* f[3] = {&c.tatm, &c.albe, &c.qatm};
+  const double* dev[3] = {nullptr, nullptr, nullptr};
+  for (int q = 0; q < 3; q++)
+    if (f[q]->size() == nm) {
+      CU(cudaMemcpyAsync(h->d_cplf + q * nm, f[q]->data(), nm * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+      dev[q] = h->d_cplf + q * nm;
+    }
+  CU(cudaMemcpyAsync(h->d_cplf + 3 * nm, c.suno.data(), ((size_t)H->m + 2) * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+  DftdmArgs a;
+  a.S = H->S; a.sig = h->d_sig; a.x = d_x; a.tatm = dev[0]; a.albe = dev[1]; a.qatm = dev[2]; a.suno = h->d_cplf + 3 * nm;
+  a.c = H->dftdm_scalars(); // products in the order of the Fortran expression, formed by the FMA-free host code
+  a.out = h->d_cplf + 3 * nm + H->m + 2;
+  launch_dftdm(a, h->stream);
+  h->launches++;
+  if (int rc = check_launch(h, "dftdm")) return rc;
+  CU(cudaMemcpyAsync(dftdm, a.out, nc * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  return 0;
+}
+// Ocean::getBlock(Atmosphere) (Ocean.C:1538-1664), T rows (Coupled Salinity = 1 is not on this path): for every ocean surface
+// point three entries -dF_T/dT_atm, -dF_T/dalbedo, -dF_T/dq_atm in the reference's push order, rows and columns global
+int thcm_b200_atmos_block(thcm_b200_t* h, int* rows, int* beg, int* jco, double* co, int* nrows_out) {
+  CHECK_H(h);
+  if (!rows || !beg || !jco || !co || !nrows_out) return fail(IEMIC_B200_EINVAL, "atmos_block: null argument");
+  *nrows_out = h->host->atmos_block(rows, beg, jco, co);
+  return 0;
+}
+// Ocean::getBlock(SeaIce) (Ocean.C:1667-1746), T rows: -dF_T/dM at the sea-ice mask unknown; dF_T/dM from the device (get_dftdm)
+int thcm_b200_seaice_block(thcm_b200_t* h, const double* d_x, int* rows, int* beg, int* jco, double* co, int* nrows_out) {
+  CHECK_H(h);
+  if (!d_x || !rows || !beg || !jco || !co || !nrows_out) return fail(IEMIC_B200_EINVAL, "seaice_block: null argument");
+  Host* H = h->host;
+  if (H->nranks > 1) return fail(IEMIC_B200_ENOTSUP, "seaice_block: the derivative field is not gathered over the ranks yet (one GPU only)");
+  const int N = H->n, M = H->m, L = H->l;
+  std::vector<double> d((size_t)N * M);
+  if (int rc = thcm_b200_get_dftdm(h, d_x, d.data())) return rc;
+  *nrows_out = H->seaice_block(d.data(), rows, beg, jco, co);
+  return 0;
+}
+
+// CouplingBlock (CouplingBlock.H): rows of the ocean that a neighbouring model's unknowns enter
+struct coupling_b200 { thcm_b200* h = nullptr; int nrows = 0; int *d_rows = nullptr, *d_beg = nullptr, *d_jco = nullptr; double* d_co = nullptr; int64_t ncols = 0; };
+int coupling_b200_create(thcm_b200_t* h, int nrows, const int* rows, const int* beg, const int* jco, const double* co, int64_t ncols, coupling_b200_t** out) {
+  CHECK_H(h);
+  if (!out || nrows < 0 || (nrows > 0 && (!rows || !beg || !jco || !co))) return fail(IEMIC_B200_EINVAL, "coupling_create: bad argument");
+  Host* H = h->host;
+  const int N = H->n, M = H->m;
+  // keep the rows this rank owns, local row numbers; entries of a row sorted by column as Epetra's FillComplete leaves them
+  std::vector<int> lr, lb(1, 0), lj; std::vector<double> lc;
+  for (int r = 0; r < nrows; r++) {
+    const int g = rows[r], X = g % 6, cell = g / 6, i = cell % N, j = (cell / N) % M, k = cell / (N * M);
+    if (g < 0 || (size_t)g >= H->ndim) return fail(IEMIC_B200_EINVAL, "coupling_create: row outside the ocean");
+    if (i + 1 < H->io0 || i + 1 >= H->io0 + H->nloc || j + 1 < H->jo0 || j + 1 >= H->jo0 + H->mloc) continue;
+    std::vector<std::pair<int, double>> e;
+    for (int p = beg[r]; p < beg[r + 1]; p++) {
+      if (jco[p] < 0 || jco[p] >= ncols) return fail(IEMIC_B200_EINVAL, "coupling_create: column outside the neighbouring model");
+      e.emplace_back(jco[p], co[p]);
+    }
+    std::stable_sort(e.begin(), e.end(), [](const std::pair<int, double>& a, const std::pair<int, double>& b) { return a.first < b.first; });
+    lr.push_back((int)(6 * cell_index(H->S, i + 1, j + 1, k + 1)) + X);
+    for (auto& q : e) { lj.push_back(q.first); lc.push_back(q.second); }
+    lb.push_back((int)lj.size());
+  }
+  coupling_b200* b = new coupling_b200();
+  b->h = h; b->nrows = (int)lr.size(); b->ncols = ncols;
+  int rc = 0;
+  if (b->nrows > 0) {
+    if (!rc) rc = dev_upload(&b->d_rows, lr);
+    if (!rc) rc = dev_upload(&b->d_beg, lb);
+    if (!rc) rc = dev_upload(&b->d_jco, lj);
+    if (!rc) rc = dev_upload(&b->d_co, lc);
+  }
+  if (rc) { coupling_b200_destroy(b); return rc; }
+  *out = b;
+  return 0;
+}
+int coupling_b200_apply(coupling_b200_t* b, const double* d_in, double* d_out, int accumulate) {
+  if (!b || !b->h) return fail(IEMIC_B200_EINVAL, "coupling_apply: null block");
+  if (!d_in || !d_out) return fail(IEMIC_B200_EINVAL, "coupling_apply: null vector");
+  thcm_b200* h = b->h;
+  if (!accumulate) CU(cudaMemsetAsync(d_out, 0, (size_t)h->nrows() * sizeof(double), h->stream)); // out = C in: zero outside the block's rows
+  launch_coupling_apply(b->nrows, b->d_rows, b->d_beg, b->d_jco, b->d_co, d_in, d_out, accumulate, h->stream);
+  h->launches++;
+  return check_launch(h, "coupling_apply");
+}
+void coupling_b200_destroy(coupling_b200_t* b) {
+  if (!b) return;
+  void* ptrs[] = {b->d_rows, b->d_beg, b->d_jco, b->d_co};
+  for (void* p : ptrs) if (p) cudaFree(p);
+  delete b;
 }
 int thcm_b200_get_par(thcm_b200_t* h, int idx1, double* value) {
   CHECK_H(h);

@@ -302,16 +302,42 @@ EXPORT void __m_usr_MOD_set_internal_forcing(double*, double*) { refuse("m_usr::
 EXPORT void __m_thcm_utils_MOD_loadbal_weights(double*, double*, double*, double*) { refuse("m_thcm_utils::loadbal_weights", "load balancing is disabled in the reference too (TRIOS_Domain.H:271)"); }
 // I-EMIC couplings (m_inserts / m_probe / m_integrals): the coupled model's surface fields, SURVEY row N2
 #define REFUSE_N2_1(name) EXPORT void name(double*) { refuse(#name, "coupled model (SURVEY row N2)"); }
-REFUSE_N2_1(__m_inserts_MOD_insert_atmosphere_t) REFUSE_N2_1(__m_inserts_MOD_insert_atmosphere_q) REFUSE_N2_1(__m_inserts_MOD_insert_atmosphere_a)
-REFUSE_N2_1(__m_inserts_MOD_insert_atmosphere_p) REFUSE_N2_1(__m_inserts_MOD_insert_seaice_q) REFUSE_N2_1(__m_inserts_MOD_insert_seaice_m)
-REFUSE_N2_1(__m_inserts_MOD_insert_seaice_g) REFUSE_N2_1(__m_inserts_MOD_insert_emip) REFUSE_N2_1(__m_inserts_MOD_insert_adapted_emip)
+// served for Coupled Temperature = 1 (the fields Coupled Salinity = 1 needs are ignored by the Fortran itself while that flag is off;
+// with it on the model is refused at creation): inserts.F90:12-166 -> thcm_b200_insert_field
+#define SERVE_INSERT(name, which) EXPORT void name(double* f) { need_model(#name); if (thcm_b200_insert_field(M.h, which, f) != 0) die(#name); }
+SERVE_INSERT(__m_inserts_MOD_insert_atmosphere_t, THCM_B200_FIELD_ATMOS_T) SERVE_INSERT(__m_inserts_MOD_insert_atmosphere_q, THCM_B200_FIELD_ATMOS_Q)
+SERVE_INSERT(__m_inserts_MOD_insert_atmosphere_a, THCM_B200_FIELD_ATMOS_A) SERVE_INSERT(__m_inserts_MOD_insert_atmosphere_p, THCM_B200_FIELD_ATMOS_P)
+SERVE_INSERT(__m_inserts_MOD_insert_seaice_q, THCM_B200_FIELD_SEAICE_Q) SERVE_INSERT(__m_inserts_MOD_insert_seaice_m, THCM_B200_FIELD_SEAICE_M)
+SERVE_INSERT(__m_inserts_MOD_insert_seaice_g, THCM_B200_FIELD_SEAICE_G)
+#undef SERVE_INSERT
+// Ocean::synchronize's parameter calls and getdeps (Ocean.C:1469, 1490, 1545; usrc.F90:201-333): not in THCM.C's extern block, bound by Ocean.C
+EXPORT void set_atmos_parameters_(void* pars) { need_model("set_atmos_parameters_"); if (thcm_b200_set_atmos_parameters(M.h, (const thcm_b200_atmos_pars*)pars) != 0) die("set_atmos_parameters_"); }
+EXPORT void set_seaice_parameters_(void* pars) { need_model("set_seaice_parameters_"); if (thcm_b200_set_seaice_parameters(M.h, (const thcm_b200_seaice_pars*)pars) != 0) die("set_seaice_parameters_"); }
+EXPORT void getdeps_(double* Ooa, double* Os, double* nus, double* eta, double* lvsc, double* qdim, double* pQSnd) {
+  need_model("getdeps_");
+  double o[7];
+  if (thcm_b200_getdeps(M.h, o) != 0) die("getdeps_");
+  *Ooa = o[0]; *Os = o[1]; *nus = o[2]; *eta = o[3]; *lvsc = o[4]; *qdim = o[5]; *pQSnd = o[6];
+}
+EXPORT void __m_probe_MOD_get_suno(double* suno) { need_model("m_probe::get_suno"); if (thcm_b200_get_suno(M.h, suno) != 0) die("m_probe::get_suno"); }
+REFUSE_N2_1(__m_inserts_MOD_insert_emip) REFUSE_N2_1(__m_inserts_MOD_insert_adapted_emip)
 REFUSE_N2_1(__m_inserts_MOD_insert_emip_pert) REFUSE_N2_1(__m_inserts_MOD_insert_tatm)
-REFUSE_N2_1(__m_probe_MOD_get_emip) REFUSE_N2_1(__m_probe_MOD_get_suno) REFUSE_N2_1(__m_probe_MOD_get_adapted_emip) REFUSE_N2_1(__m_probe_MOD_get_emip_pert)
+REFUSE_N2_1(__m_probe_MOD_get_emip) REFUSE_N2_1(__m_probe_MOD_get_adapted_emip) REFUSE_N2_1(__m_probe_MOD_get_emip_pert)
 REFUSE_N2_1(__m_probe_MOD_get_atmosphere_t) REFUSE_N2_1(__m_probe_MOD_get_atmosphere_q) REFUSE_N2_1(__m_probe_MOD_get_atmosphere_p)
 #undef REFUSE_N2_1
 EXPORT void __m_integrals_MOD_salt_advection(double*, double*) { refuse("m_integrals::salt_advection", "diagnostic integrals are not on the hot path"); }
 EXPORT void __m_integrals_MOD_salt_diffusion(double*, double*) { refuse("m_integrals::salt_diffusion", "diagnostic integrals are not on the hot path"); }
-EXPORT void __m_probe_MOD_get_derivatives(double*, double*, double*, double*, double*) { refuse("m_probe::get_derivatives", "coupled model (SURVEY row N2)"); }
+// probe.F90:381-471: dF_T/dM from the device; the three salinity derivatives are zero while Coupled Salinity = 0 (:446)
+EXPORT void __m_probe_MOD_get_derivatives(double* un, double* dftdm, double* dfsdq, double* dfsdm, double* dfsdg) {
+  need_model("m_probe::get_derivatives");
+  const size_t nm = (size_t)M.cfg.n * M.cfg.m, nvec = M.F.size();
+  void* d_x = nullptr;
+  if (iemic_b200_malloc(&d_x, (int64_t)(nvec * sizeof(double))) != 0 || iemic_b200_memcpy_h2d(d_x, un, (int64_t)(nvec * sizeof(double))) != 0) die("m_probe::get_derivatives");
+  const int rc = thcm_b200_get_dftdm(M.h, (const double*)d_x, dftdm);
+  iemic_b200_free(d_x);
+  if (rc != 0) die("m_probe::get_derivatives");
+  for (size_t q = 0; q < nm; q++) { dfsdq[q] = 0.0; dfsdm[q] = 0.0; dfsdg[q] = 0.0; }
+}
 EXPORT void __m_probe_MOD_get_salflux(double*, double*, double*, double*, double*) { refuse("m_probe::get_salflux", "coupled model (SURVEY row N2)"); }
 EXPORT void __m_probe_MOD_get_temflux(double*, double*, double*, double*, double*, double*, double*) { refuse("m_probe::get_temflux", "coupled model (SURVEY row N2)"); }
 EXPORT void __m_probe_MOD_compute_evap(double*, double*) { refuse("m_probe::compute_evap", "coupled model (SURVEY row N2)"); }

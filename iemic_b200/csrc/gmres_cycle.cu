@@ -10,8 +10,9 @@
 //   w -= V h2 ; v_{i+1} = w / sqrt(<w,w> - |h2|^2) ; block 0: Hessenberg column, Givens, residual estimate, stop flag
 //
 // = 3 barriers per iteration (4 with the block-Jacobi preconditioner), no launch, no host.  The arithmetic is the fused CGS2 of
-// gmres.cu (same projections, Pythagoras norm, givens_step), the matrix apply is the plain CSR loop in storage order (= matAvec).
-// Reductions are deterministic: per-block partial sums in global memory, added in block order by every block.
+// gmres.cu (same projections, Pythagoras norm, givens_step); the matrix apply sums a row in eight interleaved partial sums (a
+// different association than matAvec; the explicit residual that accepts a cycle is computed by the driver's bit-exact product).
+// Reductions are deterministic: per-block partial sums in global memory, added by every block in the same fixed tree.
 // Rows written by other blocks (the SpMV input) are read with ld.global.cg: L1 is not coherent between SMs within a launch.
 // Single GPU only (no halo exchange between the iterations).
 #include <cooperative_groups.h>
@@ -32,14 +33,26 @@ __device__ __forceinline__ double warp_total(double v) {
 }
 // part[k] = sum over this block's rows [r0, r1) of V_k[r] * w[r], k = 0..nk-1 (vector k == kw is w itself): one warp per k, the
 // lanes stride over the rows, no block barrier
-__device__ __forceinline__ void block_dots(const double* V, long long ld, const double* w, int nk, int kw, long long r0, long long r1, double* part) {
+// (partials are stored vector-major, part[k * ldp + block], so that the sum over the blocks reads consecutive words)
+__device__ __forceinline__ void block_dots(const double* V, long long ld, const double* w, int nk, int kw, long long r0, long long r1, double* part, int ldp) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   for (int k = warp; k < nk; k += CT / 32) {
     const double* vk = (k == kw) ? w : V + (size_t)k * ld;
     double acc = 0.0;
     for (long long r = r0 + lane; r < r1; r += 32) acc = fma(vk[r], w[r], acc);
     acc = warp_total(acc);
-    if (lane == 0) part[k] = acc;
+    if (lane == 0) part[(size_t)k * ldp + blockIdx.x] = acc;
+  }
+}
+// hs[k] = sum over the blocks of part[k][.], k < nk: a warp per k, lanes stride over the blocks, fixed tree -- the same number
+// in every block
+__device__ __forceinline__ void sum_partials(const double* part, int ldp, int nblk, int nk, double* hs) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int k = warp; k < nk; k += CT / 32) {
+    double s = 0.0;
+    for (int b = lane; b < nblk; b += 32) s += __ldcg(part + (size_t)k * ldp + b);
+    s = warp_total(s);
+    if (lane == 0) hs[k] = s;
   }
 }
 
@@ -53,7 +66,7 @@ __global__ void __launch_bounds__(CT) gmres_cycle_kernel(const CycleArgs a) {
   const long long chunk = ((a.n + nblk - 1) / nblk + 15) / 16 * 16;
   const long long r0 = (long long)blockIdx.x * chunk, r1 = r0 + chunk < a.n ? r0 + chunk : a.n;
   double* part1 = a.part;
-  double* part2 = a.part + (size_t)nblk * a.ldp;
+  double* part2 = a.part + (size_t)(a.m + 2) * a.ldp;
   for (int i = 0; i < a.maxcols; i++) {
     const double* vi = a.V + (size_t)i * a.ld;
     double* w = a.V + (size_t)(i + 1) * a.ld;
@@ -73,13 +86,20 @@ __global__ void __launch_bounds__(CT) gmres_cycle_kernel(const CycleArgs a) {
       xin = zi;
       grid.sync();
     }
-    // w = A xin: one thread per row, left to right in storage order
-    for (long long r = r0 + threadIdx.x; r < r1; r += CT) {
-      if (r == a.long_row) continue;
-      const int p0 = a.rowptr[r], p1 = a.rowptr[r + 1];
-      double s = 0.0;
-      for (int p = p0; p < p1; p++) s = __dadd_rn(s, __dmul_rn(a.val[p], __ldcg(xin + a.col[p])));
-      w[r] = s;
+    // w = A xin: 8 lanes per row, lane q takes the entries q, q+8, ... of the row (coalesced), the eight sums are added in lane order
+    {
+      const int slot = threadIdx.x >> 3, seg = threadIdx.x & 7;
+      for (long long rb = r0; rb < r1; rb += CT / 8) {
+        const long long r = rb + slot;
+        double s = 0.0;
+        if (r < r1 && r != a.long_row) {
+          const int p0 = a.rowptr[r], p1 = a.rowptr[r + 1];
+          for (int p = p0 + seg; p < p1; p += 8) s = __dadd_rn(s, __dmul_rn(__ldg(a.val + p), __ldcg(xin + __ldg(a.col + p))));
+        }
+        double tot = s;
+        for (int d = 1; d < 8; d++) { const double o = __shfl_sync(FULL, s, d, 8); tot = __dadd_rn(tot, o); }
+        if (seg == 0 && r < r1 && r != a.long_row) w[r] = tot;
+      }
     }
     if (a.long_row >= r0 && a.long_row < r1) { // dense row: the whole block, fixed order (spmv_longrow_kernel of spmv_tile.cu)
       const int p0 = a.rowptr[a.long_row], p1 = a.rowptr[a.long_row + 1];
@@ -96,13 +116,9 @@ __global__ void __launch_bounds__(CT) gmres_cycle_kernel(const CycleArgs a) {
     }
     __syncthreads(); // the block's rows of w are complete (each block only reads its own rows of w below)
     // first projection: block partials of <V_k, w>
-    block_dots(a.V, a.ld, w, i + 1, -1, r0, r1, part1 + (size_t)blockIdx.x * a.ldp);
+    block_dots(a.V, a.ld, w, i + 1, -1, r0, r1, part1, a.ldp);
     grid.sync();
-    for (int k = threadIdx.x; k <= i; k += CT) {
-      double s = 0.0;
-      for (int b = 0; b < nblk; b++) s += __ldcg(part1 + (size_t)b * a.ldp + k);
-      hs[k] = s;
-    }
+    sum_partials(part1, a.ldp, nblk, i + 1, hs);
     __syncthreads();
     if (blockIdx.x == 0) for (int k = threadIdx.x; k <= i; k += CT) a.h1[k] = hs[k];
     // w -= V h1 on this block's rows, then the second projection and <w,w> from the updated rows
@@ -112,13 +128,9 @@ __global__ void __launch_bounds__(CT) gmres_cycle_kernel(const CycleArgs a) {
       w[r] = x;
     }
     __syncthreads();
-    block_dots(a.V, a.ld, w, i + 2, i + 1, r0, r1, part2 + (size_t)blockIdx.x * a.ldp);
+    block_dots(a.V, a.ld, w, i + 2, i + 1, r0, r1, part2, a.ldp);
     grid.sync();
-    for (int k = threadIdx.x; k <= i + 1; k += CT) {
-      double s = 0.0;
-      for (int b = 0; b < nblk; b++) s += __ldcg(part2 + (size_t)b * a.ldp + k);
-      hs[k] = s;
-    }
+    sum_partials(part2, a.ldp, nblk, i + 2, hs);
     __syncthreads();
     // ||w - V h2||^2 = <w,w> - |h2|^2 for orthonormal V (givens_step computes the same number for the Hessenberg matrix)
     double hh = 0.0;
@@ -160,7 +172,7 @@ int gmres_cycle_partials(int m) { // doubles of workspace
   int dev = 0, sms = 148;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  return 2 * sms * 2 * (m + 2);
+  return 2 * ((2 * sms + 31) / 32 * 32) * (m + 2);
 }
 // returns 0 or a cudaError_t; a.part must hold gmres_cycle_partials(a.m) doubles
 int launch_gmres_cycle(CycleArgs a, cudaStream_t st) {
@@ -177,7 +189,7 @@ int launch_gmres_cycle(CycleArgs a, cudaStream_t st) {
   const long long cap = (long long)sms * (per_sm < 2 ? per_sm : 2);
   if (want > cap) want = cap;
   if (want < 1) want = 1;
-  a.ldp = a.m + 2;
+  a.ldp = (int)((want + 31) / 32 * 32); // partials: (m + 2) rows of ldp blocks, twice
   void* args[] = {(void*)&a};
   return (int)cudaLaunchCooperativeKernel((const void*)gmres_cycle_kernel, dim3((unsigned)want), dim3(CT), args, smem, st);
 }

@@ -4,6 +4,7 @@
 #include <stdint.h>
 #include "thcm_rows.cuh"
 #include "thcm_cell.cuh"
+#include "thcm_coupled.cuh"
 #include "peer.cuh"
 
 namespace thcm {
@@ -30,6 +31,18 @@ void launch_forcing_surface(const Scalars& S, const uint64_t* sig, const double*
 void launch_jac(const AsmArgs& a, cudaStream_t st);
 void launch_rhs(const AsmArgs& a, cudaStream_t st);
 void launch_asm(const AsmArgs& a, cudaStream_t st); // Jacobian and residual of the same state in one pass over the staged tiles
+// ---- row N2: coupling to an atmosphere / sea-ice model (coupled.cu) ----
+void launch_forcing_cells(const Scalars& S, const uint64_t* sig, const double* ftcell /* nloc*mloc */, double* frc, cudaStream_t st);
+struct DftdmArgs {
+  Scalars S; const uint64_t* sig; const double* x;
+  const double *tatm, *albe, *qatm;  // whole surface, (j-1)*n + (i-1), or null (zero field)
+  const double* suno;                // (m + 2), Fortran j
+  DftdmScal c;
+  double* out;                       // nloc*mloc
+};
+void launch_dftdm(const DftdmArgs& a, cudaStream_t st);
+void launch_coupling_apply(int nrows, const int* rows, const int* beg, const int* jco, const double* co, const double* x, double* y, int accumulate,
+                           cudaStream_t st);
 int jac_smem_bytes();
 int rhs_smem_bytes();
 int asm_smem_bytes();

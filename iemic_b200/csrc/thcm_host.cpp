@@ -12,7 +12,9 @@ namespace {
 const double pi = 3.14159265358979323846; // par.F90:14
 // usr.F90:129-160
 const double omegadim = 7.292e-05, r0dim = 6.37e+06, udim = 0.1e+00, gdim = 9.8e+00, rhodim = 1.024e+03;
-const double s0 = 35.0, cp0 = 4.2e+03, deltas = 1.0;
+const double s0 = 35.0, cp0 = 4.2e+03, deltas = 1.0, t0 = 15, deltat = 1.0;
+// atm.F90:5-19
+const double rhoa = 1.25, ce = 1.3e-03, ch = 0.94 * ce, cpa = 1000., uw = 8.5, c0 = 0.43, sun0 = 1360., lv = 2.5e+06;
 const double alpt1 = 2.93, alpt2 = 8.3e-02, alpt3 = 6.6e-04;
 const double ah = 2.5e+05, av = 1.0e-03, kappah = 1.0e+03, kappav = 1.0e-04;
 const double zmin = -1.0, zmax = 0.0;
@@ -43,6 +45,7 @@ Host::Host(const Config& c, const int* landm_in, int rank_, int nranks_) : cfg(c
   version = 1; mask_version = 0; intCorrection = 0.0;
   make_grid();
   stpnt();
+  atmos_coef();
   check_supported();
   set_landmask(landm_in); // signatures, graph, tables, forcing
 }
@@ -175,6 +178,105 @@ void Host::make_grid() {
     dfzT[k] = dfdz(ze, cfg.qz); dfzW[k] = dfdz(zwe, cfg.qz);
   }
   zw[0] = zmin; dfzW[0] = dfdz(zmin, cfg.qz);
+}
+
+// usrc.F90:1175-1213 (atmos_coef) with QTnd, QSnd of init (usrc.F90:117-120)
+void Host::atmos_coef() {
+  const double dzne = dz * dfzT[l];
+  cpl.QTnd = r0dim / (udim * cp0 * rhodim * cfg.hdim * dzne);
+  cpl.QSnd = s0 * r0dim / (deltas * udim * cfg.hdim * dzne);
+  const double muoa = rhoa * ch * cpa * uw;
+  cpl.Os = sun0 * c0 / 4 * cpl.QTnd;
+  cpl.Ooa = muoa * cpl.QTnd;
+  cpl.nus = 0.0; cpl.lvsc = 0.0;
+  cpl.suno.assign(m + 2, 0.0);
+  for (int j = 1; j <= m; j++) {
+    const double sj = std::sin(y[j]);
+    cpl.suno[j] = cpl.Os * (1 - .482 * (3 * (sj * sj) - 1.) / 2.);
+  }
+}
+
+// inserts.F90:12-166
+void Host::insert_field(int which, const double* field) {
+  const bool cT = cfg.coupled_T == 1, cS = cfg.coupled_S == 1;
+  std::vector<double>* dst = nullptr;
+  switch (which) {
+    case F_TATM: if (cT) dst = &cpl.tatm; break;
+    case F_QATM: if (cT || cS) dst = &cpl.qatm; break;
+    case F_ALBE: if (cT) dst = &cpl.albe; break;
+    case F_MSI: dst = &cpl.msi; break;
+    case F_PATM: case F_GSI: if (cS) throw std::runtime_error("thcm_b200: Coupled Salinity=1 is not on the B200 path yet"); return; // ignored by the Fortran too
+    case F_QSA: return; // enters the salinity forcing only (forcing.F90:181-184), which needs Coupled Salinity=1
+    default: throw std::runtime_error("thcm_b200: unknown coupling field");
+  }
+  if (!dst) return; // the Fortran ignores the insert as well when the flag is off
+  dst->assign(field, field + (size_t)n * m);
+}
+void Host::coupled_changed() {
+  build_tables();
+  if (forcing_on_device) { forcing_profiles(); frc_host_valid = false; }
+  else build_forcing(true);
+  version++;
+}
+void Host::set_atmos_parameters(const double* p) {
+  cpl.qdim = p[1]; cpl.nuq = p[2]; cpl.eta = p[3]; cpl.dqso = p[4]; cpl.eo0 = p[7]; cpl.albe0 = p[12]; cpl.albed = p[13];
+  cpl.nus = par[P_COMB] * par[P_SALT] * cpl.eta * cpl.qdim * cpl.QSnd;
+  cpl.lvsc = par[P_COMB] * par[P_TEMP] * rhodim * lv * cpl.QTnd;
+  coupled_changed();
+}
+void Host::set_seaice_parameters(const double* p) {
+  cpl.zeta = p[0]; cpl.a0 = p[1]; cpl.Lf = p[2]; cpl.Qvar = p[5]; cpl.Q0 = p[6];
+  coupled_changed();
+}
+void Host::getdeps(double* o) const {
+  o[0] = cpl.Ooa; o[1] = cpl.Os; o[2] = cpl.nus; o[3] = cpl.eta; o[4] = cpl.lvsc; o[5] = cpl.qdim;
+  o[6] = par[P_COMB] * par[P_SALT] * cpl.QSnd;
+}
+
+DftdmScal Host::dftdm_scalars() const {
+  DftdmScal a;
+  a.cs = par[P_COMB] * par[P_SUNP];
+  a.albe0 = cpl.albe0; a.albed = cpl.albed; a.Ooa = cpl.Ooa;
+  a.leq = cpl.lvsc * cpl.eta * cpl.qdim;
+  a.dq = deltat / cpl.qdim * cpl.dqso;
+  a.lveo = cpl.lvsc * cpl.eo0;
+  a.qtz = cpl.QTnd * cpl.zeta;
+  a.a0 = cpl.a0; a.s0 = s0; a.t0 = t0;
+  return a;
+}
+int Host::atmos_block(int* rows, int* beg, int* jco, double* co) const {
+  const int N = n, M = m, L = l;
+  const double comb = par[P_COMB], sunp = par[P_SUNP];
+  int nr = 0, el = 0;
+  beg[0] = 0;
+  if (cfg.coupled_T != 1) return 0;
+  for (int j = 0; j != M; ++j) for (int i = 0; i != N; ++i) {
+    if (lm(i + 1, j + 1, L) != 0) continue; // (*landmask_.global_surface)[sr] == 0
+    const size_t sr = (size_t)j * N + i;
+    const double Msi = cpl.msi.size() == (size_t)N * M ? cpl.msi[sr] : 0.0, Ssw = cpl.suno[j + 1];
+    const double dTFT = cpl.Ooa * (1.0 - Msi);
+    const double dAFT = -comb * sunp * Ssw * cpl.albed * (1.0 - Msi);
+    const double dQFT = cpl.lvsc * cpl.eta * cpl.qdim * (1.0 - Msi);
+    rows[nr] = 6 * ((L - 1) * N * M + N * j + i) + TT - 1;
+    co[el] = -dTFT; jco[el++] = 3 * (N * j + i) + 0; // ATMOS_TT_ (Atmosphere::interface_row, dof 3)
+    co[el] = -dAFT; jco[el++] = 3 * (N * j + i) + 2; // ATMOS_AA_
+    co[el] = -dQFT; jco[el++] = 3 * (N * j + i) + 1; // ATMOS_QQ_
+    beg[++nr] = el;
+  }
+  return nr;
+}
+int Host::seaice_block(const double* dftdm, int* rows, int* beg, int* jco, double* co) const {
+  const int N = n, M = m, L = l;
+  int nr = 0, el = 0;
+  beg[0] = 0;
+  if (cfg.coupled_T != 1) return 0;
+  for (int j = 0; j != M; ++j) for (int i = 0; i != N; ++i) {
+    if (lm(i + 1, j + 1, L) != 0) continue;
+    rows[nr] = 6 * ((L - 1) * N * M + N * j + i) + TT - 1;
+    co[el] = -dftdm[(size_t)j * N + i]; jco[el++] = 4 * (N * j + i) + 3 - 1; // SEAICE_MM_ = 3, dof 4 (SeaIce::find_row0)
+    beg[++nr] = el;
+  }
+  return nr;
 }
 
 // usrc.F90:1136-1172 and mix_imp.f:92-107
@@ -328,6 +430,7 @@ Tables Host::tables(const double* base) const {
   for (int q = 0; q < NJTAB; q++) { if (jt[q]) *jt[q] = p; p += nj; }
   const double** kt[NKTAB] = {&T.uu_b, &T.uu_t, &T.uu_cv, &T.tt_b, &T.tt_t, &T.tt_cv, &T.wp, &T.pw, &T.tdzi8, &T.dfzT, &T.dzdfzT, &T.dzdfzW, &T.r_dfzT, &T.r_dzdfzT, &T.r_dzdfzW};
   for (int q = 0; q < NKTAB; q++) { *kt[q] = p; p += nk; }
+  T.msi = nullptr; // set by whoever owns a copy of the sea-ice mask in the same memory space as `base`
   return T;
 }
 
@@ -432,11 +535,19 @@ void Host::build_tables() {
   S.w_ss = lambda * Ra * 1.0 / 2.;                // Al(:,WW,SS) = lambda*Ra*tbc/2.
   S.ra_a2 = Ra * xes * alpt2; S.ra_a3 = Ra * xes * alpt3;
   S.tt_surf = cfg.tres * bi * 1.0; S.ss_surf = cfg.sres * bi * 1.0;
-  if (cfg.coupled_T == 1) { // Ooa*tc with msi=0, lvsc=0 (usrc.F90:711-722, atmos_coef :1175-1213)
-    const double rhoa = 1.25, ce = 1.3e-03, ch = 0.94 * ce, cpa = 1000., uw = 8.5;
-    double muoa = rhoa * ch * cpa * uw, dzne = dz * dfzT[l];
-    double QTnd = r0dim / (udim * cp0 * rhodim * cfg.hdim * dzne);
-    S.tt_surf = (muoa * QTnd) * 1.0;
+  if (cfg.coupled_T == 1) { // usrc.F90:725-741 with tc = sc = 1: Ooa*tc, then + dedt*sc + mc*(QTnd*zeta*tc - Ooa*tc - dedt*sc)
+    const double dedt = cpl.lvsc * cpl.eta * cpl.qdim * (deltat / cpl.qdim) * cpl.dqso;
+    S.coupled_T = 1;
+    S.tt_surf = cpl.Ooa * 1.0;
+    S.tt_dedt = dedt * 1.0;
+    S.tt_mc = cpl.QTnd * cpl.zeta * 1.0 - cpl.Ooa * 1.0 - dedt * 1.0;
+    S.ts_mc = -cpl.QTnd * cpl.zeta * cpl.a0;
+    if (cpl.msi_lin != cpl.msi) { // masksi(mc, msi) of this `lin` call (usrc.F90:723)
+      cpl.msi_lin = cpl.msi;
+      cpl.have_msi = false;
+      for (double v : cpl.msi_lin) if (v != 0.0) { cpl.have_msi = true; break; }
+      cpl.msi_version++;
+    }
   }
   S.dyi = 1. / (2 * dy); S.dzi = dzi; S.tdzi2 = 1.0 / (2 * dz);
   S.kvc = par[P_P_VC]; S.lambda = lambda; S.xes = xes;
@@ -495,8 +606,16 @@ void Host::forcing_profiles() {
     if (TRES == 0) temcor = qint(&tj, false);
     for (int j = 1; j <= m; j++) ft[j] = etabi * (tj[j] - temcor);
   }
-  // coupled_T == 1 with no atmosphere attached: tatm = qatm = albe = msi = 0, lvsc = 0 => Frc(TT) = par(COMB)*par(SUNP)*suno(j)*(1-albe0)
-  // with the unset albe0 = 0; only meaningful once set_atmos_parameters exists, kept at 0 here.
+  if (cfg.coupled_T == 1) { // forcing.F90:73-96: per cell, from the inserted fields (zero until an atmosphere / sea ice is attached)
+    ftcell.assign((size_t)nloc * mloc, 0.0);
+    auto fld = [&](const std::vector<double>& f, int i, int j) { return f.empty() ? 0.0 : f[(size_t)(j - 1) * n + (i - 1)]; };
+    for (int j = jo0; j < jo0 + mloc; j++) for (int i = io0; i < io0 + nloc; i++) {
+      const double QToa = par[P_COMB] * par[P_SUNP] * cpl.suno[j] * (1 - cpl.albe0 - cpl.albed * fld(cpl.albe, i, j)) +
+                          cpl.Ooa * fld(cpl.tatm, i, j) + cpl.lvsc * cpl.eta * cpl.qdim * fld(cpl.qatm, i, j) - cpl.lvsc * cpl.eo0;
+      const double QTos = cpl.QTnd * cpl.zeta * (cpl.a0 * s0 - t0);
+      ftcell[(size_t)(j - jo0) * nloc + (i - io0)] = (QToa + fld(cpl.msi, i, j) * (QTos - QToa)) * (1 - lm(i, j, l));
+    }
+  }
   const double gamma = par[P_COMB] * par[P_SALT] * (1 - SRES + SRES * par[P_BIOT]);
   double salcor = 0.0, adapted_salcor = 0.0, spertcor = 0.0;
   if (SRES == 0) { salcor = qint(&sj, true); adapted_salcor = qint(nullptr, false); spertcor = qint(nullptr, false); }
@@ -524,7 +643,8 @@ void Host::build_forcing(bool surface_only) {
   const double *fu = fprof.data(), *fv = fu + (m + 2), *ft = fv + (m + 2), *fs = ft + (m + 2);
   for (int j = j1; j <= j2; j++) for (int i = i1; i <= i2; i++) {
     frc[row(i, j, l, UU)] = fu[j]; frc[row(i, j, l, VV)] = fv[j];
-    frc[row(i, j, l, TT)] = ft[j]; frc[row(i, j, l, SS)] = fs[j];
+    frc[row(i, j, l, TT)] = cfg.coupled_T == 1 ? ftcell[(size_t)(j - jo0) * nloc + (i - io0)] : ft[j];
+    frc[row(i, j, l, SS)] = fs[j];
   }
   if (!surface_only)
   for (int k = 1; k <= l - 1; k++) for (int j = j1; j <= j2; j++) for (int i = i1; i <= i2; i++) // internal T/S forcing is zero (THCM.C:540-544)

@@ -10,6 +10,7 @@
 #include <string>
 #include <vector>
 #include "thcm_rows.cuh"
+#include "thcm_coupled.cuh"
 
 namespace thcm {
 
@@ -77,11 +78,36 @@ class Host {
 
   std::vector<unsigned> diag_info() const; // per row: where its own cell's 6x6 block entries sit (scaling.cu)
 
+  // ---- coupling to an atmosphere / sea-ice model (Coupled Temperature = 1 only) ----
+  // module variables of atm.F90 / ice.F90 with the reference's defaults (usrc.F90:62-65, ice.F90:6-10, atmos_coef usrc.F90:1175-1213)
+  struct Coupling {
+    double qdim = 0.01, nuq = 0.0, eta = 0.0, dqso = 0.0, eo0 = 0.0, albe0 = 0.0, albed = 0.0, nus = 0.0, lvsc = 0.0;
+    double zeta = 0.0, a0 = -0.0575, Lf = 3.347e+05, Qvar = 0.0, Q0 = 0.0;
+    double Ooa = 0.0, Os = 0.0, QTnd = 0.0, QSnd = 0.0;
+    std::vector<double> suno;                    // (m + 2), Fortran j
+    std::vector<double> tatm, qatm, albe, msi;   // whole surface, (j-1)*n + (i-1); empty = the zero field
+    std::vector<double> msi_lin;                 // the mask the coefficients were last built with (`lin` reads msi when it runs, not at the insert)
+    bool have_msi = false;                       // msi_lin has a non-zero entry
+    uint64_t msi_version = 0;                    // bumped when msi_lin changes (device copy)
+  } cpl;
+  enum Field { F_TATM = 0, F_QATM, F_ALBE, F_PATM, F_QSA, F_MSI, F_GSI };
+  void insert_field(int which, const double* field);       // inserts.F90:12-166 (takes effect at the next set_* call, as there)
+  void set_atmos_parameters(const double* pars18);         // usrc.F90:237-293
+  void set_seaice_parameters(const double* pars7);         // usrc.F90:296-333
+  void getdeps(double* out7) const;                        // usrc.F90:201-219: Ooa, Os, nus, eta, lvsc, qdim, pQSnd
+  DftdmScal dftdm_scalars() const;                         // probe.F90:433-440
+  // Ocean::getBlock(Atmosphere) / getBlock(SeaIce) (Ocean.C:1538-1746), T rows, compact (see include/iemic_b200.h); return the row count
+  int atmos_block(int* rows, int* beg, int* jco, double* co) const;
+  int seaice_block(const double* dftdm /* n*m */, int* rows, int* beg, int* jco, double* co) const;
+  // probe.F90:381-444, coupled_T part: the fields the formula needs per surface point; the arithmetic runs in a kernel (coupled.cu)
+  std::vector<double> ftcell;   // coupled_T = 1: surface T forcing of the owned cells, (j-jo0)*nloc + (i-io0), before the Frc zeroing
+
   std::vector<double> fprof;    // surface forcing of an ocean cell per latitude: fu | fv | ft | fs, (m + 2) doubles each (forcing_profiles)
   bool forcing_on_device = false, frc_host_valid = true; // set_par leaves `frc` stale when a kernel fills the device copy
   void refresh_host_forcing() { if (!frc_host_valid) build_forcing(true); }
   size_t frc_dirty_from = 0; // first row of `frc` a device copy made before the last change does not have yet
   Tables tables(const double* base) const; // pointers into a (host or device) copy of `tab`
+  Tables host_tables() const { Tables T = tables(tab.data()); T.msi = (cfg.coupled_T == 1 && cpl.have_msi) ? cpl.msi_lin.data() : nullptr; return T; }
   inline int lm(int i, int j, int k) const { return landm[(size_t)i + (size_t)(n + 2) * (j + (size_t)(m + 2) * k)]; }
 
  private:
@@ -93,6 +119,8 @@ class Host {
   // surface_only: a parameter change touches the top level only (wind stress, surface T/S forcing); the body rows stay zero
   void build_forcing(bool surface_only = false);
   void forcing_profiles();
+  void atmos_coef();
+  void coupled_changed();
   void build_graph();
   void check_supported() const;
 };

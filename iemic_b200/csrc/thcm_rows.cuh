@@ -51,6 +51,10 @@ struct Scalars {
   double w_tt, w_ss;           // Al(5|23,WW,TT) , Al(5|23,WW,SS)            (usrc.F90:676-678)
   double ra_a2, ra_a3;         // Ra*xes*alpt2, Ra*xes*alpt3                   (usrc.F90:841-842)
   double tt_surf, ss_surf;     // TRES*bi, SRES*bi                              (usrc.F90:727,766)
+  // coupled to an atmosphere / sea ice (coupled_T = 1, usrc.F90:725-741): tt_surf = Ooa*tc and, added one after the other,
+  // dedt*sc and mc*(QTnd*zeta*tc - Ooa*tc - dedt*sc) with the sea-ice mask mc = msi(i,j); Al(5,TT,SS) = -QTnd*zeta*a0*mc
+  int coupled_T;
+  double tt_dedt, tt_mc, ts_mc;
   double dyi;                  // 1./(2*dy)                                     (spf.F90:337)
   double dzi;                  // 1./dz
   double tdzi2;                // 1.0/(2*dz)                                    (spf.F90:446)
@@ -83,6 +87,8 @@ struct Tables {
   const double *dzdfzT;                  // dz*dfzT(k)
   const double *dzdfzW;                  // dz*dfzW(k), k=0..l
   const double *r_dfzT, *r_dzdfzT, *r_dzdfzW; // correctly rounded reciprocals of the three divisors above (see thcm_div)
+  // sea-ice mask msi(i,j) of the whole surface, index (j-1)*n + (i-1) with global Fortran i, j; null while no sea ice is attached
+  const double* msi;
 };
 static const int NJTAB = 29, NKTAB = 15; // number of per-j / per-k tables above
 
@@ -411,6 +417,18 @@ template <class F> struct JacRow<PP, F> {
 };
 
 // T and S rows share one implementation (X = own tracer, Y = the other one)
+// Surface T row of an ocean coupled to an atmosphere / sea-ice model (lin, usrc.F90:725-741), the terms that follow Ooa*tc in the
+// reference's expression, added in its order: + dedt*sc + mc*(QTnd*zeta*tc - Ooa*tc - dedt*sc); cross = Al(5,TT,SS).
+// tc = sc = 1 on the surface level (tderiv 1, 2: spf.F90:206-209), mc = msi(i,j) there (masksi, spf.F90:347-359).
+THCM_HD void thcm_coupled_surface(const Scalars& S, const Tables& T, const Cell& c, double& cen, double& cross) {
+  cen = cen + S.tt_dedt;
+  if (T.msi) {
+    const double mc = T.msi[(size_t)(c.j - 1) * S.n + (c.i - 1)];
+    cen = cen + mc * S.tt_mc;
+    cross = S.ts_mc * mc;
+  }
+}
+
 template <int X, class F> struct TracerJac {
   static THCM_HD double c_(const F& f, int di, int dj, int dk) { return X == TT ? f.t(di, dj, dk) : f.s(di, dj, dk); }
   static THCM_HD void build(Row<X>& r, const Scalars& S, const Tables& T, const Cell& c, const F& f, const MixFD* fd = nullptr) {
@@ -437,8 +455,10 @@ template <int X, class F> struct TracerJac {
     r.template at<6, X>() = T.tt_n[j] + y6;
     r.template at<14, X>() = T.tt_b[k] + z14;
     r.template at<23, X>() = T.tt_t[k] + z23;
-    r.template at<5, X>() = (((T.tt_ch[j] - T.tt_cv[k]) + surf) + (x2 + x8)) + (y4 + y6) + (z14 + z23);
-    r.template at<14, Y>() = 0.0; r.template at<5, Y>() = 0.0; r.template at<23, Y>() = 0.0;
+    double cen = (T.tt_ch[j] - T.tt_cv[k]) + surf, cross = 0.0;
+    if (X == TT && S.coupled_T && k == S.l) thcm_coupled_surface(S, T, c, cen, cross);
+    r.template at<5, X>() = ((cen + (x2 + x8)) + (y4 + y6)) + (z14 + z23);
+    r.template at<14, Y>() = 0.0; r.template at<5, Y>() = cross; r.template at<23, Y>() = 0.0;
     // vmix_jac: forward differences, eps = 1e-8 (mix_imp.f:745-769), only OCEAN rows carry a pattern (:891)
     if (S.vmix_on && !sbit(c.sig, SIG_NOTOCEAN)) {
       const double eps = 1.0e-08, reps = 1.0 / 1.0e-08;
@@ -549,7 +569,13 @@ template <int X, class F> struct TracerRhs {
     r.template at<6, X>() = T.tt_n[j] + y6;
     r.template at<14, X>() = T.tt_b[k] + z14;
     r.template at<23, X>() = T.tt_t[k] + z23;
-    r.template at<5, X>() = (((T.tt_ch[j] - T.tt_cv[k]) + surf) + (x2 + x8)) + (y4 + y6) + (z14 + z23);
+    double cen = (T.tt_ch[j] - T.tt_cv[k]) + surf;
+    if (X == TT && S.coupled_T && k == S.l) {
+      double cross = 0.0;
+      thcm_coupled_surface(S, T, c, cen, cross);
+      r.template at<5, SS>() = cross;
+    }
+    r.template at<5, X>() = ((cen + (x2 + x8)) + (y4 + y6)) + (z14 + z23);
   }
 };
 template <class F> struct RhsRow<TT, F> : TracerRhs<TT, F> {};

@@ -99,6 +99,43 @@ int thcm_b200_halo_exchange(thcm_b200_t* h, double* d_x);
 /* THCM::evaluateB (src/ocean/THCM.C:1195-1235): diag(B) alone into d_diagB (nrows_local doubles; NULL: the handle's own array
  * that thcm_b200_csr returns) -- fillcolB (assemble.F90:18-54) with the fixed-pressure and integral rows zeroed. */
 int thcm_b200_evaluate_b(thcm_b200_t* h, double* d_diagB);
+
+/* ---- Coupling to an atmosphere / sea-ice model ("Coupled Temperature" = 1, "Coupled Salinity" = 1 is refused) ----
+ * The ocean side of Ocean::synchronize (src/ocean/Ocean.C:1443-1493): the neighbouring model's interface fields go in with
+ * thcm_b200_insert_field (THCM::setAtmosphereT/Q/A, setSeaIceM, src/ocean/THCM.C:1375-1462 -> m_inserts, src/ocean/inserts.F90:12-166:
+ * whole n x m surface, i fastest, every rank passes the whole field), and take effect at the following set_*_parameters /
+ * set_par call, which reruns forcing and lin exactly like the Fortran (src/ocean/usrc.F90:237-333, 163-181):
+ *   surface T forcing per cell   (src/ocean/forcing.F90:73-96)        -> forcing_cells_kernel
+ *   surface T row coefficients   (src/ocean/usrc.F90:725-741)         -> the assembly kernels (mask-dependent centre entry, (T,S) entry)
+ * The structs are the bind(C) types of usrc.F90:250-269 / :303-311 = Atmosphere::CommPars / SeaIce::CommPars. */
+typedef struct { double tdim, qdim, nuq, eta, dqso, dqsi, dqdt, Eo0, Ei0, Cs, t0o, t0i, a0, da, tauf, tauc, comb, albf; } thcm_b200_atmos_pars;
+typedef struct { double zeta, a0, Lf, s0, rhoo, qvar, q0; } thcm_b200_seaice_pars;
+enum { THCM_B200_FIELD_ATMOS_T = 0, THCM_B200_FIELD_ATMOS_Q = 1, THCM_B200_FIELD_ATMOS_A = 2, THCM_B200_FIELD_ATMOS_P = 3,
+       THCM_B200_FIELD_SEAICE_Q = 4, THCM_B200_FIELD_SEAICE_M = 5, THCM_B200_FIELD_SEAICE_G = 6 };
+int thcm_b200_insert_field(thcm_b200_t* h, int which, const double* field /* n*m */);
+int thcm_b200_set_atmos_parameters(thcm_b200_t* h, const thcm_b200_atmos_pars* pars);   /* set_atmos_parameters_, usrc.F90:237-293 */
+int thcm_b200_set_seaice_parameters(thcm_b200_t* h, const thcm_b200_seaice_pars* pars); /* set_seaice_parameters_, usrc.F90:296-333 */
+int thcm_b200_getdeps(thcm_b200_t* h, double* out7);  /* getdeps_, usrc.F90:201-219: Ooa, Os, nus, eta, lvsc, qdim, pQSnd */
+int thcm_b200_get_suno(thcm_b200_t* h, double* suno /* n*m */);                         /* THCM::getSunO */
+/* m_probe::get_derivatives, coupled_T part (src/ocean/probe.F90:381-444, THCM::getDerivatives THCM.C:1596-1626): dF_T/dM_seaice
+ * on the owned surface points, (j-j0)*nloc + (i-i0) (one GPU: the whole surface); d_x is a device state vector. */
+int thcm_b200_get_dftdm(thcm_b200_t* h, const double* d_x, double* dftdm /* nloc*mloc, host */);
+/* Ocean::getBlock(Atmosphere) / getBlock(SeaIce) (src/ocean/Ocean.C:1538-1746), the T rows, in compact form: rows[r] is the global
+ * ocean row of the r-th non-empty row, its entries are jco/co[beg[r] .. beg[r+1]) in the reference's push order, columns are
+ * Atmosphere::interface_row / SeaIce::interface_row (dof 3 / 4).  Capacity: n*m rows, 3*n*m entries.  Utils::CRSMat over all
+ * ocean rows follows by scattering beg. */
+int thcm_b200_atmos_block(thcm_b200_t* h, int* rows, int* beg, int* jco, double* co, int* nrows_out);
+int thcm_b200_seaice_block(thcm_b200_t* h, const double* d_x, int* rows, int* beg, int* jco, double* co, int* nrows_out);
+/* CouplingBlock<Ocean, Model> (src/coupledmodel/CouplingBlock.H): the block on the device; entries of a row are kept sorted by column
+ * as Epetra's FillComplete leaves them.  apply: d_out = C d_in over the rank's ocean rows (accumulate = 0, CouplingBlock::applyMatrix
+ * :206) or d_out += C d_in (accumulate = 1: the out.Update(1.0, z, 1.0) of CoupledModel::applyMatrix, CoupledModel.C:436-470, without
+ * the temporary).  d_in: the neighbouring model's state (ncols doubles, replicated on every rank), on the handle's stream. */
+typedef struct coupling_b200 coupling_b200_t;
+int coupling_b200_create(thcm_b200_t* h, int nrows, const int* rows, const int* beg, const int* jco, const double* co, int64_t ncols,
+                         coupling_b200_t** out);
+int coupling_b200_apply(coupling_b200_t* b, const double* d_in, double* d_out, int accumulate);
+void coupling_b200_destroy(coupling_b200_t* b);
+
 int thcm_b200_exchange_mode(thcm_b200_t* h);             /* fills the halo part of a stored vector (no-op on 1 GPU) */
 /* residual (d_F may be NULL) and/or Jacobian on one state; on several GPUs the halo exchange of d_x runs concurrently with
  * the tiles that read no halo cell (NCCL on a second stream), the rim tiles follow.  Replaces the sequence

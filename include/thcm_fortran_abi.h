@@ -97,6 +97,9 @@ void __m_monthly_MOD_update_forcing(double* t, double* gammaw, double* gammat, d
 void __m_monthly_MOD_update_internal_forcing(double* t, double* gammat, double* gammas);
 void __m_usr_MOD_set_internal_forcing(double* temp, double* salt);
 void __m_thcm_utils_MOD_loadbal_weights(double* weights, double* a, double* b, double* c);
+/* Ocean.C's own Fortran bindings for the coupled model (Ocean.C:1469, 1490, 1545; usrc.F90:201-333), served for Coupled Temperature = 1 */
+void set_atmos_parameters_(void* pars /* Atmosphere::CommPars */); void set_seaice_parameters_(void* pars /* SeaIce::CommPars */);
+void getdeps_(double* Ooa, double* Os, double* nus, double* eta, double* lvsc, double* qdim, double* pQSnd);
 void __m_inserts_MOD_insert_atmosphere_t(double* f); void __m_inserts_MOD_insert_atmosphere_q(double* f);
 void __m_inserts_MOD_insert_atmosphere_a(double* f); void __m_inserts_MOD_insert_atmosphere_p(double* f);
 void __m_inserts_MOD_insert_seaice_q(double* f); void __m_inserts_MOD_insert_seaice_m(double* f); void __m_inserts_MOD_insert_seaice_g(double* f);

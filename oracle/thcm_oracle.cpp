@@ -1583,6 +1583,66 @@ void thcm_oracle_set_par(thcm_oracle* t, int idx1, double value) { // usrc.F90:1
   forcing(*t);
   lin(*t);
 }
+// ---- coupling to an atmosphere / sea-ice model ----
+// usrc.F90:237-293 (set_atmos_parameters): pars in the order of the bind(C) struct atmos_pars / Atmosphere::CommPars
+void thcm_oracle_set_atmos_parameters(thcm_oracle* tp, const double* pars /* 18 */) {
+  T& t = *tp;
+  t.qdim = pars[1]; t.nuq = pars[2]; t.eta = pars[3]; t.dqso = pars[4]; t.eo0 = pars[7]; t.albe0 = pars[12]; t.albed = pars[13];
+  t.nus = t.par[COMB] * t.par[SALT] * t.eta * t.qdim * t.QSnd;
+  t.lvsc = t.par[COMB] * t.par[TEMP] * rhodim * lv * t.QTnd;
+  forcing(t);
+  lin(t);
+}
+// usrc.F90:296-333 (set_seaice_parameters): zeta, a0, Lf, s0, rhoo, qvar, q0
+void thcm_oracle_set_seaice_parameters(thcm_oracle* tp, const double* pars /* 7 */) {
+  T& t = *tp;
+  t.zeta = pars[0]; t.a0 = pars[1]; t.Lf = pars[2]; t.Qvar = pars[5]; t.Q0 = pars[6];
+  forcing(t);
+  lin(t);
+}
+// inserts.F90:12-166; which: 0 tatm, 1 qatm, 2 albe, 3 patm, 4 qsa, 5 msi, 6 gsi.  Like the Fortran, an insert does not
+// recompute forcing / lin: the next set_*_parameters or set_par does (Ocean::synchronize, Ocean.C:1443-1493).
+void thcm_oracle_insert(thcm_oracle* tp, int which, const double* field /* n*m, i fastest */) {
+  T& t = *tp;
+  const bool cT = t.cfg.coupled_T == 1, cS = t.cfg.coupled_S == 1;
+  std::vector<double>* dst = nullptr;
+  switch (which) {
+    case 0: if (cT) dst = &t.tatm; break;
+    case 1: if (cT || cS) dst = &t.qatm; break;
+    case 2: if (cT) dst = &t.albe; break;
+    case 3: if (cS) dst = &t.patm; break;
+    case 4: dst = &t.qsa; break;
+    case 5: dst = &t.msi; break;
+    case 6: if (cS) dst = &t.gsi; break;
+  }
+  if (dst) std::copy(field, field + (size_t)t.n * t.m, dst->begin());
+}
+// usrc.F90:201-219 (getdeps)
+void thcm_oracle_getdeps(thcm_oracle* tp, double* out /* Ooa, Os, nus, eta, lvsc, qdim, pQSnd */) {
+  T& t = *tp;
+  out[0] = t.Ooa; out[1] = t.Os; out[2] = t.nus; out[3] = t.eta; out[4] = t.lvsc; out[5] = t.qdim;
+  out[6] = t.par[COMB] * t.par[SALT] * t.QSnd;
+}
+void thcm_oracle_suno(thcm_oracle* tp, double* suno /* m, index j-1 */) { for (int j = 1; j <= tp->m; j++) suno[j - 1] = tp->suno[j]; }
+// probe.F90:381-444 (get_derivatives), the coupled_T part: dftdm(pos) = QTos - QToa on OCEAN surface points, else 0
+void thcm_oracle_dftdm(thcm_oracle* tp, const double* un, double* dftdm /* n*m */) {
+  T& t = *tp;
+  const int n = t.n, m = t.m, l = t.l;
+  size_t pos = 0;
+  for (int j = 1; j <= m; j++)
+    for (int i = 1; i <= n; i++, pos++) {
+      dftdm[pos] = 0.0;
+      if (t.lm(i, j, l) != OCEAN || t.cfg.coupled_T != 1) continue;
+      // usol (usrc.F90:997-1104) leaves T, S of an OCEAN cell as they are in un
+      const double To = un[t.find_row2(i, j, l, TT) - 1], So = un[t.find_row2(i, j, l, SS) - 1];
+      const double Ta = t.s2(t.tatm, i, j), Ab = t.s2(t.albe, i, j), qa = t.s2(t.qatm, i, j);
+      const double QTos = t.QTnd * t.zeta * (t.a0 * (So + s0) - (To + t0));
+      const double QToa = t.par[COMB] * t.par[SUNP] * t.suno[j] * (1 - t.albe0 - t.albed * Ab) - t.Ooa * (To - Ta) -
+                          t.lvsc * t.eta * t.qdim * (deltat / t.qdim * t.dqso * To - qa) - t.lvsc * t.eo0;
+      dftdm[pos] = QTos - QToa;
+    }
+}
+
 double thcm_oracle_get_par(thcm_oracle* t, int idx1) { return (idx1 >= 1 && idx1 <= NPAR) ? t->par[idx1] : 0.0; }
 int thcm_oracle_ndim(thcm_oracle* t) { return t->ndim; }
 

@@ -78,6 +78,16 @@ void thcm_oracle_intcond_coeff(thcm_oracle*, double* c /* ndim */);
 void thcm_oracle_set_intcond_correction(thcm_oracle*, double corr);
 int64_t thcm_oracle_dropped_entries(thcm_oracle*); /* Fortran entries outside the static graph in the last eval_jac */
 
+/* Coupling to an atmosphere / sea-ice model: usrc.F90:237-333 (pars in the order of the bind(C) structs),
+ * inserts.F90:12-166 (which: 0 tatm, 1 qatm, 2 albe, 3 patm, 4 qsa, 5 msi, 6 gsi; takes effect at the next set_* call as in the
+ * Fortran), getdeps usrc.F90:201-219 (Ooa, Os, nus, eta, lvsc, qdim, pQSnd), suno(j), probe.F90:381-444 (dftdm). */
+void thcm_oracle_set_atmos_parameters(thcm_oracle*, const double* pars /* 18 */);
+void thcm_oracle_set_seaice_parameters(thcm_oracle*, const double* pars /* 7 */);
+void thcm_oracle_insert(thcm_oracle*, int which, const double* field /* n*m */);
+void thcm_oracle_getdeps(thcm_oracle*, double* out /* 7 */);
+void thcm_oracle_suno(thcm_oracle*, double* suno /* m */);
+void thcm_oracle_dftdm(thcm_oracle*, const double* un, double* dftdm /* n*m */);
+
 /* m_scaling::average_block / scal (scaling.F90:29-62, 198-284) on the Fortran CSR of the last fortran_matrix / eval_jac
  * call, and THCM::RecomputeScaling (THCM.C:1694-1750) on one process.  db, mat: column-major 6x6. */
 void thcm_oracle_average_block(thcm_oracle*, double* db /* 36 */);

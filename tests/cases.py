@@ -47,6 +47,15 @@ def case(name):
     if name == "coupled4":     # BASELINE config 3 (ocean block): Coupled Temperature=1, qz=1.5
         cfg = g.global_config(96, 38, 12, qz=1.5, coupled_T=1)
         return cfg, g.synthetic_mask(96, 38, 12), dict(g.STARTING_PARS["global"])
+    if name == "coupled_small":  # row N2: small periodic globe with land, Coupled Temperature = 1, non-zero solar forcing
+        cfg = g.global_config(24, 12, 6, qz=1.5, coupled_T=1)
+        return cfg, g.random_mask(24, 12, 6, True, 13), dict(g.STARTING_PARS["global"], SUNP=0.7)
+    if name == "coupled_small_nomix":  # Mixing = 0: no tanh anywhere, the CUDA path must reproduce every bit of the oracle
+        cfg = g.global_config(24, 12, 6, qz=1.5, coupled_T=1, vmix=0)
+        return cfg, g.random_mask(24, 12, 6, True, 13), dict(g.STARTING_PARS["global"], SUNP=0.7)
+    if name == "coupled_box":    # same without periodicity, pressure points fixed
+        cfg = g.default_config(14, 9, 5, coupled_T=1, fix_pressure_points=1)
+        return cfg, g.random_mask(14, 9, 5, False, 17, land_frac=0.15), dict(g.STARTING_PARS["global"], SUNP=1.0)
     if name == "global_half":  # 48x19x12 sweep point
         cfg = g.global_config(48, 19, 12)
         return cfg, g.upsample_mask(g.fixture_mask("mask_global_96x38x12"), 48, 19, 12), dict(g.STARTING_PARS["global"])
@@ -83,3 +92,62 @@ def make_pair(name):
         O.set_par(k, v)
         G.setPar(k, v)
     return cfg, mask, O, G
+
+
+# ---- row N2: an attached atmosphere and sea ice (values of the order the reference's models hand over) ----
+ATMOS_PARS = dict(tdim=1.0, qdim=0.01, nuq=2.58e-2, eta=4.68e-2, dqso=5.6e-4, dqsi=6.4e-4, dqdt=5.0e-4, Eo0=3.1e-8, Ei0=2.2e-8, Cs=1.0e-3,
+                  t0o=15.0, t0i=-5.0, a0=0.3, da=0.5, tauf=1.4e5, tauc=3.0e6, comb=1.0, albf=1.0)
+SEAICE_PARS = dict(zeta=1.7e3, a0=-0.0575, Lf=3.347e5, s0=35.0, rhoo=1.024e3, qvar=5.0e-1, q0=-1.0e2)
+
+
+def coupling_fields(cfg, seed=3):
+    """synthetic interface fields on the n x m surface (i fastest): atmosphere temperature / humidity / albedo anomalies and a
+    sea-ice mask with open water, full cover and fractional values (the reference's mask is a smooth tanh of the ice thickness)"""
+    n, m = cfg["n"], cfg["m"]
+    rng = np.random.default_rng(seed)
+    lat = np.repeat(np.linspace(-1.0, 1.0, m), n)
+    f = dict(tatm=rng.normal(0.0, 3.0, n * m) - 10.0 * lat ** 2,
+             qatm=rng.normal(0.0, 2.0e-3, n * m),
+             albe=rng.uniform(0.0, 1.0, n * m),
+             msi=np.where(np.abs(lat) > 0.7, 1.0, np.where(np.abs(lat) > 0.45, rng.uniform(0.0, 1.0, n * m), 0.0)))
+    return f
+
+
+def attach(obj, cfg, seed=3, seaice=True):
+    """Ocean::synchronize(atmos) then Ocean::synchronize(seaice) (Ocean.C:1443-1493): inserts, then the parameter calls"""
+    f = coupling_fields(cfg, seed)
+    for k in ("tatm", "qatm", "albe"):
+        obj.insert(k, f[k])
+    obj.set_atmos_parameters(ATMOS_PARS)
+    if seaice:
+        obj.insert("msi", f["msi"])
+        obj.set_seaice_parameters(SEAICE_PARS)
+    return f
+
+
+def blocks_from_oracle(O, cfg, mask, x, f, albed):
+    """Ocean::getBlock(Atmosphere) / getBlock(SeaIce), T rows, restated on the oracle's numbers (Ocean.C:1538-1746)"""
+    n, m, l = cfg["n"], cfg["m"], cfg["l"]
+    d = O.getdeps()
+    comb, sunp = O.get_par("COMB"), O.get_par("SUNP")
+    suno, dftdm = O.suno(), O.dftdm(x)
+    surf = np.asarray(mask).reshape(l + 2, m + 2, n + 2)[l, 1:m + 1, 1:n + 1]
+    A, S = [], []
+    for j in range(m):
+        for i in range(n):
+            if surf[j, i] != 0:
+                continue
+            sr = j * n + i
+            M = f["msi"][sr]
+            row = 6 * ((l - 1) * n * m + n * j + i) + 4
+            dTFT = d["Ooa"] * (1.0 - M)
+            dAFT = -comb * sunp * suno[j] * albed * (1.0 - M)
+            dQFT = d["lvsc"] * d["eta"] * d["qdim"] * (1.0 - M)
+            A.append((row, [(3 * sr + 0, -dTFT), (3 * sr + 2, -dAFT), (3 * sr + 1, -dQFT)]))
+            S.append((row, [(4 * sr + 2, -dftdm[sr])]))
+    return A, S
+
+
+def compact(block):
+    rows, beg, jco, co = block
+    return [(int(rows[r]), [(int(jco[p]), float(co[p])) for p in range(beg[r], beg[r + 1])]) for r in range(rows.size)]

@@ -58,6 +58,31 @@ int hostcheck_set_par(void* h, int idx, double v, char* err, int errlen) {
   try { ((Host*)h)->set_par(idx, v); return 0; }
   catch (const std::exception& e) { if (err) { strncpy(err, e.what(), errlen - 1); err[errlen - 1] = 0; } return -1; }
 }
+// coupling to an atmosphere / sea-ice model
+int hostcheck_insert(void* h, int which, const double* field, char* err, int errlen) {
+  try { ((Host*)h)->insert_field(which, field); return 0; } catch (std::exception& e) { snprintf(err, errlen, "%s", e.what()); return 1; }
+}
+void hostcheck_set_atmos_parameters(void* h, const double* pars) { ((Host*)h)->set_atmos_parameters(pars); }
+void hostcheck_set_seaice_parameters(void* h, const double* pars) { ((Host*)h)->set_seaice_parameters(pars); }
+void hostcheck_getdeps(void* h, double* out) { ((Host*)h)->getdeps(out); }
+void hostcheck_suno(void* h, double* out) { Host* H = (Host*)h; for (int j = 1; j <= H->m; j++) out[j - 1] = H->cpl.suno[j]; }
+// m_probe::get_derivatives, coupled_T part: the loop of dftdm_kernel (coupled.cu) around the shared expression thcm_dftdm
+void hostcheck_dftdm(void* h, const double* x, double* out) {
+  Host* H = (Host*)h;
+  const Scalars& S = H->S;
+  const DftdmScal a = H->dftdm_scalars();
+  const Host::Coupling& c = H->cpl;
+  const size_t nm = (size_t)H->n * H->m;
+  for (int j = S.jo0; j < S.jo0 + S.mloc; j++) for (int i = S.io0; i < S.io0 + S.nloc; i++) {
+    const size_t ci = cell_index(S, i, j, S.l), g = (size_t)(j - 1) * S.n + (i - 1), t = (size_t)(j - S.jo0) * S.nloc + (i - S.io0);
+    out[t] = 0.0;
+    if (H->cfg.coupled_T != 1 || sbit(H->sig[ci], SIG_NOTOCEAN)) continue;
+    out[t] = thcm_dftdm(a, x[6 * ci + 4], x[6 * ci + 5], c.tatm.size() == nm ? c.tatm[g] : 0.0, c.albe.size() == nm ? c.albe[g] : 0.0,
+                        c.qatm.size() == nm ? c.qatm[g] : 0.0, c.suno[j]);
+  }
+}
+int hostcheck_atmos_block(void* h, int* rows, int* beg, int* jco, double* co) { return ((Host*)h)->atmos_block(rows, beg, jco, co); }
+int hostcheck_seaice_block(void* h, const double* dftdm, int* rows, int* beg, int* jco, double* co) { return ((Host*)h)->seaice_block(dftdm, rows, beg, jco, co); }
 double hostcheck_get_par(void* h, int idx) { return ((Host*)h)->get_par(idx); }
 long long hostcheck_nnz(void* h) { return (long long)((Host*)h)->col.size(); }
 int hostcheck_rowintcon(void* h) { return ((Host*)h)->rowintcon; }
@@ -110,7 +135,7 @@ int hostcheck_scal(const double* db, double* dr, double* dc) { return scal(db, d
 static void jac_with_side(void* h, const double* x, double* val, double* diagB, double* side) {
   Host* H = (Host*)h;
   const Scalars& S = H->S;
-  Tables T = H->tables(H->tab.data());
+  Tables T = H->host_tables();
   SpecialRows sp{H->owns_rowintcon ? H->rowintcon_local : -1, H->rowPfix1_local, H->rowPfix2_local, side};
   for (size_t q = 0; q < H->col.size(); q++) val[q] = 0.0;
   for (int k = 1; k <= S.l; k++) for (int j = S.jo0; j < S.jo0 + S.mloc; j++) for (int i = S.io0; i < S.io0 + S.nloc; i++) {
@@ -134,7 +159,7 @@ static void jac_with_side(void* h, const double* x, double* val, double* diagB, 
 void hostcheck_rhs(void* h, const double* x, double* Fo) {
   Host* H = (Host*)h;
   const Scalars& S = H->S;
-  Tables T = H->tables(H->tab.data());
+  Tables T = H->host_tables();
   for (int k = 1; k <= S.l; k++) for (int j = S.jo0; j < S.jo0 + S.mloc; j++) for (int i = S.io0; i < S.io0 + S.nloc; i++) {
     size_t ci = cell_index(S, i, j, k);
     Cell c{i, j, k, H->sig[ci]};

@@ -14,7 +14,7 @@ _LIB = None
 _SO = os.path.join(ROOT, "tests", "_build", "libhostcheck.so")
 _SRCS = [os.path.join(ROOT, "tests", "host_rowcheck.cpp"), os.path.join(ROOT, "iemic_b200", "csrc", "thcm_host.cpp")]
 _DEPS = _SRCS + [os.path.join(ROOT, "iemic_b200", "csrc", f) for f in
-                 ("thcm_rows.cuh", "thcm_stage.cuh", "thcm_cell.cuh", "thcm_host.h")]
+                 ("thcm_rows.cuh", "thcm_stage.cuh", "thcm_cell.cuh", "thcm_coupled.cuh", "thcm_host.h")]
 
 
 def lib():
@@ -54,6 +54,14 @@ def lib():
         L.hostcheck_rhs.argtypes = [C.c_void_p, dp, dp]
         L.hostcheck_scaling.argtypes = [C.c_void_p, dp, dp, dp, dp]
         L.hostcheck_scal.argtypes = [dp, dp, dp]
+        L.hostcheck_insert.argtypes = [C.c_void_p, C.c_int, dp, C.c_char_p, C.c_int]
+        L.hostcheck_set_atmos_parameters.argtypes = [C.c_void_p, dp]
+        L.hostcheck_set_seaice_parameters.argtypes = [C.c_void_p, dp]
+        L.hostcheck_getdeps.argtypes = [C.c_void_p, dp]
+        L.hostcheck_suno.argtypes = [C.c_void_p, dp]
+        L.hostcheck_dftdm.argtypes = [C.c_void_p, dp, dp]
+        L.hostcheck_atmos_block.argtypes = [C.c_void_p, ip, ip, ip, dp]
+        L.hostcheck_seaice_block.argtypes = [C.c_void_p, dp, ip, ip, ip, dp]
         _LIB = L
     return _LIB
 
@@ -111,6 +119,54 @@ class HostCheck:
 
     def get_par(self, name):
         return lib().hostcheck_get_par(self.h, PAR[name] if isinstance(name, str) else name)
+
+    # coupling: same names and orders as oracle_lib.Oracle
+    def insert(self, which, field):
+        from oracle_lib import Oracle
+        f = np.ascontiguousarray(field, np.float64).ravel()
+        err = C.create_string_buffer(512)
+        if lib().hostcheck_insert(self.h, Oracle.FIELDS[which], _dp(f), err, 512) != 0:
+            raise RuntimeError(err.value.decode())
+
+    def set_atmos_parameters(self, pars):
+        from oracle_lib import Oracle
+        a = np.array([float(pars[k]) for k in Oracle.ATMOS_PARS])
+        lib().hostcheck_set_atmos_parameters(self.h, _dp(a))
+
+    def set_seaice_parameters(self, pars):
+        from oracle_lib import Oracle
+        a = np.array([float(pars[k]) for k in Oracle.SEAICE_PARS])
+        lib().hostcheck_set_seaice_parameters(self.h, _dp(a))
+
+    def getdeps(self):
+        out = np.zeros(7)
+        lib().hostcheck_getdeps(self.h, _dp(out))
+        return dict(zip(("Ooa", "Os", "nus", "eta", "lvsc", "qdim", "pQSnd"), out))
+
+    def suno(self):
+        out = np.zeros(self.c.m)
+        lib().hostcheck_suno(self.h, _dp(out))
+        return out
+
+    def dftdm(self, x):
+        x = np.ascontiguousarray(x, np.float64)
+        i0, j0, nloc, mloc, _, _ = self.block()
+        out = np.zeros(nloc * mloc)
+        lib().hostcheck_dftdm(self.h, _dp(x), _dp(out))
+        return out
+
+    def _block(self, fn, *lead):
+        nm = self.c.n * self.c.m
+        rows, beg, jco, co = np.zeros(nm, np.int32), np.zeros(nm + 1, np.int32), np.zeros(3 * nm, np.int32), np.zeros(3 * nm)
+        k = fn(self.h, *lead, _ip(rows), _ip(beg), _ip(jco), _dp(co))
+        return rows[:k].copy(), beg[:k + 1].copy(), jco[:beg[k]].copy(), co[:beg[k]].copy()
+
+    def atmos_block(self):
+        return self._block(lib().hostcheck_atmos_block)
+
+    def seaice_block(self, dftdm):
+        d = np.ascontiguousarray(dftdm, np.float64)
+        return self._block(lib().hostcheck_seaice_block, _dp(d))
 
     def graph(self):
         if self._graph is None:

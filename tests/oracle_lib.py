@@ -83,6 +83,12 @@ def lib():
         L.thcm_oracle_set_intcond_correction.argtypes = [C.c_void_p, C.c_double]
         L.thcm_oracle_dropped_entries.argtypes = [C.c_void_p]
         L.thcm_oracle_dropped_entries.restype = C.c_int64
+        L.thcm_oracle_set_atmos_parameters.argtypes = [C.c_void_p, dp]
+        L.thcm_oracle_set_seaice_parameters.argtypes = [C.c_void_p, dp]
+        L.thcm_oracle_insert.argtypes = [C.c_void_p, C.c_int, dp]
+        L.thcm_oracle_getdeps.argtypes = [C.c_void_p, dp]
+        L.thcm_oracle_suno.argtypes = [C.c_void_p, dp]
+        L.thcm_oracle_dftdm.argtypes = [C.c_void_p, dp, dp]
         L.thcm_oracle_average_block.argtypes = [C.c_void_p, dp]
         L.thcm_oracle_scal.argtypes = [dp, dp, dp]
         L.thcm_oracle_recompute_scaling.argtypes = [C.c_void_p, dp, dp]
@@ -123,6 +129,40 @@ class Oracle:
 
     def get_par(self, name):
         return lib().thcm_oracle_get_par(self.h, PAR[name] if isinstance(name, str) else name)
+
+    # ---- coupling: usrc.F90:237-333, inserts.F90, getdeps, probe.F90:381-444 ----
+    FIELDS = dict(tatm=0, qatm=1, albe=2, patm=3, qsa=4, msi=5, gsi=6)
+    ATMOS_PARS = ("tdim", "qdim", "nuq", "eta", "dqso", "dqsi", "dqdt", "Eo0", "Ei0", "Cs", "t0o", "t0i", "a0", "da", "tauf", "tauc", "comb", "albf")
+    SEAICE_PARS = ("zeta", "a0", "Lf", "s0", "rhoo", "qvar", "q0")
+
+    def set_atmos_parameters(self, pars):
+        a = np.array([float(pars[k]) for k in self.ATMOS_PARS])
+        lib().thcm_oracle_set_atmos_parameters(self.h, _dp(a))
+
+    def set_seaice_parameters(self, pars):
+        a = np.array([float(pars[k]) for k in self.SEAICE_PARS])
+        lib().thcm_oracle_set_seaice_parameters(self.h, _dp(a))
+
+    def insert(self, which, field):
+        f = np.ascontiguousarray(field, np.float64).ravel()
+        assert f.size == self.cfg["n"] * self.cfg["m"]
+        lib().thcm_oracle_insert(self.h, self.FIELDS[which], _dp(f))
+
+    def getdeps(self):
+        out = np.zeros(7)
+        lib().thcm_oracle_getdeps(self.h, _dp(out))
+        return dict(zip(("Ooa", "Os", "nus", "eta", "lvsc", "qdim", "pQSnd"), out))
+
+    def suno(self):
+        out = np.zeros(self.cfg["m"])
+        lib().thcm_oracle_suno(self.h, _dp(out))
+        return out
+
+    def dftdm(self, x):
+        x = np.ascontiguousarray(x, np.float64)
+        out = np.zeros(self.cfg["n"] * self.cfg["m"])
+        lib().thcm_oracle_dftdm(self.h, _dp(x), _dp(out))
+        return out
 
     def graph(self):
         if self._graph is None:

@@ -10,7 +10,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 def _declared():
     src = open(os.path.join(ROOT, "include", "iemic_b200.h")).read()
     src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
-    return sorted(set(re.findall(r"\b((?:thcm_b200|gmres_b200|vec_b200|iemic_b200)_[a-z0-9_]+)\s*\(", src)))
+    return sorted(set(re.findall(r"\b((?:thcm_b200|gmres_b200|vec_b200|iemic_b200|coupling_b200)_[a-z0-9_]+)\s*\(", src)))
 
 
 def test_library_exports_every_declared_symbol():

@@ -1,0 +1,125 @@
+"""Row N2 on the CPU: the ocean side of the coupling to an atmosphere / sea-ice model (Coupled Temperature = 1).
+
+The product's host code (parameters, per-cell surface forcing, coefficient tables) and its __host__ __device__ row code --
+the arithmetic the CUDA kernels run -- against the oracle's restatement of usrc.F90:237-333, 725-741, forcing.F90:73-96 and
+inserts.F90: bit-exact, like every other case of tests/test_host_rows.py."""
+import numpy as np
+import pytest
+
+import cases
+import hostcheck_lib as hl
+import oracle_lib as ol
+
+
+def _pair(name):
+    cfg, mask, pars = cases.case(name)
+    O, H = ol.Oracle(cfg, mask), hl.HostCheck(cfg, mask)
+    for k, v in pars.items():
+        O.set_par(k, v)
+        H.set_par(k, v)
+    return cfg, mask, O, H
+
+
+def _same(O, H, cfg, mask):
+    O.rhs(np.zeros(O.ndim))  # the oracle masks Frc during an evaluation
+    assert np.array_equal(O.frc(), H.frc())
+    for kind, seed in (("random", 1), ("smooth", 2)):
+        x = cases.state(cfg, mask, seed=seed, kind=kind)
+        assert np.array_equal(O.rhs(x), H.rhs(x))
+        vo, bo = O.jac(x)
+        vh, bh = H.jac(x)
+        assert O.dropped() == 0
+        assert np.array_equal(vo, vh)
+        assert np.array_equal(bo, bh)
+
+
+@pytest.mark.parametrize("name", ["coupled_small", "coupled_box"])
+def test_attached_atmosphere_and_sea_ice_bit_exact(name):
+    cfg, mask, O, H = _pair(name)
+    _same(O, H, cfg, mask)                                  # nothing attached yet: only the solar term of the forcing
+    x = cases.state(cfg, mask, seed=1)
+    F0, (v0, _) = O.rhs(x), O.jac(x)
+    cases.attach(O, cfg, seaice=False)
+    cases.attach(H, cfg, seaice=False)
+    assert O.getdeps() == H.getdeps() and O.getdeps()["lvsc"] != 0.0
+    _same(O, H, cfg, mask)                                  # atmosphere: latent heat term dedt, per-cell forcing
+    F1, (v1, _) = O.rhs(x), O.jac(x)
+    assert not np.array_equal(F0, F1) and not np.array_equal(v0, v1)
+    cases.attach(O, cfg, seaice=True)
+    cases.attach(H, cfg, seaice=True)
+    _same(O, H, cfg, mask)                                  # sea ice: mask-dependent centre coefficient and the (T,S) entry
+    F2, (v2, _) = O.rhs(x), O.jac(x)
+    assert not np.array_equal(F1, F2) and not np.array_equal(v1, v2)
+    # the T row of an ice-covered surface cell now depends on S (Al(5,TT,SS) = -QTnd*zeta*a0*mc)
+    rp, col = O.graph()
+    rows = np.repeat(np.arange(rp.size - 1), np.diff(rp))
+    ts = (rows % 6 == 4) & (col == rows + 1)
+    assert np.count_nonzero(v2[ts] != v1[ts]) > 0
+    # a parameter change afterwards keeps lvsc / nus as the last synchronisation left them (usrc.F90:163-181 calls forcing and lin only)
+    O.set_par("COMB", 0.35)
+    H.set_par("COMB", 0.35)
+    assert O.getdeps() == H.getdeps()
+    _same(O, H, cfg, mask)
+
+
+def test_insert_takes_effect_at_the_next_parameter_call():
+    """inserts.F90 only stores the field; forcing and lin run in set_*_parameters / setparcs (Ocean::synchronize, Ocean.C:1443-1493)"""
+    cfg, mask, O, H = _pair("coupled_small")
+    f = cases.coupling_fields(cfg)
+    before = H.frc().copy()
+    for obj in (O, H):
+        obj.insert("tatm", f["tatm"])
+        obj.insert("msi", f["msi"])
+    assert np.array_equal(H.frc(), before)
+    x = cases.state(cfg, mask, seed=4)
+    assert np.array_equal(O.rhs(x), H.rhs(x))               # the sea-ice mask is not in the coefficients yet either
+    for obj in (O, H):
+        obj.set_par("TEMP", 9.0)
+    assert not np.array_equal(H.frc(), before)
+    _same(O, H, cfg, mask)
+
+
+def test_uncoupled_model_ignores_the_atmosphere_fields():
+    cfg, mask, O, H = _pair("natl8")
+    f = cases.coupling_fields(cfg)
+    x = cases.state(cfg, mask, seed=5)
+    F0 = H.rhs(x)
+    for obj in (O, H):
+        obj.insert("tatm", f["tatm"])                       # coupled_T = 0: inserts.F90:24 ignores it
+        obj.insert("albe", f["albe"])
+        obj.set_par("TEMP", obj.get_par("TEMP"))
+    assert np.array_equal(H.rhs(x), F0)
+    assert np.array_equal(O.rhs(x), F0)
+
+
+def test_coupled_salinity_fields_are_refused():
+    cfg, mask, pars = cases.case("coupled_small")
+    H = hl.HostCheck(cfg, mask)
+    f = cases.coupling_fields(cfg)
+    H.insert("patm", f["qatm"])                             # coupled_S = 0: ignored, as in inserts.F90:91
+    with pytest.raises(RuntimeError):
+        hl.HostCheck(dict(cfg, coupled_S=1), mask)
+
+
+@pytest.mark.parametrize("name", ["coupled_small", "coupled_box"])
+def test_derivative_field_and_coupling_blocks(name):
+    """m_probe::get_derivatives (probe.F90:429-444: the expression the CUDA kernel runs, compiled for the CPU) and
+    Ocean::getBlock(Atmosphere / SeaIce) (Ocean.C:1538-1746) against the oracle / a restatement on the oracle's numbers"""
+    cfg, mask, O, H = _pair(name)
+    f = cases.attach(O, cfg)
+    cases.attach(H, cfg)
+    x = cases.state(cfg, mask, seed=5)
+    assert np.array_equal(O.suno(), H.suno())
+    d = O.dftdm(x)
+    assert np.array_equal(d, H.dftdm(x))
+    surf = np.asarray(mask).reshape(cfg["l"] + 2, cfg["m"] + 2, cfg["n"] + 2)[cfg["l"], 1:-1, 1:-1].ravel()
+    assert np.all(d[surf != 0] == 0.0) and np.count_nonzero(d[surf == 0]) == np.count_nonzero(surf == 0)
+    Ao, So = cases.blocks_from_oracle(O, cfg, mask, x, f, cases.ATMOS_PARS["da"])
+    assert cases.compact(H.atmos_block()) == Ao
+    assert cases.compact(H.seaice_block(d)) == So
+    assert len(Ao) == np.count_nonzero(surf == 0)
+    # an ice-covered point is cut off from the atmosphere (1 - M = 0), open water feels all three atmosphere unknowns
+    full = [e for (row, e), M in zip(Ao, f["msi"][surf == 0]) if M == 1.0]
+    open_ = [e for (row, e), M in zip(Ao, f["msi"][surf == 0]) if M == 0.0]
+    assert full and all(all(a == 0.0 for _, a in e) for e in full)
+    assert open_ and all(all(a != 0.0 for _, a in e) for e in open_)

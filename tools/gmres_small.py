@@ -57,6 +57,7 @@ def main():
     out = {}
     for flag in ("1", "0"):
         env = dict(os.environ, IEMIC_GMRES_CYCLE=flag)
+        env.setdefault("IEMIC_GMRES_CYCLE_ROWS", "400000") # so that the 4-degree grid shows what the cooperative kernel does there
         p = subprocess.run([sys.executable, os.path.abspath(__file__), "--child"], env=env, capture_output=True, text=True, timeout=170)
         if p.returncode != 0:
             print("leg", flag, "failed:", p.stderr[-2000:])
