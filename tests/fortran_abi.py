@@ -100,6 +100,36 @@ class FortranTHCM:
             v[5::6] = mean
         return db.reshape(6, 6).T.copy(), r, c
 
+    # ---- row N2: m_inserts, set_*_parameters_, getdeps_, m_probe (Ocean::synchronize / getBlock, Ocean.C:1443-1746) ----
+    INSERTS = dict(tatm="atmosphere_t", qatm="atmosphere_q", albe="atmosphere_a", patm="atmosphere_p", qsa="seaice_q", msi="seaice_m", gsi="seaice_g")
+
+    def insert(self, which, field):
+        f = np.ascontiguousarray(field, np.float64).ravel()
+        getattr(self.L, "__m_inserts_MOD_insert_" + self.INSERTS[which])(f.ctypes.data_as(C.POINTER(C.c_double)))
+
+    def set_atmos_parameters(self, pars):
+        from oracle_lib import Oracle
+        a = np.array([float(pars[k]) for k in Oracle.ATMOS_PARS])
+        self.L.set_atmos_parameters_(a.ctypes.data_as(C.c_void_p))
+
+    def set_seaice_parameters(self, pars):
+        from oracle_lib import Oracle
+        a = np.array([float(pars[k]) for k in Oracle.SEAICE_PARS])
+        self.L.set_seaice_parameters_(a.ctypes.data_as(C.c_void_p))
+
+    def getdeps(self):
+        v = [C.c_double(0.0) for _ in range(7)]
+        self.L.getdeps_(*[C.byref(q) for q in v])
+        return dict(zip(("Ooa", "Os", "nus", "eta", "lvsc", "qdim", "pQSnd"), (q.value for q in v)))
+
+    def get_derivatives(self, un):
+        un = np.ascontiguousarray(un, np.float64)
+        nm = self.cfg["n"] * self.cfg["m"]
+        out = [np.full(nm, np.nan) for _ in range(4)]
+        dp = lambda a: a.ctypes.data_as(C.POINTER(C.c_double))
+        getattr(self.L, "__m_probe_MOD_get_derivatives")(dp(un), *[dp(o) for o in out])
+        return out
+
     def close(self):
         self.L.finalize_()
         getattr(self.L, "__m_global_MOD_finalize")()

@@ -79,3 +79,31 @@ def test_setsres_switches_surface_condition():
         assert np.abs(Bo - Bt).max() <= 1e-12 * np.abs(Bo).max()
     finally:
         T.close()
+
+
+def test_coupling_symbols_match_oracle():
+    """row N2 through the Fortran names: m_inserts, set_atmos_parameters_ / set_seaice_parameters_, getdeps_, m_probe::get_derivatives"""
+    import oracle_lib as ol
+    import iemic_b200 as ib
+    from fortran_abi import FortranTHCM
+    cfg, mask, pars = cases.case("coupled_small_nomix")
+    O = ol.Oracle(cfg, mask)
+    T = FortranTHCM(cfg, mask)
+    try:
+        for k, v in pars.items():
+            O.set_par(k, v)
+            T.setpar(ib.PAR[k], v)
+        cases.attach(O, cfg)
+        cases.attach(T, cfg)
+        assert O.getdeps() == T.getdeps()
+        x = cases.state(cfg, mask, seed=12)
+        assert np.array_equal(O.fortran_rhs(x), T.rhs(x))          # Mixing = 0: no tanh, every bit
+        bo, jo, co, cbo = O.fortran_matrix(x)
+        bt, jt, ct, cbt = T.matrix(x)
+        assert np.array_equal(bo, bt) and np.array_equal(jo, jt) and np.array_equal(co, ct) and np.array_equal(cbo, cbt)
+        dftdm, dfsdq, dfsdm, dfsdg = T.get_derivatives(x)
+        assert np.array_equal(dftdm, O.dftdm(x))
+        assert not dfsdq.any() and not dfsdm.any() and not dfsdg.any()   # Coupled Salinity = 0 (probe.F90:446)
+    finally:
+        T.close()
+
