@@ -98,6 +98,54 @@ int main() {
       std::printf("reference GMRESSolver on OceanB200: rc=%d iters=%d resid=%g\n", rrc, ref.getNumIters(), ref.residual());
     }
 #endif
+    { // coupled model, ocean side (row N2): attach an atmosphere and sea ice, blocks in the reference's container and on the device
+      thcm_b200_config cc = box_config(n, m, l);
+      cc.coupled_T = 1;
+      OceanB200 oc(cc, mask.data());
+      oc.setPar("Combined Forcing", 0.05); oc.setPar("Temperature Forcing", 10.0); oc.setPar("Solar Forcing", 1.0);
+      oc.getState('V')->fromHost(hx.data());
+      oc.computeRHS();
+      const double f_alone = oc.getRHS('V')->norm();
+      const size_t nm = (size_t)n * m;
+      std::vector<double> Ta(nm), Qa(nm), Aa(nm), Ms(nm);
+      for (size_t q = 0; q < nm; q++) { Ta[q] = 5.0 * rnd(); Qa[q] = 1e-3 * rnd(); Aa[q] = 0.5 + rnd(); Ms[q] = (q / n) >= (size_t)(m - 3) ? 1.0 : 0.0; }
+      thcm_b200_atmos_pars ap{}; ap.tdim = 1.0; ap.qdim = 0.01; ap.nuq = 2.58e-2; ap.eta = 4.68e-2; ap.dqso = 5.6e-4; ap.Eo0 = 3.1e-8; ap.a0 = 0.3; ap.da = 0.5;
+      thcm_b200_seaice_pars sp{}; sp.zeta = 1.7e3; sp.a0 = -0.0575; sp.Lf = 3.347e5; sp.s0 = 35.0; sp.rhoo = 1.024e3;
+      oc.synchronizeAtmosphere(Ta.data(), Qa.data(), Aa.data(), ap);
+      oc.synchronizeSeaIce(Ms.data(), sp);
+      oc.computeRHS();
+      const double f_coupled = oc.getRHS('V')->norm();
+      if (!(f_coupled != f_alone) || !std::isfinite(f_coupled)) { std::printf("coupling left the residual unchanged (%g)\n", f_coupled); return 1; }
+      auto A = oc.getAtmosBlock();
+      auto S = oc.getSeaIceBlock();
+      if (A->beg.size() != (size_t)N + 1 || A->beg.back() != (int)(3 * nm) || S->beg.back() != (int)nm) { std::printf("coupling block sizes %zu %d %d\n", A->beg.size(), A->beg.back(), S->beg.back()); return 1; }
+      // J d + C_OA v on the device against the same sum on the host
+      oc.computeJacobian();
+      DeviceVector dd(oc.handle()), out(oc.handle());
+      dd.fromHost(hd.data());
+      oc.applyMatrix(dd, out);
+      std::vector<double> base((size_t)N), got((size_t)N), v(3 * nm);
+      out.toHost(base.data());
+      for (auto& q : v) q = rnd();
+      double* d_v = nullptr;
+      check(iemic_b200_malloc((void**)&d_v, (int64_t)(v.size() * sizeof(double))));
+      check(iemic_b200_memcpy_h2d(d_v, v.data(), (int64_t)(v.size() * sizeof(double))));
+      OceanB200::CouplingBlock C(oc, false, (int64_t)(3 * nm));
+      C.addTo(d_v, out);
+      out.toHost(got.data());
+      iemic_b200_free(d_v);
+      double worst = 0.0;
+      for (int64_t r = 0; r < N; r++) {
+        double sum = 0.0;
+        for (int p = A->beg[r]; p < A->beg[r + 1]; p++) sum += A->co[p] * v[A->jco[p]];
+        double mag = std::fabs(base[r]);
+        for (int p = A->beg[r]; p < A->beg[r + 1]; p++) mag += std::fabs(A->co[p] * v[A->jco[p]]);
+        // (the device adds a row's entries in column order, this loop in the reference's push order: rounding only)
+        worst = std::fmax(worst, std::fabs(got[r] - (base[r] + sum)) / (mag > 0 ? mag : 1.0));
+      }
+      std::printf("coupled: |F| %.6e -> %.6e, block product deviation %.3e\n", f_alone, f_coupled, worst);
+      if (!(worst <= 1e-14)) return 1;
+    }
     std::printf("selftest ok\n");
   } catch (const std::exception& e) {
     std::printf("selftest failed: %s\n", e.what());
