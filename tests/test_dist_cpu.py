@@ -16,10 +16,14 @@ import oracle_lib as ol
 
 
 def _assemble(name, nranks):
+    attach = name.endswith("+coupling")   # row N2: an atmosphere and sea ice attached (every rank gets the whole interface fields)
+    name = name.replace("+coupling", "")
     cfg, mask, pars = cases.case(name)
     O = ol.Oracle(cfg, mask)
     for k, v in pars.items():
         O.set_par(k, v)
+    if attach:
+        cases.attach(O, cfg)
     x = cases.state(cfg, mask, seed=7)
     N = O.ndim
     F = np.full(N, np.nan)
@@ -30,6 +34,8 @@ def _assemble(name, nranks):
         H = hl.HostCheck(cfg, mask, rank=r, nranks=nranks)
         for k, v in pars.items():
             H.set_par(k, v)
+        if attach:
+            cases.attach(H, cfg)
         gid = H.gid()
         assert np.all(gid[:H.ndim] >= 0)
         seen[gid[:H.ndim]] += 1
@@ -51,7 +57,7 @@ def _assemble(name, nranks):
 
 
 @pytest.mark.parametrize("name,nranks", [("rand_periodic", 2), ("rand_periodic", 4), ("rand_periodic", 8), ("rand_box", 2), ("rand_box", 6),
-                                         ("global_half", 8), ("coupled4", 4), ("natl8_sres1", 4), ("2dmoc_sres1", 2), ("2dmoc_run_sres1", 4)])
+                                         ("global_half", 8), ("coupled4", 4), ("coupled_small+coupling", 4), ("coupled_box+coupling", 6), ("natl8_sres1", 4), ("2dmoc_sres1", 2), ("2dmoc_run_sres1", 4)])
 def test_rank_pieces_reproduce_the_global_problem(name, nranks):
     cfg, O, x, F, B, rows_g, cols_g, vals_g = _assemble(name, nranks)
     assert np.array_equal(F, O.rhs(x))
