@@ -233,8 +233,9 @@ void Host::getdeps(double* o) const {
   o[6] = par[P_COMB] * par[P_SALT] * cpl.QSnd;
 }
 
-DftdmScal Host::dftdm_scalars() const {
+DftdmScal Host::dftdm_scalars() {
   DftdmScal a;
+  cpl.nus = par[P_COMB] * par[P_SALT] * cpl.eta * cpl.qdim * cpl.QSnd; // probe.F90:414: get_derivatives refreshes the module variable
   a.cs = par[P_COMB] * par[P_SUNP];
   a.albe0 = cpl.albe0; a.albed = cpl.albed; a.Ooa = cpl.Ooa;
   a.leq = cpl.lvsc * cpl.eta * cpl.qdim;

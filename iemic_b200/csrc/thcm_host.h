@@ -95,7 +95,7 @@ class Host {
   void set_atmos_parameters(const double* pars18);         // usrc.F90:237-293
   void set_seaice_parameters(const double* pars7);         // usrc.F90:296-333
   void getdeps(double* out7) const;                        // usrc.F90:201-219: Ooa, Os, nus, eta, lvsc, qdim, pQSnd
-  DftdmScal dftdm_scalars() const;                         // probe.F90:433-440
+  DftdmScal dftdm_scalars();                               // probe.F90:414-440 (assigns nus like the Fortran does there)
   // Ocean::getBlock(Atmosphere) / getBlock(SeaIce) (Ocean.C:1538-1746), T rows, compact (see include/iemic_b200.h); return the row count
   int atmos_block(int* rows, int* beg, int* jco, double* co) const;
   int seaice_block(const double* dftdm /* n*m */, int* rows, int* beg, int* jco, double* co) const;

@@ -1629,6 +1629,7 @@ void thcm_oracle_dftdm(thcm_oracle* tp, const double* un, double* dftdm /* n*m *
   T& t = *tp;
   const int n = t.n, m = t.m, l = t.l;
   size_t pos = 0;
+  t.nus = t.par[COMB] * t.par[SALT] * t.eta * t.qdim * t.QSnd; // probe.F90:414 assigns the module variable
   for (int j = 1; j <= m; j++)
     for (int i = 1; i <= n; i++, pos++) {
       dftdm[pos] = 0.0;

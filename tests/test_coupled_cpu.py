@@ -123,3 +123,17 @@ def test_derivative_field_and_coupling_blocks(name):
     open_ = [e for (row, e), M in zip(Ao, f["msi"][surf == 0]) if M == 0.0]
     assert full and all(all(a == 0.0 for _, a in e) for e in full)
     assert open_ and all(all(a != 0.0 for _, a in e) for e in open_)
+
+
+def test_get_derivatives_refreshes_nus_like_the_fortran():
+    """probe.F90:414 assigns the module variable nus from the current parameters; set_par alone does not (usrc.F90:163-181)"""
+    cfg, mask, O, H = _pair("coupled_small")
+    cases.attach(O, cfg)
+    cases.attach(H, cfg)
+    nus0 = H.getdeps()["nus"]
+    for obj in (O, H):
+        obj.set_par("COMB", 0.6)
+    assert H.getdeps()["nus"] == nus0 == O.getdeps()["nus"]
+    x = cases.state(cfg, mask, seed=5)
+    assert np.array_equal(O.dftdm(x), H.dftdm(x))
+    assert O.getdeps() == H.getdeps() and H.getdeps()["nus"] != nus0
