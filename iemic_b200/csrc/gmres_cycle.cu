@@ -3,8 +3,10 @@
 // GMRESSolver::solve (src/gmressolver/GMRESSolver.H:142-213) runs, per inner iteration, a preconditioner apply, a matrix apply,
 // the orthogonalisation, the Givens update and a convergence test.  The large-grid path of this library spends 4..6 kernel
 // launches per iteration on that (and one device -> host round trip per convergence test), which is what bounds the small
-// configurations: 2-D MOC (648 unknowns: 35 us per iteration, all launch latency and host time) and the L2-resident 4-degree
-// grid.  Here the blocks of one cooperative launch walk through the iterations themselves, separated by grid-wide barriers:
+// configurations.  The tiniest ones (2-D MOC, 648 unknowns) run inside one cluster (gmres_cluster.cu); this kernel takes the
+// sizes between that and IEMIC_GMRES_CYCLE_ROWS (20 000 rows: measured 28.3 k against 18.3 k iterations/s at 17 094 rows; at
+// the 262 656 rows of the 4-degree grid it loses, 9.5 k against 11.2 k, and is not selected).  The blocks of one cooperative
+// launch walk through the iterations themselves, separated by grid-wide barriers:
 //
 //   [z_i = B^-1 v_i]  |  w = A z_i  |  h1 = V^T w (block partials)  |  w -= V h1 ; h2 = V^T w, <w,w> (partials)  |
 //   w -= V h2 ; v_{i+1} = w / sqrt(<w,w> - |h2|^2) ; block 0: Hessenberg column, Givens, residual estimate, stop flag
