@@ -80,7 +80,9 @@ int64_t thcm_oracle_dropped_entries(thcm_oracle*); /* Fortran entries outside th
 
 /* Coupling to an atmosphere / sea-ice model: usrc.F90:237-333 (pars in the order of the bind(C) structs),
  * inserts.F90:12-166 (which: 0 tatm, 1 qatm, 2 albe, 3 patm, 4 qsa, 5 msi, 6 gsi; takes effect at the next set_* call as in the
- * Fortran), getdeps usrc.F90:201-219 (Ooa, Os, nus, eta, lvsc, qdim, pQSnd), suno(j), probe.F90:381-444 (dftdm). */
+ * Fortran), getdeps usrc.F90:201-219 (Ooa, Os, nus, eta, lvsc, qdim, pQSnd), suno(j), probe.F90:381-444 (dftdm).
+ * Pinned by the known answer of the reference's own coupling test (src/tests/test_coupled.C:402-447: the T-row sum of C12) and by
+ * differences of this oracle's F with respect to the inserted fields (tests/test_coupled_cpu.py); no stored vectors exist for it. */
 void thcm_oracle_set_atmos_parameters(thcm_oracle*, const double* pars /* 18 */);
 void thcm_oracle_set_seaice_parameters(thcm_oracle*, const double* pars /* 7 */);
 void thcm_oracle_insert(thcm_oracle*, int which, const double* field /* n*m */);

@@ -137,3 +137,65 @@ def test_get_derivatives_refreshes_nus_like_the_fortran():
     x = cases.state(cfg, mask, seed=5)
     assert np.array_equal(O.dftdm(x), H.dftdm(x))
     assert O.getdeps() == H.getdeps() and H.getdeps()["nus"] != nus0
+
+
+def test_coupling_block_known_answer_of_the_reference_test():
+    """src/tests/test_coupled.C:402-447: C12 applied to a constant atmosphere vector gives, in the T row of an ocean surface point
+    without sea ice, -(Ooa + lvsc*eta*qdim - comb*sunp*So*da) * value within 1e-7."""
+    cfg, mask, O, H = _pair("coupled_box")
+    cases.attach(O, cfg, seaice=False)
+    cases.attach(H, cfg, seaice=False)
+    n, m, l = cfg["n"], cfg["m"], cfg["l"]
+    d = H.getdeps()
+    rows, beg, jco, co = H.atmos_block()
+    suno = H.suno()
+    surf = np.asarray(mask).reshape(l + 2, m + 2, n + 2)[l, 1:-1, 1:-1]
+    checked = 0
+    for value in (1.234, 2.12, -23.5):
+        v = np.full(3 * n * m, value)
+        for r in range(rows.size):
+            cell = rows[r] // 6
+            i, j = cell % n, (cell // n) % m
+            assert rows[r] % 6 == 4 and cell // (n * m) == l - 1 and surf[j, i] == 0
+            got = sum(co[p] * v[jco[p]] for p in range(beg[r], beg[r + 1]))
+            want = -(d["Ooa"] + d["lvsc"] * d["eta"] * d["qdim"] - H.get_par("COMB") * H.get_par("SUNP") * suno[j] * cases.ATMOS_PARS["da"]) * value
+            assert abs(got - want) <= 1e-7 * max(1.0, abs(want))
+            checked += 1
+    assert checked == 3 * np.count_nonzero(surf == 0)
+
+
+def test_coupling_blocks_are_the_derivatives_of_the_residual():
+    """The blocks against the oracle's F by differences: -d F / d(atmosphere unknown) and -dF/dM at a handful of surface points
+    (the sign convention of Ocean::getBlock: "negating as the Jacobian is taken negative" means block = d F_THCM / d unknown)."""
+    cfg, mask, O, H = _pair("coupled_small")
+    f = cases.attach(O, cfg)
+    cases.attach(H, cfg)
+    n, m, l = cfg["n"], cfg["m"], cfg["l"]
+    x = cases.state(cfg, mask, seed=5)
+    A = dict((r, dict(e)) for r, e in cases.compact(H.atmos_block()))
+    S = dict((r, dict(e)) for r, e in cases.compact(H.seaice_block(H.dftdm(x))))
+
+    def F_with(field, values, seaice):
+        O.insert(field, values)
+        (O.set_seaice_parameters if seaice else O.set_atmos_parameters)(cases.SEAICE_PARS if seaice else cases.ATMOS_PARS)
+        return O.rhs(x)
+
+    rng = np.random.default_rng(0)
+    ocean_rows = sorted(A)
+    for row in rng.choice(ocean_rows, size=6, replace=False):
+        sr = (row // 6) % (n * m)
+        for field, colv, blk, seaice, h in (("tatm", 3 * sr + 0, A, False, 1e-3), ("qatm", 3 * sr + 1, A, False, 1e-7), ("albe", 3 * sr + 2, A, False, 1e-4),
+                                              ("msi", 4 * sr + 2, S, True, 1e-5)):
+            base = f[field].copy()
+            up, dn = base.copy(), base.copy()
+            up[sr] += h
+            dn[sr] -= h
+            dF = (F_with(field, up, seaice) - F_with(field, dn, seaice)) / (2 * h)
+            F_with(field, base, seaice)
+            want = blk[row][colv]
+            # the sea-ice mask also sits in the operator (mc terms of lin): F = A(M) x - Frc(M); the block holds the forcing part
+            # plus the operator part evaluated at this state, which is what dftdm = QTos - QToa contains (probe.F90:433-442)
+            assert abs(dF[row] - want) <= 1e-6 * max(abs(want), 1.0), (field, dF[row], want)
+            others = np.delete(dF, row)
+            if field != "msi":
+                assert np.abs(others).max() <= 1e-6 * max(abs(want), 1.0)
